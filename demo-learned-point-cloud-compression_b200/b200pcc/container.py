@@ -1,0 +1,94 @@
+"""Bitstream containers of the reference, written with ``struct`` instead of the
+``bitstream`` package's bit strings (sender/encoder/codec_pipeline.py:464-517 <->
+receiver/decoder/codec_parallel.py:173-216 for the batched layout; codec_single.py:269-337 <->
+receiver/decoder/codec_single.py:90-136 for the per-frame layout).  Field order, widths and
+endianness are the reference's (int32 / float64, big endian); the y/z strings are this repository's
+PCL1 lane containers and ``points_i`` is the octree stream of geometry.py instead of a tmc3 stream.
+"""
+import struct
+from typing import List, Sequence, Tuple
+
+
+def make_bitstream_batched(y_string: bytes, z_string: bytes, y_shape: int, z_shape: int,
+                           points_streams: Sequence[bytes], ks, q) -> bytes:
+    """One blob per quality per GOP (codec_pipeline.py:464-517)."""
+    num_frames = len(points_streams)
+    parts = [struct.pack(">idd", num_frames, float(q[0]), float(q[1])),
+             struct.pack(">iiii", int(y_shape), int(z_shape), len(y_string), len(z_string)),
+             y_string, z_string]
+    for i in range(num_frames):
+        p = points_streams[i]
+        parts.append(struct.pack(">iiii", len(p), int(ks[0][i]), int(ks[1][i]), int(ks[2][i])))
+        parts.append(p)
+    return b"".join(parts)
+
+
+def read_bitstream_batched(data: bytes):
+    """-> y_strings, z_strings, y_shape, z_shape, points_streams, ks, q (codec_parallel.py:173-216)."""
+    mv = memoryview(data)
+    pos = 0
+
+    def take(fmt):
+        nonlocal pos
+        sz = struct.calcsize(fmt)
+        if pos + sz > len(mv):
+            raise ValueError("truncated bitstream")
+        v = struct.unpack_from(fmt, mv, pos)
+        pos += sz
+        return v
+
+    def take_bytes(n):
+        nonlocal pos
+        if n < 0 or pos + n > len(mv):
+            raise ValueError("truncated bitstream")
+        b = bytes(mv[pos:pos + n])
+        pos += n
+        return b
+
+    num_frames, q_g, q_a = take(">idd")
+    y_shape, z_shape, y_len, z_len = take(">iiii")
+    y_string = take_bytes(y_len)
+    z_string = take_bytes(z_len)
+    points_streams, ks = [], [[], [], []]
+    if num_frames < 0 or num_frames > 65534:
+        raise ValueError("bad frame count")
+    for _ in range(num_frames):
+        plen, k1, k2, k3 = take(">iiii")
+        ks[0].append(k1)
+        ks[1].append(k2)
+        ks[2].append(k3)
+        points_streams.append(take_bytes(plen))
+    return [y_string], [z_string], y_shape, z_shape, points_streams, ks, (q_g, q_a)
+
+
+def make_bitstream(y_strings: Sequence[bytes], z_strings: Sequence[bytes], y_shapes: Sequence[int],
+                   z_shapes: Sequence[int], points_streams: Sequence[bytes], ks, q) -> bytes:
+    """Per-frame layout (codec_single.py:269-337)."""
+    num_frames = len(y_strings)
+    parts = [struct.pack(">idd", num_frames, float(q[0]), float(q[1]))]
+    for i in range(num_frames):
+        p, ys, zs = points_streams[i], y_strings[i], z_strings[i]
+        parts.append(struct.pack(">iiiiiiii", int(y_shapes[i]), int(z_shapes[i]), len(p), len(ys), len(zs),
+                                 int(ks[0][i]), int(ks[1][i]), int(ks[2][i])))
+        parts += [p, ys, zs]
+    return b"".join(parts)
+
+
+def read_bitstream(data: bytes):
+    """Per-frame layout reader (receiver/decoder/codec_single.py:90-136)."""
+    mv = memoryview(data)
+    pos = 0
+    num_frames, q_g, q_a = struct.unpack_from(">idd", mv, pos)
+    pos += struct.calcsize(">idd")
+    y_strings, z_strings, y_shapes, z_shapes, points_streams, ks = [], [], [], [], [], [[], [], []]
+    for _ in range(num_frames):
+        ysh, zsh, plen, ylen, zlen, k1, k2, k3 = struct.unpack_from(">iiiiiiii", mv, pos)
+        pos += 32
+        if min(plen, ylen, zlen) < 0 or pos + plen + ylen + zlen > len(mv):
+            raise ValueError("truncated bitstream")
+        points_streams.append(bytes(mv[pos:pos + plen])); pos += plen
+        y_strings.append(bytes(mv[pos:pos + ylen])); pos += ylen
+        z_strings.append(bytes(mv[pos:pos + zlen])); pos += zlen
+        y_shapes.append(ysh); z_shapes.append(zsh)
+        ks[0].append(k1); ks[1].append(k2); ks[2].append(k3)
+    return y_strings, z_strings, y_shapes, z_shapes, points_streams, ks, (q_g, q_a)

@@ -1,0 +1,592 @@
+"""ColorModel-shaped object graph on the B200 kernels.
+
+Mirrors the surface of ``unified.model.model.ColorModel`` that the reference pipelines touch
+(sender/encoder/codec_pipeline.py:56-72, 273, 287, 305-306, 354, 418-430;
+receiver/decoder/codec_parallel.py:302-307, 376, 394-409, 469):
+
+    ColorModel(config) .load_state_dict .to .update() .eval()
+      .g_a(x) -> (y, k)         .g_s(y_hat, k=ks)        .g_s.down_conv(t)
+      .entropy_model.h_a(y)  .h_s(z_hat)  .scale_nn(q)  .eps  .get_offsets(stdev, scale)
+      .entropy_model.entropy_bottleneck.compress(x) / .decompress(strings, size)
+      .entropy_model.gaussian_conditional.build_indexes(s) / .compress(x, idx, means=) /
+          .decompress(strings, idx) / .lower_bound_scale(s)
+
+The layer graph is the canonical stand-in of config.py.  All sparse convolutions run through
+libpcc_b200.so: tcgen05 gather-GEMM for wide layers, the CUDA-core path for <= 8 output channels.
+"""
+import math
+from typing import List, Optional
+
+import numpy as np
+import torch
+
+from . import ops
+from . import config as cfgmod
+from .sparse import CoordMap, SparseTensor
+
+SCALE_MIN, SCALE_MAX, SCALE_LEVELS = 0.11, 256.0, 64
+SCALE_BOUND = 0.11
+TAIL_MASS = 1e-9
+
+
+def _pad16(c: int) -> int:
+    return (c + 15) // 16 * 16
+
+
+# ------------------------------------------------------------------------------------------------------
+# convolution layers
+# ------------------------------------------------------------------------------------------------------
+class Conv:
+    """One sparse convolution's parameters, prepared for the kernels on ``.to(device)``."""
+
+    def __init__(self, name: str, kvol: int, cin: int, cout: int):
+        self.name, self.kvol, self.cin, self.cout = name, kvol, cin, cout
+        self.kernel = np.zeros((kvol, cin, cout), dtype=np.float32)
+        self.bias = np.zeros(cout, dtype=np.float32)
+        self.device = None
+        self.narrow = cout <= 8
+        self.cin_pad = _pad16(cin)
+
+    def load(self, sd):
+        k = np.asarray(sd[self.name + ".kernel"], dtype=np.float32)
+        b = np.asarray(sd[self.name + ".bias"], dtype=np.float32).reshape(-1)
+        if k.shape != self.kernel.shape or b.shape != self.bias.shape:
+            raise ValueError(f"{self.name}: state_dict shape {k.shape}/{b.shape} != {self.kernel.shape}/{self.bias.shape}")
+        self.kernel, self.bias = k.copy(), b.copy()
+
+    def to(self, device):
+        self.device = device
+        self.bias_d = torch.from_numpy(self.bias).to(device)
+        if self.narrow:
+            w = np.zeros((self.kvol, self.cin_pad, self.cout), dtype=np.float32)
+            w[:, : self.cin] = self.kernel
+            self.w_d = torch.from_numpy(w).to(device).to(torch.bfloat16).contiguous()
+        else:
+            self.w_d = ops.pack_weights_umma(self.kernel, self.cin_pad).to(device)
+        return self
+
+    def __call__(self, x: torch.Tensor, nbr: Optional[torch.Tensor], n_out: int, relu=False,
+                 residual: Optional[torch.Tensor] = None, out_f32=False):
+        """x: bf16 [n_in, cin_pad].  Returns bf16 [n_out, cout] (or fp32 when out_f32)."""
+        dev = x.device
+        if self.narrow:
+            out = torch.empty((n_out, self.cout), dtype=torch.float32, device=dev)
+            ops.spconv_simt(x, nbr, n_out, self.kvol, self.w_d, self.bias_d, self.cout, residual, relu, None, out)
+            return out
+        ob = of = None
+        if out_f32:
+            of = torch.empty((n_out, self.cout), dtype=torch.float32, device=dev)
+        else:
+            ob = torch.empty((n_out, self.cout), dtype=torch.bfloat16, device=dev)
+        ops.spconv_umma(x, nbr, n_out, self.kvol, self.w_d, self.bias_d, self.cout, residual, relu, ob, of)
+        return of if out_f32 else ob
+
+
+class GenUp:
+    """k=2, s=2 generative transposed convolution in its dense form: out viewed as
+    [n_parent, 8*cout] = in [n_parent, cin] @ concat_j W[j]; child row 8p+j holds columns
+    [j*cout, (j+1)*cout).  Column chunks of <= 256 go through the tcgen05 kernel."""
+
+    def __init__(self, name: str, cin: int, cout: int):
+        self.name, self.cin, self.cout = name, cin, cout
+        self.kernel = np.zeros((8, cin, cout), dtype=np.float32)
+        self.bias = np.zeros(cout, dtype=np.float32)
+        self.cin_pad = _pad16(cin)
+
+    def load(self, sd):
+        k = np.asarray(sd[self.name + ".kernel"], dtype=np.float32)
+        b = np.asarray(sd[self.name + ".bias"], dtype=np.float32).reshape(-1)
+        if k.shape != self.kernel.shape or b.shape != self.bias.shape:
+            raise ValueError(f"{self.name}: bad state_dict shapes")
+        self.kernel, self.bias = k.copy(), b.copy()
+
+    def to(self, device):
+        wcat = np.concatenate([self.kernel[j] for j in range(8)], axis=1)  # [cin, 8*cout]
+        bcat = np.tile(self.bias, 8)
+        total = 8 * self.cout
+        self.chunks = []
+        c0 = 0
+        while c0 < total:
+            cw = min(256, total - c0)
+            wp = ops.pack_weights_umma(wcat[None, :, c0:c0 + cw], self.cin_pad).to(device)
+            bd = torch.from_numpy(bcat[c0:c0 + cw].copy()).to(device)
+            self.chunks.append((c0, cw, wp, bd))
+            c0 += cw
+        return self
+
+    def __call__(self, x: torch.Tensor, relu=True) -> torch.Tensor:
+        n = x.shape[0]
+        out = torch.empty((n, 8 * self.cout), dtype=torch.bfloat16, device=x.device)
+        for c0, cw, wp, bd in self.chunks:
+            ops.spconv_umma(x, None, n, 1, wp, bd, cw, None, relu, out, None, col0=c0)
+        return out.view(8 * n, self.cout)
+
+
+class _Module:
+    def convs(self) -> List:
+        out = []
+        for v in self.__dict__.values():
+            if isinstance(v, (Conv, GenUp)):
+                out.append(v)
+            elif isinstance(v, (list, tuple)):
+                for e in v:
+                    if isinstance(e, (Conv, GenUp)):
+                        out.append(e)
+                    elif isinstance(e, (list, tuple)):
+                        out.extend(x for x in e if isinstance(x, (Conv, GenUp)))
+        return out
+
+
+def _resblock(c0: Conv, c1: Conv, cmap: CoordMap, x: torch.Tensor) -> torch.Tensor:
+    nbr = cmap.nbr3()
+    h = c0(x, nbr, cmap.n, relu=True)
+    return c1(h, nbr, cmap.n, relu=True, residual=x)
+
+
+class AnalysisTransform(_Module):
+    def __init__(self, cfg):
+        self.cfg = cfg
+        self.stem = Conv("g_a.stem", 27, cfg["c_in"], cfg["stem"])
+        self.down, self.blocks = [], []
+        cprev = cfg["stem"]
+        for i, c in enumerate(cfg["widths"]):
+            self.down.append(Conv(f"g_a.down{i}", 8, cprev, c))
+            self.blocks.append([Conv(f"g_a.block{i}_{b}.conv{j}", 27, c, c)
+                                for b in range(cfg["blocks"]) for j in range(2)])
+            cprev = c
+        self.head = Conv("g_a.head", 1, cprev, cfg["c_y"])
+
+    def __call__(self, x: SparseTensor):
+        """g_a(x) -> (y, k): y at tensor stride 8 (fp32 features), k[level][frame] point counts
+        (codec_pipeline.py:273, 505-507)."""
+        cm = x.cmap
+        num_frames = int(x.num_frames) if hasattr(x, "num_frames") else None
+        f = x.feats_bf16(self.stem.cin_pad)
+        if num_frames is None:
+            num_frames = int((cm.keys[-1:] >> 48).item()) + 1 if cm.n else 0
+        f = self.stem(f, cm.nbr3(), cm.n, relu=True)
+        offs = []
+        for i in range(len(self.down)):
+            offs.append(ops.frame_offsets(cm.keys, num_frames))
+            coarse = cm.downsample()
+            f = self.down[i](f, cm.nbr_down(), coarse.n, relu=True)
+            cm.release_maps()
+            cm = coarse
+            blk = self.blocks[i]
+            for b in range(0, len(blk), 2):
+                f = _resblock(blk[b], blk[b + 1], cm, f)
+        yf = self.head(f, None, cm.n, out_f32=True)
+        offs_h = torch.stack(offs).cpu().numpy()  # one D2H for all three levels
+        counts = [list(map(int, np.diff(o))) for o in offs_h]
+        k = counts[::-1]
+        y = SparseTensor(_cmap=cm, _feats=yf, _channels=self.cfg["c_y"])
+        y.num_frames = num_frames
+        return y, k
+
+
+class SynthesisTransform(_Module):
+    def __init__(self, cfg):
+        self.cfg = cfg
+        w = cfg["widths"]
+        self.pre = Conv("g_s.pre", 1, cfg["c_y"], w[-1])
+        ups = [w[1], w[0], cfg["stem"]]
+        self.up, self.blocks, self.occ = [], [], []
+        cprev = w[-1]
+        for i, c in enumerate(ups):
+            self.up.append(GenUp(f"g_s.up{i}", cprev, c))
+            self.blocks.append([Conv(f"g_s.block{i}_{b}.conv{j}", 27, c, c)
+                                for b in range(cfg["blocks"]) for j in range(2)])
+            self.occ.append(Conv(f"g_s.occ{i}", 27, c, 1))
+            cprev = c
+        self.color = Conv("g_s.color", 27, cprev, 3)
+        self.down_conv_w = Conv("g_s.down_conv", 8, 1, 1)
+
+    def down_conv(self, t: SparseTensor) -> SparseTensor:
+        """g_s.down_conv(t): MinkowskiConvolution(1,1,k=2,s=2) used by the decoder only for its output
+        coordinates (codec_parallel.py:302-303)."""
+        cm = t.cmap
+        coarse = cm.downsample()
+        f = t.feats_bf16(self.down_conv_w.cin_pad)
+        out = self.down_conv_w(f, cm.nbr_down(), coarse.n)
+        r = SparseTensor(_cmap=coarse, _feats=out, _channels=1)
+        if hasattr(t, "num_frames"):
+            r.num_frames = t.num_frames
+        return r
+
+    def __call__(self, y_hat: SparseTensor, k=None, return_intermediates=False):
+        """g_s(y_hat, k=ks): three generative up-samplings, each followed by occupancy logits and the
+        per-frame top-k prune; colour head (codec_parallel.py:469)."""
+        cm = y_hat.cmap
+        num_frames = len(k[0])
+        dev = cm.device
+        f = y_hat.feats_bf16(self.pre.cin_pad)
+        f = self.pre(f, None, cm.n, relu=True)
+        inter = []
+        for i in range(3):
+            f = self.up[i](f, relu=True)
+            cm = cm.children()
+            blk = self.blocks[i]
+            for b in range(0, len(blk), 2):
+                f = _resblock(blk[b], blk[b + 1], cm, f)
+            logits = self.occ[i](f, cm.nbr3(), cm.n)
+            off = ops.frame_offsets(cm.keys, num_frames)
+            kd = torch.tensor(list(k[i]), dtype=torch.int32, device=dev)
+            keep = ops.topk_select(logits.view(-1), cm.keys, off, kd, num_frames)
+            if return_intermediates:
+                inter.append({"keys": cm.keys, "F": f, "logits": logits, "keep": keep})
+            pruned = cm.subset(keep)
+            f = ops.gather_rows(f, keep)
+            cm.release_maps()
+            cm = pruned
+        colors = self.color(f, cm.nbr3(), cm.n)
+        out = SparseTensor(_cmap=cm, _feats=colors, _channels=3)
+        out.num_frames = num_frames
+        if return_intermediates:
+            return out, inter
+        return out
+
+
+class HyperAnalysis(_Module):
+    def __init__(self, cfg):
+        self.down0 = Conv("entropy_model.h_a.down0", 8, cfg["c_y"], cfg["c_h"])
+        self.down1 = Conv("entropy_model.h_a.down1", 8, cfg["c_h"], cfg["c_z"])
+        self.cfg = cfg
+
+    def __call__(self, y: SparseTensor) -> SparseTensor:
+        cm = y.cmap
+        f = y.feats_bf16(self.down0.cin_pad)
+        c1 = cm.downsample()
+        f = self.down0(f, cm.nbr_down(), c1.n, relu=True)
+        c2 = c1.downsample()
+        z = self.down1(f, c1.nbr_down(), c2.n, out_f32=True)
+        out = SparseTensor(_cmap=c2, _feats=z, _channels=self.cfg["c_z"])
+        if hasattr(y, "num_frames"):
+            out.num_frames = y.num_frames
+        return out
+
+
+class HyperSynthesis(_Module):
+    def __init__(self, cfg):
+        self.up0 = GenUp("entropy_model.h_s.up0", cfg["c_z"], cfg["c_h"])
+        self.up1 = GenUp("entropy_model.h_s.up1", cfg["c_h"], cfg["c_h"])
+        self.head = Conv("entropy_model.h_s.head", 1, cfg["c_h"], 2 * cfg["c_y"])
+        self.cfg = cfg
+
+    def __call__(self, z_hat: SparseTensor) -> SparseTensor:
+        cm = z_hat.cmap
+        f = z_hat.feats_bf16(self.up0.cin_pad)
+        f = self.up0(f, relu=True)
+        cm = cm.children()
+        f = self.up1(f, relu=True)
+        cm = cm.children()
+        p = self.head(f, None, cm.n, out_f32=True)
+        return SparseTensor(_cmap=cm, _feats=p, _channels=2 * self.cfg["c_y"])
+
+
+# ------------------------------------------------------------------------------------------------------
+# entropy models
+# ------------------------------------------------------------------------------------------------------
+def _std_round_clip(a):
+    return a
+
+
+class _CodedModel:
+    """Shared by both entropy models: device CDF tables + PCL1 string coding."""
+
+    tables: ops.DeviceCdfTables = None
+    seg_size = ops.DEFAULT_SEG
+
+    def _encode(self, sym_flat: torch.Tensor, idx_flat: Optional[torch.Tensor], chan_len: int) -> bytes:
+        buf, nbytes = ops.rans_encode(sym_flat, idx_flat, chan_len, self.tables, self.seg_size)
+        nb = int(nbytes.item())
+        return bytes(buf[:nb].cpu().numpy().tobytes())
+
+    def _decode(self, string: bytes, idx_flat: Optional[torch.Tensor], chan_len: int, n: int, device):
+        if len(string) < 16:
+            raise ops._lib.PccError("rANS container too short")
+        hdr = np.frombuffer(string[:16], dtype=np.uint32)
+        if hdr[0] != 0x314C4350 or int(hdr[1]) != n:
+            raise ops._lib.PccError("rANS container header mismatch")
+        seg_size = int(hdr[2])
+        arr = np.frombuffer(string, dtype=np.uint8)
+        pad = (-len(arr)) % 4
+        if pad:
+            arr = np.concatenate([arr, np.zeros(pad, np.uint8)])
+        cont = torch.from_numpy(arr.copy()).to(device)
+        sym, status = ops.rans_decode(cont, seg_size, idx_flat, chan_len, n, self.tables)
+        return sym, status
+
+
+class EntropyBottleneck(_CodedModel):
+    """CompressAI EntropyBottleneck surface used by the reference (codec_pipeline.py:305-306,
+    codec_parallel.py:307): per-channel factorized prior, symbols = round(z - median_c)."""
+
+    def __init__(self, channels: int, filters=(3, 3, 3, 3)):
+        self.channels = channels
+        self.filters = tuple(filters)
+        self.matrices, self.biases, self.factors = [], [], []
+        self.quantiles = None
+        self.device = None
+
+    def load(self, sd, prefix="entropy_model.entropy_bottleneck."):
+        n = len(self.filters) + 1
+        self.matrices = [np.asarray(sd[f"{prefix}matrices.{i}"], np.float32) for i in range(n)]
+        self.biases = [np.asarray(sd[f"{prefix}biases.{i}"], np.float32) for i in range(n)]
+        self.factors = [np.asarray(sd[f"{prefix}factors.{i}"], np.float32) for i in range(n - 1)]
+        self.quantiles = np.asarray(sd[f"{prefix}quantiles"], np.float32)
+
+    @staticmethod
+    def _softplus(x):
+        return np.maximum(x, 0) + np.log1p(np.exp(-np.abs(x)))
+
+    def _logits_cumulative(self, x):
+        logits = x
+        for i in range(len(self.matrices)):
+            logits = np.matmul(self._softplus(self.matrices[i].astype(np.float64)), logits) + \
+                self.biases[i].astype(np.float64)
+            if i < len(self.factors):
+                logits = logits + np.tanh(self.factors[i].astype(np.float64)) * np.tanh(logits)
+        return logits
+
+    def update(self, device, force=True):
+        q = self.quantiles.astype(np.float64)
+        medians = q[:, 0, 1]
+        minima = np.maximum(np.ceil(medians - q[:, 0, 0]), 0).astype(np.int64)
+        maxima = np.maximum(np.ceil(q[:, 0, 2] - medians), 0).astype(np.int64)
+        pmf_start = medians - minima
+        pmf_length = maxima + minima + 1
+        max_length = int(pmf_length.max())
+        samples = np.arange(max_length, dtype=np.float64)[None, None, :] + pmf_start[:, None, None]
+        lower = self._logits_cumulative(samples - 0.5)
+        upper = self._logits_cumulative(samples + 0.5)
+        sign = -np.sign(lower + upper)
+        sig = lambda v: 1.0 / (1.0 + np.exp(-v))
+        pmf = np.abs(sig(sign * upper) - sig(sign * lower))[:, 0, :]
+        tail = sig(lower[:, 0, :1]) + sig(-upper[:, 0, -1:])
+        rows = []
+        for c in range(self.channels):
+            L = int(pmf_length[c])
+            rows.append(ops.pmf_to_quantized_cdf(np.concatenate([pmf[c, :L], tail[c]]).astype(np.float32)))
+        self._quantized_cdf = rows
+        self._cdf_length = (pmf_length + 2).astype(np.int32)
+        self._offset = (-minima).astype(np.int32)
+        self.medians = medians.astype(np.float32)
+        self.device = device
+        self.tables = ops.DeviceCdfTables(rows, self._offset, device)
+        self.medians_d = torch.from_numpy(self.medians).to(device)
+        return True
+
+    # symbols for z [n, C] rows in key order, serialised channel-major in canonical column order
+    def quantize_rows(self, z_rows: torch.Tensor, perm: torch.Tensor):
+        return ops.factorized_quant(z_rows, perm, self.medians_d)
+
+    def compress_rows(self, z_rows: torch.Tensor, perm: torch.Tensor):
+        sym, zb, _ = self.quantize_rows(z_rows, perm)
+        n = z_rows.shape[0]
+        return [self._encode(sym.view(-1), None, n)], zb
+
+    def decompress_rows(self, strings, n: int, perm: torch.Tensor):
+        sym, status = self._decode(strings[0], None, n, n * self.channels, self.device)
+        zb, _ = ops.factorized_dequant(sym.view(self.channels, n), perm, self.medians_d)
+        return zb, status
+
+    # CompressAI-shaped entry points (x: [1, C, N] in canonical column order)
+    def compress(self, x: torch.Tensor):
+        assert x.dim() == 3 and x.shape[0] == 1
+        rows = x[0].t().contiguous().float()
+        return self.compress_rows(rows, None)[0]
+
+    def decompress(self, strings, size):
+        n = int(size[0]) if isinstance(size, (list, tuple)) else int(size)
+        zb, status = self.decompress_rows(strings, n, None)
+        if int(status.item()) != 0:
+            raise ops._lib.PccError(f"rANS decode failed (status {int(status.item())})")
+        return zb.float().t().unsqueeze(0)
+
+
+class GaussianConditional(_CodedModel):
+    """CompressAI GaussianConditional surface used by the reference (codec_pipeline.py:425-430,
+    codec_parallel.py:398-403)."""
+
+    def __init__(self):
+        self.scale_bound = SCALE_BOUND
+        self.scale_table = np.exp(np.linspace(math.log(SCALE_MIN), math.log(SCALE_MAX), SCALE_LEVELS)).astype(
+            np.float32)
+        self.device = None
+
+    def update(self, device):
+        from scipy.special import erfc, ndtri
+        t64 = self.scale_table.astype(np.float64)
+        multiplier = -ndtri(TAIL_MASS / 2)
+        pmf_center = np.ceil(t64 * multiplier).astype(np.int64)
+        pmf_length = 2 * pmf_center + 1
+        phi = lambda x: 0.5 * erfc(-x / math.sqrt(2.0))
+        rows = []
+        for i, s in enumerate(t64):
+            samples = np.abs(np.arange(pmf_length[i]) - pmf_center[i]).astype(np.float64)
+            upper = phi((0.5 - samples) / s)
+            lower = phi((-0.5 - samples) / s)
+            pmf = upper - lower
+            tail = 2.0 * lower[:1]
+            rows.append(ops.pmf_to_quantized_cdf(np.concatenate([pmf, tail]).astype(np.float32)))
+        self._quantized_cdf = rows
+        self._cdf_length = (pmf_length + 2).astype(np.int32)
+        self._offset = (-pmf_center).astype(np.int32)
+        self.device = device
+        self.tables = ops.DeviceCdfTables(rows, self._offset, device)
+        self.table_d = torch.from_numpy(self.scale_table).to(device)
+
+    def lower_bound_scale(self, s: torch.Tensor) -> torch.Tensor:
+        return torch.clamp_min(s, self.scale_bound)
+
+    def build_indexes(self, scales: torch.Tensor) -> torch.Tensor:
+        """scales [B, C, N] (already multiplied by the gain) -> int32 indexes."""
+        B, Cc, N = scales.shape
+        flat = scales.reshape(B * Cc, N).t().contiguous().float()       # rows = columns, "channels" = B*C
+        zeros = torch.zeros_like(flat)
+        params = torch.cat([flat, zeros], dim=1).contiguous()
+        ones = torch.ones(B * Cc, dtype=torch.float32, device=scales.device)
+        idx = ops.gauss_indexes(params, None, None, ones, self.table_d, self.scale_bound, N, B * Cc)
+        return idx.view(B, Cc, N).int()
+
+    def compress(self, x: torch.Tensor, indexes: torch.Tensor, means: Optional[torch.Tensor] = None):
+        """x, indexes, means [B, C, N] -> list of B strings (symbols = round(x - means))."""
+        d = x if means is None else x - means
+        sym = torch.round(d).clamp_(-2.0 ** 30, 2.0 ** 30).int().contiguous()
+        out = []
+        for b in range(x.shape[0]):
+            out.append(self._encode(sym[b].reshape(-1), indexes[b].reshape(-1).to(torch.int16).contiguous(), 1))
+        return out
+
+    def decompress(self, strings, indexes: torch.Tensor):
+        outs = []
+        for b, s in enumerate(strings):
+            idx = indexes[b].reshape(-1).to(torch.int16).contiguous()
+            sym, status = self._decode(s, idx, 1, idx.numel(), indexes.device)
+            if int(status.item()) != 0:
+                raise ops._lib.PccError(f"rANS decode failed (status {int(status.item())})")
+            outs.append(sym.view(indexes.shape[1:]).float())
+        return torch.stack(outs)
+
+
+class ScaleNN:
+    """Rate-control gain q=(q_geo,q_att) -> per-channel gain (entropy_model.scale_nn,
+    codec_pipeline.py:418, codec_parallel.py:394).  Evaluated on the host as sequential fp32
+    accumulation: encoder and decoder (different machines in the demo) must agree bit for bit."""
+
+    def __init__(self, hidden, cy):
+        self.w1 = np.zeros((2, hidden), np.float32)
+        self.b1 = np.zeros(hidden, np.float32)
+        self.w2 = np.zeros((hidden, cy), np.float32)
+        self.b2 = np.zeros(cy, np.float32)
+
+    def load(self, sd, prefix="entropy_model.scale_nn."):
+        for k in ("w1", "b1", "w2", "b2"):
+            a = np.asarray(sd[prefix + k], np.float32)
+            if a.shape != getattr(self, k).shape:
+                raise ValueError(f"scale_nn.{k}: bad shape {a.shape}")
+            setattr(self, k, a.copy())
+
+    def numpy(self, q) -> np.ndarray:
+        q = np.asarray(q, dtype=np.float32).reshape(-1, 2)
+        outs = []
+        for row in q:
+            h = self.b1.copy()
+            for k in range(2):
+                h = h + self.w1[k] * row[k]
+            h = np.maximum(h, np.float32(0))
+            o = self.b2.copy()
+            for k in range(h.shape[0]):
+                o = o + self.w2[k] * h[k]
+            outs.append((np.maximum(o, 0) + np.log1p(np.exp(-np.abs(o)))).astype(np.float32))
+        return np.stack(outs)
+
+    def __call__(self, q: torch.Tensor) -> torch.Tensor:
+        out = self.numpy(q.detach().cpu().numpy())
+        return torch.from_numpy(out).to(q.device)
+
+
+class EntropyModel:
+    def __init__(self, cfg):
+        self.cfg = cfg
+        self.h_a = HyperAnalysis(cfg)
+        self.h_s = HyperSynthesis(cfg)
+        self.entropy_bottleneck = EntropyBottleneck(cfg["c_z"], cfg["eb_filters"])
+        self.gaussian_conditional = GaussianConditional()
+        self.scale_nn = ScaleNN(cfg["scale_nn_hidden"], cfg["c_y"])
+        self.eps = float(cfg["eps"])
+        self.offset_gain = np.ones(cfg["c_y"], np.float32)
+        self.offset_gain_d = None
+
+    def get_offsets(self, stdev: torch.Tensor, scale: torch.Tensor) -> torch.Tensor:
+        """Centroid shift (toward zero) of a unit bin for a Laplacian of std `stdev`, times the
+        per-channel gain; broadcastable to [1, Cy, Ny] (codec_parallel.py:405)."""
+        b = stdev * 0.70710678118654752
+        ib = 1.0 / b
+        far = ib * (1.0 / 12.0) - ib * ib * ib * (1.0 / 720.0)
+        near = 0.5 / torch.tanh(0.5 / b) - b
+        d = torch.where(b > 4.0, far, near).clamp(0.0, 0.5)
+        g = torch.from_numpy(self.offset_gain).to(stdev.device).view(1, -1, 1)
+        return d * g
+
+    def scale_for(self, settings, device) -> torch.Tensor:
+        """[Q, Cy] gains = scale_nn(q) + eps for a list of [q_geo, q_att]."""
+        s = self.scale_nn.numpy(np.asarray(settings, dtype=np.float32)) + np.float32(self.eps)
+        return torch.from_numpy(s.astype(np.float32)).to(device)
+
+
+class ColorModel:
+    def __init__(self, config=None):
+        if config is None:
+            config = cfgmod.SYNTH_SMALL
+        if isinstance(config, str):
+            config = cfgmod.CONFIGS[config]
+        self.config = dict(cfgmod.SYNTH_SMALL, **config)
+        self.g_a = AnalysisTransform(self.config)
+        self.g_s = SynthesisTransform(self.config)
+        self.entropy_model = EntropyModel(self.config)
+        self.device = None
+        self._sd = None
+        self.load_state_dict(cfgmod.make_state_dict(self.config))
+
+    def _all_convs(self):
+        em = self.entropy_model
+        return self.g_a.convs() + self.g_s.convs() + em.h_a.convs() + em.h_s.convs()
+
+    def state_dict(self):
+        return dict(self._sd)
+
+    def load_state_dict(self, sd, strict=True):
+        sd = {k: (v.detach().cpu().numpy() if isinstance(v, torch.Tensor) else np.asarray(v)) for k, v in sd.items()}
+        for c in self._all_convs():
+            c.load(sd)
+        em = self.entropy_model
+        em.entropy_bottleneck.load(sd)
+        em.scale_nn.load(sd)
+        em.offset_gain = np.asarray(sd["entropy_model.offset_gain"], np.float32).copy()
+        self._sd = sd
+        if self.device is not None:
+            self.to(self.device)
+        return self
+
+    def to(self, device):
+        device = torch.device(device)
+        if device.type != "cuda":
+            raise RuntimeError("b200pcc.ColorModel runs on CUDA devices only (no CPU fallback)")
+        self.device = device
+        with torch.cuda.device(device):
+            for c in self._all_convs():
+                c.to(device)
+            self.entropy_model.offset_gain_d = torch.from_numpy(self.entropy_model.offset_gain).to(device)
+        return self
+
+    def update(self, force=True):
+        if self.device is None:
+            raise RuntimeError("call .to(device) before .update()")
+        with torch.cuda.device(self.device):
+            self.entropy_model.gaussian_conditional.update(self.device)
+            self.entropy_model.entropy_bottleneck.update(self.device, force=force)
+        return True
+
+    def eval(self):
+        return self

@@ -1,0 +1,379 @@
+"""Tensor-level wrappers over the C ABI (include/pcc_b200.h).
+
+torch is used for device memory and streams only: every function hands raw ``data_ptr()``s and the
+current CUDA stream to libpcc_b200.so.  Nothing here computes on the host.
+"""
+import ctypes as C
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import lib, check, CdfTables
+
+_WS = {}
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    if t is None:
+        return None
+    return t.data_ptr()
+
+
+def workspace(nbytes: int, device, slot: str = "ws") -> torch.Tensor:
+    """Growing per-device scratch buffer (stream ordered reuse on the current stream)."""
+    key = (str(device), slot)
+    buf = _WS.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(int(nbytes * 1.25), 1 << 20), dtype=torch.uint8, device=device)
+        _WS[key] = buf
+    return buf
+
+
+def _need_cuda(t: torch.Tensor, dtype=None):
+    if not t.is_cuda:
+        raise _lib.PccError("b200pcc kernels need CUDA tensors; there is no CPU fallback")
+    if dtype is not None and t.dtype != dtype:
+        raise _lib.PccError(f"expected dtype {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise _lib.PccError("expected a contiguous tensor")
+
+
+# ------------------------------------------------------------------------------------------------
+# coordinates
+# ------------------------------------------------------------------------------------------------
+def keys_from_coords(coords: torch.Tensor) -> torch.Tensor:
+    """[N,4] int32 or float32 (b,x,y,z) -> uint64 keys stored as int64 tensor."""
+    _need_cuda(coords)
+    n = coords.shape[0]
+    keys = torch.empty(n, dtype=torch.int64, device=coords.device)
+    if coords.dtype == torch.int32:
+        check(lib.pcc_keys_from_coords_i32(_ptr(coords), n, _ptr(keys), _stream()))
+    elif coords.dtype == torch.float32:
+        check(lib.pcc_keys_from_coords_f32(_ptr(coords), n, _ptr(keys), _stream()))
+    else:
+        raise _lib.PccError(f"coordinates must be int32 or float32, got {coords.dtype}")
+    return keys
+
+
+def ingest_frame(points_i16: torch.Tensor, colors_f64: torch.Tensor, batch: int, keys_out: torch.Tensor,
+                 feats_out: torch.Tensor) -> None:
+    _need_cuda(points_i16, torch.int16)
+    _need_cuda(colors_f64, torch.float64)
+    n = points_i16.shape[0]
+    check(lib.pcc_ingest_frame(_ptr(points_i16), _ptr(colors_f64), n, batch, _ptr(keys_out), _ptr(feats_out),
+                               _stream()))
+
+
+def coords_from_keys(keys: torch.Tensor) -> torch.Tensor:
+    _need_cuda(keys, torch.int64)
+    n = keys.shape[0]
+    out = torch.empty((n, 4), dtype=torch.int32, device=keys.device)
+    check(lib.pcc_coords_from_keys(_ptr(keys), n, _ptr(out), _stream()))
+    return out
+
+
+def sort_unique(keys: torch.Tensor, want_src: bool = True):
+    """-> (unique sorted keys, src_row or None).  One host sync for the count."""
+    _need_cuda(keys, torch.int64)
+    n = keys.shape[0]
+    dev = keys.device
+    out = torch.empty(n, dtype=torch.int64, device=dev)
+    src = torch.empty(n, dtype=torch.int32, device=dev) if want_src else None
+    cnt = torch.empty(1, dtype=torch.int32, device=dev)
+    wsb = lib.pcc_sort_unique_workspace_bytes(n)
+    ws = workspace(wsb, dev)
+    check(lib.pcc_sort_unique(_ptr(keys), n, _ptr(out), _ptr(src), _ptr(cnt), _ptr(ws), ws.numel(), _stream()))
+    m = int(cnt.item())
+    return out[:m], (src[:m] if want_src else None)
+
+
+def coords_downsample(keys: torch.Tensor, log2_stride: int):
+    """-> (parent keys, parent_row[int32, n])."""
+    _need_cuda(keys, torch.int64)
+    n = keys.shape[0]
+    dev = keys.device
+    out = torch.empty(n, dtype=torch.int64, device=dev)
+    parent = torch.empty(n, dtype=torch.int32, device=dev)
+    cnt = torch.empty(1, dtype=torch.int32, device=dev)
+    wsb = lib.pcc_coords_downsample_workspace_bytes(n)
+    ws = workspace(wsb, dev)
+    check(lib.pcc_coords_downsample(_ptr(keys), n, log2_stride, _ptr(out), _ptr(parent), _ptr(cnt), _ptr(ws),
+                                    ws.numel(), _stream()))
+    m = int(cnt.item())
+    return out[:m], parent
+
+
+def coords_children(keys: torch.Tensor, log2_stride_out: int) -> torch.Tensor:
+    _need_cuda(keys, torch.int64)
+    n = keys.shape[0]
+    out = torch.empty(8 * n, dtype=torch.int64, device=keys.device)
+    check(lib.pcc_coords_children(_ptr(keys), n, log2_stride_out, _ptr(out), _stream()))
+    return out
+
+
+def hash_capacity(n: int) -> int:
+    cap = 8
+    while cap < 2 * n:
+        cap *= 2
+    return cap
+
+
+def hash_build(keys: torch.Tensor):
+    _need_cuda(keys, torch.int64)
+    n = keys.shape[0]
+    cap = hash_capacity(n)
+    tk = torch.empty(cap, dtype=torch.int64, device=keys.device)
+    tv = torch.empty(cap, dtype=torch.int32, device=keys.device)
+    check(lib.pcc_hash_build(_ptr(keys), n, _ptr(tk), _ptr(tv), cap, _stream()))
+    return tk, tv
+
+
+def hash_query(queries: torch.Tensor, table) -> torch.Tensor:
+    _need_cuda(queries, torch.int64)
+    tk, tv = table
+    nq = queries.shape[0]
+    rows = torch.empty(nq, dtype=torch.int32, device=queries.device)
+    check(lib.pcc_hash_query(_ptr(queries), nq, _ptr(tk), _ptr(tv), tk.shape[0], _ptr(rows), _stream()))
+    return rows
+
+
+def kmap_k3(keys: torch.Tensor, log2_stride: int, table) -> torch.Tensor:
+    tk, tv = table
+    n = keys.shape[0]
+    nbr = torch.empty((27, n), dtype=torch.int32, device=keys.device)
+    check(lib.pcc_kmap_k3(_ptr(keys), n, log2_stride, _ptr(tk), _ptr(tv), tk.shape[0], _ptr(nbr), _stream()))
+    return nbr
+
+
+def kmap_down2(child_keys: torch.Tensor, parent_row: torch.Tensor, log2_child_stride: int, n_parent: int):
+    n = child_keys.shape[0]
+    nbr = torch.empty((8, n_parent), dtype=torch.int32, device=child_keys.device)
+    check(lib.pcc_kmap_down2(_ptr(child_keys), _ptr(parent_row), n, log2_child_stride, _ptr(nbr), n_parent,
+                             _stream()))
+    return nbr
+
+
+def frame_offsets(keys: torch.Tensor, num_frames: int) -> torch.Tensor:
+    off = torch.empty(num_frames + 1, dtype=torch.int32, device=keys.device)
+    check(lib.pcc_frame_offsets(_ptr(keys), keys.shape[0], num_frames, _ptr(off), _stream()))
+    return off
+
+
+def lex_order(keys: torch.Tensor) -> torch.Tensor:
+    n = keys.shape[0]
+    perm = torch.empty(n, dtype=torch.int32, device=keys.device)
+    wsb = lib.pcc_lex_order_workspace_bytes(n)
+    ws = workspace(wsb, keys.device)
+    check(lib.pcc_lex_order(_ptr(keys), n, _ptr(perm), _ptr(ws), ws.numel(), _stream()))
+    return perm
+
+
+# ------------------------------------------------------------------------------------------------
+# rows
+# ------------------------------------------------------------------------------------------------
+def rows_f32_to_bf16(src: torch.Tensor, c_dst: int, src_row: Optional[torch.Tensor] = None,
+                     n_out: Optional[int] = None) -> torch.Tensor:
+    _need_cuda(src, torch.float32)
+    n = n_out if n_out is not None else (src_row.shape[0] if src_row is not None else src.shape[0])
+    out = torch.empty((n, c_dst), dtype=torch.bfloat16, device=src.device)
+    check(lib.pcc_rows_f32_to_bf16(_ptr(src), src.shape[1], _ptr(src_row), n, _ptr(out), c_dst, _stream()))
+    return out
+
+
+def rows_bf16_to_f32(src: torch.Tensor, c_dst: int) -> torch.Tensor:
+    _need_cuda(src, torch.bfloat16)
+    n = src.shape[0]
+    out = torch.empty((n, c_dst), dtype=torch.float32, device=src.device)
+    check(lib.pcc_rows_bf16_to_f32(_ptr(src), src.shape[1], n, _ptr(out), c_dst, _stream()))
+    return out
+
+
+def gather_rows(src: torch.Tensor, src_row: torch.Tensor) -> torch.Tensor:
+    n = src_row.shape[0]
+    out = torch.empty((n, src.shape[1]), dtype=src.dtype, device=src.device)
+    if src.dtype == torch.bfloat16:
+        check(lib.pcc_gather_rows_bf16(_ptr(src), src.shape[1], _ptr(src_row), n, _ptr(out), _stream()))
+    elif src.dtype == torch.float32:
+        check(lib.pcc_gather_rows_f32(_ptr(src), src.shape[1], _ptr(src_row), n, _ptr(out), _stream()))
+    else:
+        raise _lib.PccError(f"gather_rows: unsupported dtype {src.dtype}")
+    return out
+
+
+def gather_keys(src: torch.Tensor, src_row: torch.Tensor) -> torch.Tensor:
+    n = src_row.shape[0]
+    out = torch.empty(n, dtype=torch.int64, device=src.device)
+    check(lib.pcc_gather_keys(_ptr(src), _ptr(src_row), n, _ptr(out), _stream()))
+    return out
+
+
+def topk_select(logits: torch.Tensor, keys: torch.Tensor, frame_off: torch.Tensor, k: torch.Tensor,
+                num_frames: int) -> torch.Tensor:
+    """-> kept rows (ascending).  One host sync for the count."""
+    _need_cuda(logits, torch.float32)
+    n = keys.shape[0]
+    dev = keys.device
+    keep = torch.empty(n, dtype=torch.int32, device=dev)
+    cnt = torch.empty(1, dtype=torch.int32, device=dev)
+    wsb = lib.pcc_topk_workspace_bytes(n)
+    ws = workspace(wsb, dev)
+    check(lib.pcc_topk_select(_ptr(logits), _ptr(keys), n, _ptr(frame_off), _ptr(k), num_frames, _ptr(keep),
+                              _ptr(cnt), _ptr(ws), ws.numel(), _stream()))
+    m = int(cnt.item())
+    return keep[:m]
+
+
+# ------------------------------------------------------------------------------------------------
+# sparse convolution
+# ------------------------------------------------------------------------------------------------
+def pack_weights_umma(w: np.ndarray, cin_pad: int) -> torch.Tensor:
+    """w float32 [kvol, cin, cout] -> packed bf16 panels (uint8 CPU tensor)."""
+    w = np.ascontiguousarray(w, dtype=np.float32)
+    kvol, cin, cout = w.shape
+    nb = lib.pcc_spconv_packed_weight_bytes(kvol, cin_pad, cout)
+    out = np.empty(nb, dtype=np.uint8)
+    check(lib.pcc_spconv_pack_weights(w.ctypes.data, kvol, cin, cout, cin_pad, out.ctypes.data))
+    return torch.from_numpy(out)
+
+
+def spconv_umma(x: torch.Tensor, nbr: Optional[torch.Tensor], n_out: int, kvol: int, w_packed: torch.Tensor,
+                bias: Optional[torch.Tensor], cout: int, residual: Optional[torch.Tensor] = None,
+                relu: bool = False, out_bf16: Optional[torch.Tensor] = None,
+                out_f32: Optional[torch.Tensor] = None, col0: int = 0) -> None:
+    """Writes columns [col0, col0+cout) of the given output tensors."""
+    _need_cuda(x, torch.bfloat16)
+    esz_b = 2
+    ob = None if out_bf16 is None else out_bf16.data_ptr() + col0 * esz_b
+    of = None if out_f32 is None else out_f32.data_ptr() + col0 * 4
+    ldo = (out_bf16 if out_bf16 is not None else out_f32).shape[1]
+    rp, ldr = None, 0
+    if residual is not None:
+        rp = residual.data_ptr() + col0 * esz_b
+        ldr = residual.shape[1]
+    check(lib.pcc_spconv_umma(_ptr(x), x.shape[0], x.shape[1], _ptr(nbr), n_out, kvol, _ptr(w_packed),
+                              _ptr(bias), cout, rp, ldr, int(relu), ob, of, ldo, _stream()))
+
+
+def spconv_simt(x: torch.Tensor, nbr: Optional[torch.Tensor], n_out: int, kvol: int, w_bf16: torch.Tensor,
+                bias: Optional[torch.Tensor], cout: int, residual: Optional[torch.Tensor] = None,
+                relu: bool = False, out_bf16: Optional[torch.Tensor] = None,
+                out_f32: Optional[torch.Tensor] = None) -> None:
+    _need_cuda(x, torch.bfloat16)
+    ldo = (out_bf16 if out_bf16 is not None else out_f32).shape[1]
+    ldr = residual.shape[1] if residual is not None else 0
+    check(lib.pcc_spconv_simt(_ptr(x), x.shape[0], x.shape[1], _ptr(nbr), n_out, kvol, _ptr(w_bf16),
+                              _ptr(bias), cout, _ptr(residual), ldr, int(relu), _ptr(out_bf16), _ptr(out_f32),
+                              ldo, _stream()))
+
+
+# ------------------------------------------------------------------------------------------------
+# entropy model
+# ------------------------------------------------------------------------------------------------
+def factorized_quant(z: torch.Tensor, perm: Optional[torch.Tensor], medians: torch.Tensor, want_f32=False):
+    _need_cuda(z, torch.float32)
+    n, c = z.shape
+    sym = torch.empty((c, n), dtype=torch.int32, device=z.device)
+    zb = torch.empty((n, c), dtype=torch.bfloat16, device=z.device)
+    zf = torch.empty((n, c), dtype=torch.float32, device=z.device) if want_f32 else None
+    check(lib.pcc_factorized_quant(_ptr(z), _ptr(perm), _ptr(medians), n, c, _ptr(sym), _ptr(zb), _ptr(zf),
+                                   _stream()))
+    return sym, zb, zf
+
+
+def factorized_dequant(sym: torch.Tensor, perm: Optional[torch.Tensor], medians: torch.Tensor, want_f32=False):
+    _need_cuda(sym, torch.int32)
+    c, n = sym.shape
+    zb = torch.empty((n, c), dtype=torch.bfloat16, device=sym.device)
+    zf = torch.empty((n, c), dtype=torch.float32, device=sym.device) if want_f32 else None
+    check(lib.pcc_factorized_dequant(_ptr(sym), _ptr(perm), _ptr(medians), n, c, _ptr(zb), _ptr(zf), _stream()))
+    return zb, zf
+
+
+def gauss_encode(y: torch.Tensor, params: torch.Tensor, prow: Optional[torch.Tensor],
+                 perm: Optional[torch.Tensor], scale: torch.Tensor, table: torch.Tensor, bound: float):
+    _need_cuda(y, torch.float32)
+    _need_cuda(params, torch.float32)
+    n, c = y.shape
+    q = scale.shape[0]
+    sym = torch.empty((q, c, n), dtype=torch.int32, device=y.device)
+    idx = torch.empty((q, c, n), dtype=torch.int16, device=y.device)
+    check(lib.pcc_gauss_encode(_ptr(y), _ptr(params), _ptr(prow), _ptr(perm), _ptr(scale), _ptr(table),
+                               table.shape[0], bound, n, c, q, _ptr(sym), _ptr(idx), _stream()))
+    return sym, idx
+
+
+def gauss_indexes(params: torch.Tensor, prow, perm, scale: torch.Tensor, table: torch.Tensor, bound: float,
+                  n: int, c: int):
+    idx = torch.empty((c, n), dtype=torch.int16, device=params.device)
+    check(lib.pcc_gauss_indexes(_ptr(params), _ptr(prow), _ptr(perm), _ptr(scale), _ptr(table), table.shape[0],
+                                bound, n, c, _ptr(idx), _stream()))
+    return idx
+
+
+def gauss_dequant(sym: torch.Tensor, params: torch.Tensor, prow, perm, scale: torch.Tensor,
+                  gain: Optional[torch.Tensor], bound: float, want_f32=False):
+    c, n = sym.shape
+    yb = torch.empty((n, c), dtype=torch.bfloat16, device=sym.device)
+    yf = torch.empty((n, c), dtype=torch.float32, device=sym.device) if want_f32 else None
+    check(lib.pcc_gauss_dequant(_ptr(sym), _ptr(params), _ptr(prow), _ptr(perm), _ptr(scale), _ptr(gain), bound,
+                                n, c, _ptr(yb), _ptr(yf), _stream()))
+    return yb, yf
+
+
+def pmf_to_quantized_cdf(pmf: np.ndarray, precision: int = 16) -> np.ndarray:
+    pmf = np.ascontiguousarray(pmf, dtype=np.float32)
+    out = np.empty(pmf.shape[0] + 1, dtype=np.int32)
+    check(lib.pcc_pmf_to_quantized_cdf(pmf.ctypes.data, pmf.shape[0], precision, out.ctypes.data))
+    return out
+
+
+class DeviceCdfTables:
+    """Quantised CDF tables resident on the device (flat cdf + per-table offset/size/symbol offset)."""
+
+    def __init__(self, cdf_rows, offsets, device):
+        sizes = np.array([len(r) for r in cdf_rows], dtype=np.int32)
+        offs = np.zeros(len(cdf_rows), dtype=np.int32)
+        offs[1:] = np.cumsum(sizes)[:-1]
+        flat = np.concatenate([np.asarray(r, dtype=np.uint32) for r in cdf_rows]).astype(np.uint32)
+        self.num_tables = len(cdf_rows)
+        self.cdf = torch.from_numpy(flat.view(np.int32)).to(device)
+        self.cdf_off = torch.from_numpy(offs).to(device)
+        self.cdf_size = torch.from_numpy(sizes).to(device)
+        self.offset = torch.from_numpy(np.asarray(offsets, dtype=np.int32)).to(device)
+        self.struct = CdfTables(self.cdf.data_ptr(), self.cdf_off.data_ptr(), self.cdf_size.data_ptr(),
+                                self.offset.data_ptr(), self.num_tables)
+
+
+DEFAULT_SEG = 1 << 15
+
+
+def rans_encode(sym: torch.Tensor, idx: Optional[torch.Tensor], chan_len: int, tables: DeviceCdfTables,
+                seg_size: int = DEFAULT_SEG):
+    """sym: flat int32 device tensor.  Returns (device uint8 buffer, device int32 byte count)."""
+    _need_cuda(sym, torch.int32)
+    n = sym.numel()
+    dev = sym.device
+    out = torch.empty(lib.pcc_rans_max_bytes(n, seg_size), dtype=torch.uint8, device=dev)
+    nbytes = torch.empty(1, dtype=torch.int32, device=dev)
+    wsb = lib.pcc_rans_workspace_bytes(n, seg_size)
+    ws = workspace(wsb, dev, "rans")
+    check(lib.pcc_rans_encode(_ptr(sym), _ptr(idx), chan_len, n, seg_size, C.byref(tables.struct), _ptr(out),
+                              _ptr(nbytes), _ptr(ws), ws.numel(), _stream()))
+    return out, nbytes
+
+
+def rans_decode(container: torch.Tensor, seg_size: int, idx: Optional[torch.Tensor], chan_len: int, n: int,
+                tables: DeviceCdfTables) -> torch.Tensor:
+    _need_cuda(container, torch.uint8)
+    dev = container.device
+    sym = torch.empty(n, dtype=torch.int32, device=dev)
+    status = torch.empty(1, dtype=torch.int32, device=dev)
+    check(lib.pcc_rans_decode(_ptr(container), container.numel(), seg_size, _ptr(idx), chan_len, n,
+                              C.byref(tables.struct), _ptr(sym), _ptr(status), _stream()))
+    return sym, status

@@ -1,0 +1,195 @@
+"""SparseTensor-shaped host objects over device-resident Morton-key coordinate maps.
+
+Mirrors the slice of ``ME.SparseTensor`` the reference touches: constructor kwargs
+``coordinates, features, tensor_stride, device``; attributes ``.C .F .tensor_stride .device .dtype``;
+method ``.features_at_coordinates(float coords)``.  Row order is ascending Morton key (ME leaves row
+order implementation defined; the reference canonicalises with shared/utils.py:116-165, mirrored by
+``sort_tensor`` / ``sort_points`` below).
+"""
+from typing import Optional
+
+import torch
+
+from . import ops
+
+
+class CoordMap:
+    """A sorted, duplicate-free coordinate set at one tensor stride plus lazily built companions
+    (hash table, k=3 kernel map, links to the coarser map).  Plays the role of ME's coordinate
+    manager entry; shared by every tensor living on these coordinates."""
+
+    def __init__(self, keys: torch.Tensor, log2_stride: int):
+        self.keys = keys
+        self.n = int(keys.shape[0])
+        self.log2_stride = int(log2_stride)
+        self._table = None
+        self._nbr3 = None
+        self._coords = None
+        self._lex = None
+        self.coarse = None          # CoordMap at 2x stride
+        self.parent_row = None      # int32 [n]: row in `coarse`
+        self._nbr_down = None
+
+    @property
+    def stride(self) -> int:
+        return 1 << self.log2_stride
+
+    @property
+    def device(self):
+        return self.keys.device
+
+    def table(self):
+        if self._table is None:
+            self._table = ops.hash_build(self.keys)
+        return self._table
+
+    def nbr3(self) -> torch.Tensor:
+        """[27, n] kernel map of a k=3 stride-1 convolution on this map."""
+        if self._nbr3 is None:
+            self._nbr3 = ops.kmap_k3(self.keys, self.log2_stride, self.table())
+        return self._nbr3
+
+    def coords(self) -> torch.Tensor:
+        if self._coords is None:
+            self._coords = ops.coords_from_keys(self.keys)
+        return self._coords
+
+    def lex_perm(self) -> torch.Tensor:
+        """perm[r] = row holding canonical (b,x,y,z) rank r."""
+        if self._lex is None:
+            self._lex = ops.lex_order(self.keys)
+        return self._lex
+
+    def downsample(self) -> "CoordMap":
+        """Output coordinates of a stride-2 convolution (c' = floor(c / 2t) * 2t)."""
+        if self.coarse is None:
+            keys, parent = ops.coords_downsample(self.keys, self.log2_stride + 1)
+            self.coarse = CoordMap(keys, self.log2_stride + 1)
+            self.parent_row = parent
+        return self.coarse
+
+    def nbr_down(self) -> torch.Tensor:
+        """[8, n_coarse] kernel map of the k=2 stride-2 convolution onto ``downsample()``."""
+        if self._nbr_down is None:
+            coarse = self.downsample()
+            self._nbr_down = ops.kmap_down2(self.keys, self.parent_row, self.log2_stride, coarse.n)
+        return self._nbr_down
+
+    def children(self) -> "CoordMap":
+        """Generative k=2 s=2 transposed-convolution coordinates: child row 8p + octant."""
+        assert self.log2_stride >= 1
+        keys = ops.coords_children(self.keys, self.log2_stride - 1)
+        return CoordMap(keys, self.log2_stride - 1)
+
+    def subset(self, rows: torch.Tensor) -> "CoordMap":
+        """Pruned map (rows ascending => still sorted)."""
+        return CoordMap(ops.gather_keys(self.keys, rows), self.log2_stride)
+
+    def release_maps(self):
+        self._table = None
+        self._nbr3 = None
+        self._nbr_down = None
+
+
+def _log2(stride) -> int:
+    if isinstance(stride, (list, tuple)):
+        stride = stride[0]
+    stride = int(stride)
+    l = stride.bit_length() - 1
+    if (1 << l) != stride:
+        raise ValueError(f"tensor_stride must be a power of two, got {stride}")
+    return l
+
+
+class SparseTensor:
+    def __init__(self, features=None, coordinates=None, tensor_stride=1, device=None, *, _cmap: CoordMap = None,
+                 _feats: torch.Tensor = None, _channels: Optional[int] = None):
+        if _cmap is not None:
+            self.cmap = _cmap
+            self._feats = _feats
+            self._channels = _channels if _channels is not None else (_feats.shape[1] if _feats is not None else 0)
+            return
+        if device is None:
+            device = coordinates.device if coordinates.is_cuda else torch.device("cuda", torch.cuda.current_device())
+        device = torch.device(device)
+        if device.type != "cuda":
+            raise RuntimeError("b200pcc.SparseTensor lives on a CUDA device (no CPU backend)")
+        coords = coordinates.to(device)
+        if coords.dtype in (torch.float64, torch.float16, torch.bfloat16):
+            coords = coords.float()
+        if coords.dtype in (torch.int64, torch.int16, torch.uint8):
+            coords = coords.int()
+        coords = coords.contiguous()
+        keys = ops.keys_from_coords(coords)
+        ukeys, src = ops.sort_unique(keys, want_src=True)
+        self.cmap = CoordMap(ukeys, _log2(tensor_stride))
+        feats = features.to(device=device, dtype=torch.float32).contiguous()
+        self._channels = feats.shape[1]
+        self._feats = ops.gather_rows(feats, src)
+
+    # ---- reference-visible surface -------------------------------------------------------------------
+    @property
+    def C(self) -> torch.Tensor:
+        return self.cmap.coords()
+
+    @property
+    def F(self) -> torch.Tensor:
+        f = self._feats
+        if f.dtype == torch.bfloat16:
+            return ops.rows_bf16_to_f32(f, self._channels)
+        return f[:, : self._channels] if f.shape[1] != self._channels else f
+
+    @property
+    def tensor_stride(self):
+        s = self.cmap.stride
+        return [s, s, s]
+
+    @property
+    def device(self):
+        return self.cmap.device
+
+    @property
+    def dtype(self):
+        return torch.float32
+
+    @property
+    def shape(self):
+        return (self.cmap.n, self._channels)
+
+    def features_at_coordinates(self, query_coordinates: torch.Tensor) -> torch.Tensor:
+        """Rows at (on-grid) float query coordinates, zeros where absent (ME interpolation at grid
+        nodes; codec_pipeline.py:401, codec_parallel.py:387)."""
+        q = query_coordinates.to(self.device)
+        if q.dtype != torch.float32 and q.dtype != torch.int32:
+            q = q.float()
+        rows = ops.hash_query(ops.keys_from_coords(q.contiguous()), self.cmap.table())
+        f = self._feats if self._feats.dtype == torch.float32 else self.F
+        return ops.gather_rows(f.contiguous(), rows)
+
+    # ---- internal -----------------------------------------------------------------------------------
+    def feats_bf16(self, c_pad: int) -> torch.Tensor:
+        f = self._feats
+        if f.dtype == torch.bfloat16 and f.shape[1] == c_pad:
+            return f
+        if f.dtype == torch.bfloat16:
+            f = ops.rows_bf16_to_f32(f, self._channels)
+        return ops.rows_f32_to_bf16(f.contiguous(), c_pad)
+
+
+def sort_points(points: torch.Tensor) -> torch.Tensor:
+    """shared/utils.py:145-165: rows of an [N,4] (b,x,y,z) tensor in canonical order."""
+    keys = ops.keys_from_coords(points.contiguous() if points.dtype in (torch.int32, torch.float32)
+                                else points.int().contiguous())
+    skeys, src = ops.sort_unique(keys, want_src=True)
+    cm = CoordMap(skeys, 0)
+    perm = cm.lex_perm().long()
+    return points[src.long()[perm]]
+
+
+def sort_tensor(t: SparseTensor) -> SparseTensor:
+    """shared/utils.py:116-141: same coordinates/features with rows in canonical order, as plain
+    tensors wrapped in a SparseTensor view whose .C/.F are canonically ordered."""
+    perm = t.cmap.lex_perm().long()
+    out = SparseTensor(_cmap=t.cmap, _feats=t._feats, _channels=t._channels)
+    out._sorted_view = (t.C[perm], t.F[perm])
+    return out

@@ -1,0 +1,89 @@
+// Shared device/host helpers for the pcc_b200 kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <atomic>
+#include <cstdio>
+#include <cstdarg>
+
+#include "../../include/pcc_b200.h"
+
+namespace pcc {
+
+void set_error(const char* fmt, ...);
+extern std::atomic<int64_t> g_launches;
+
+#define PCC_CHECK_ARG(cond)                                                       \
+  do {                                                                            \
+    if (!(cond)) {                                                                \
+      pcc::set_error("%s:%d: invalid argument: %s", __FILE__, __LINE__, #cond);  \
+      return PCC_E_INVALID;                                                       \
+    }                                                                             \
+  } while (0)
+
+#define PCC_CUDA(expr)                                                                 \
+  do {                                                                                 \
+    cudaError_t _e = (expr);                                                           \
+    if (_e != cudaSuccess) {                                                           \
+      pcc::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+      return PCC_E_CUDA;                                                               \
+    }                                                                                  \
+  } while (0)
+
+// Call right after a <<<>>> launch.
+#define PCC_LAUNCHED()                  \
+  do {                                  \
+    pcc::g_launches.fetch_add(1);       \
+    PCC_CUDA(cudaGetLastError());       \
+  } while (0)
+
+static inline cudaStream_t as_stream(pcc_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
+
+static inline int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
+
+// ---------------------------------------------------------------------------------------------
+// Morton keys.  key = b << 48 | spread3(x+32768) | spread3(y+32768) << 1 | spread3(z+32768) << 2
+// ---------------------------------------------------------------------------------------------
+__host__ __device__ __forceinline__ uint64_t spread3_16(uint32_t v) {
+  uint64_t x = v & 0xffffu;
+  x = (x | (x << 16)) & 0x001f0000ff0000ffull;
+  x = (x | (x << 8)) & 0x100f00f00f00f00full;
+  x = (x | (x << 4)) & 0x10c30c30c30c30c3ull;
+  x = (x | (x << 2)) & 0x1249249249249249ull;
+  return x;
+}
+__host__ __device__ __forceinline__ uint32_t compact3_16(uint64_t x) {
+  x &= 0x1249249249249249ull;
+  x = (x | (x >> 2)) & 0x10c30c30c30c30c3ull;
+  x = (x | (x >> 4)) & 0x100f00f00f00f00full;
+  x = (x | (x >> 8)) & 0x001f0000ff0000ffull;
+  x = (x | (x >> 16)) & 0x001f00000000ffffull;
+  return (uint32_t)(x & 0xffffu);
+}
+__host__ __device__ __forceinline__ uint64_t pack_key(int b, int x, int y, int z) {
+  uint64_t m = spread3_16((uint32_t)(x + 32768)) | (spread3_16((uint32_t)(y + 32768)) << 1) |
+               (spread3_16((uint32_t)(z + 32768)) << 2);
+  return ((uint64_t)(uint32_t)(b & 0xffff) << 48) | m;
+}
+__host__ __device__ __forceinline__ void unpack_key(uint64_t key, int& b, int& x, int& y, int& z) {
+  b = (int)(key >> 48);
+  uint64_t m = key & 0x0000FFFFFFFFFFFFull;
+  x = (int)compact3_16(m) - 32768;
+  y = (int)compact3_16(m >> 1) - 32768;
+  z = (int)compact3_16(m >> 2) - 32768;
+}
+
+constexpr uint64_t kEmptyKey = 0xFFFFFFFFFFFFFFFFull;
+
+__host__ __device__ __forceinline__ uint64_t hash_key(uint64_t k) {
+  // murmur3 finaliser
+  k ^= k >> 33;
+  k *= 0xff51afd7ed558ccdull;
+  k ^= k >> 33;
+  k *= 0xc4ceb9fe1a85ec53ull;
+  k ^= k >> 33;
+  return k;
+}
+
+}  // namespace pcc

@@ -1,0 +1,418 @@
+// (1) coordinate kernels: Morton keys, sort/dedup, stride-2 coarsening, generative children,
+// frame offsets, canonical lexicographic order, row gathers.  All HBM-bound, one pass each.
+#include "common.cuh"
+#include <cub/cub.cuh>
+
+namespace pcc {
+
+thread_local char g_err[512] = "";
+std::atomic<int64_t> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+constexpr int kThreads = 256;
+static inline unsigned blocks_for(int64_t n, int per_block = kThreads) {
+  return (unsigned)((n + per_block - 1) / per_block);
+}
+
+__global__ void k_keys_from_i32(const int4* __restrict__ c, int64_t n, uint64_t* __restrict__ keys) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int4 v = c[i];
+  keys[i] = pack_key(v.x, v.y, v.z, v.w);
+}
+__global__ void k_keys_from_f32(const float4* __restrict__ c, int64_t n, uint64_t* __restrict__ keys) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float4 v = c[i];
+  keys[i] = pack_key((int)floorf(v.x), (int)floorf(v.y), (int)floorf(v.z), (int)floorf(v.w));
+}
+__global__ void k_ingest(const int16_t* __restrict__ p, const double* __restrict__ col, int64_t n,
+                         int batch, uint64_t* __restrict__ keys, float4* __restrict__ feats) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int x = p[3 * i], y = p[3 * i + 1], z = p[3 * i + 2];
+  keys[i] = pack_key(batch, x, y, z);
+  feats[i] = make_float4(1.0f, (float)col[3 * i], (float)col[3 * i + 1], (float)col[3 * i + 2]);
+}
+__global__ void k_coords_from_keys(const uint64_t* __restrict__ keys, int64_t n, int4* __restrict__ c) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int b, x, y, z;
+  unpack_key(keys[i], b, x, y, z);
+  c[i] = make_int4(b, x, y, z);
+}
+
+__global__ void k_iota(int32_t* v, int64_t n) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) v[i] = (int32_t)i;
+}
+
+// flags[i] = 1 where sorted key i starts a new run (after masking low bits)
+__global__ void k_run_flags(const uint64_t* __restrict__ keys, int64_t n, uint64_t mask,
+                            int32_t* __restrict__ flags) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint64_t k = keys[i] & mask;
+  flags[i] = (i == 0 || (keys[i - 1] & mask) != k) ? 1 : 0;
+}
+// incl = inclusive scan of flags. Writes unique keys, the first source row of each run and the
+// run id of every input row.
+__global__ void k_scatter_runs(const uint64_t* __restrict__ keys, const int32_t* __restrict__ src,
+                               const int32_t* __restrict__ incl, int64_t n, uint64_t mask,
+                               uint64_t* __restrict__ keys_out, int32_t* __restrict__ src_out,
+                               int32_t* __restrict__ run_of, int32_t* __restrict__ n_out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int32_t r = incl[i] - 1;
+  bool first = (i == 0) || (incl[i - 1] != incl[i]);
+  if (first) {
+    keys_out[r] = keys[i] & mask;
+    if (src_out) src_out[r] = src ? src[i] : (int32_t)i;
+  }
+  if (run_of) run_of[i] = r;
+  if (i == n - 1) *n_out = incl[i];
+}
+
+__global__ void k_children(const uint64_t* __restrict__ keys, int64_t n, int shift,
+                           uint64_t* __restrict__ out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;  // over 8n
+  if (i >= 8 * n) return;
+  out[i] = keys[i >> 3] | ((uint64_t)(i & 7) << shift);
+}
+
+__global__ void k_frame_offsets(const uint64_t* __restrict__ keys, int64_t n, int nf,
+                                int32_t* __restrict__ off) {
+  int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b > nf) return;
+  uint64_t target = (uint64_t)b << 48;
+  int64_t lo = 0, hi = n;
+  while (lo < hi) {
+    int64_t mid = (lo + hi) >> 1;
+    if (keys[mid] < target) lo = mid + 1; else hi = mid;
+  }
+  off[b] = (int32_t)lo;
+}
+
+__global__ void k_lex_keys(const uint64_t* __restrict__ keys, int64_t n, uint64_t* __restrict__ lex,
+                           int32_t* __restrict__ row) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int b, x, y, z;
+  unpack_key(keys[i], b, x, y, z);
+  lex[i] = ((uint64_t)b << 48) | ((uint64_t)(x + 32768) << 32) | ((uint64_t)(y + 32768) << 16) |
+           (uint64_t)(z + 32768);
+  row[i] = (int32_t)i;
+}
+
+// ---- row gathers -----------------------------------------------------------------------------
+__global__ void k_rows_f32_to_bf16(const float* __restrict__ src, int c_src,
+                                   const int32_t* __restrict__ src_row, int64_t n_out,
+                                   __nv_bfloat16* __restrict__ dst, int c_dst) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n_out * c_dst) return;
+  int64_t r = i / c_dst;
+  int c = (int)(i - r * c_dst);
+  int64_t sr = src_row ? src_row[r] : r;
+  float v = (c < c_src && sr >= 0) ? src[sr * c_src + c] : 0.0f;
+  dst[i] = __float2bfloat16_rn(v);
+}
+__global__ void k_rows_bf16_to_f32(const __nv_bfloat16* __restrict__ src, int c_src, int64_t n,
+                                   float* __restrict__ dst, int c_dst) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n * c_dst) return;
+  int64_t r = i / c_dst;
+  int c = (int)(i - r * c_dst);
+  dst[i] = __bfloat162float(src[r * c_src + c]);
+}
+// 16-byte chunks per row; c*2 bytes must be a multiple of 16.
+__global__ void k_gather_rows16(const uint4* __restrict__ src, int chunks,
+                                const int32_t* __restrict__ src_row, int64_t n_out,
+                                uint4* __restrict__ dst) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n_out * chunks) return;
+  int64_t r = i / chunks;
+  int c = (int)(i - r * chunks);
+  int64_t sr = src_row[r];
+  dst[i] = sr >= 0 ? src[sr * chunks + c] : make_uint4(0, 0, 0, 0);
+}
+__global__ void k_gather_rows_f32(const float* __restrict__ src, int c,
+                                  const int32_t* __restrict__ src_row, int64_t n_out,
+                                  float* __restrict__ dst) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n_out * c) return;
+  int64_t r = i / c;
+  int cc = (int)(i - r * c);
+  int64_t sr = src_row[r];
+  dst[i] = sr >= 0 ? src[sr * c + cc] : 0.0f;
+}
+__global__ void k_gather_keys(const uint64_t* __restrict__ src, const int32_t* __restrict__ src_row,
+                              int64_t n_out, uint64_t* __restrict__ dst) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n_out) dst[i] = src[src_row[i]];
+}
+
+struct WsCarver {
+  char* p;
+  int64_t left;
+  WsCarver(void* ws, int64_t bytes) : p((char*)ws), left(bytes) {}
+  void* take(int64_t bytes) {
+    bytes = align_up(bytes, 256);
+    if (bytes > left) return nullptr;
+    void* r = p;
+    p += bytes;
+    left -= bytes;
+    return r;
+  }
+};
+
+}  // namespace pcc
+
+using namespace pcc;
+
+extern "C" {
+
+int pcc_version(void) { return 100; }
+const char* pcc_last_error(void) { return pcc::g_err; }
+int64_t pcc_launch_count(void) { return pcc::g_launches.load(); }
+
+int pcc_keys_from_coords_i32(const int32_t* coords, int64_t n, uint64_t* keys, pcc_stream_t s) {
+  PCC_CHECK_ARG(n >= 0);
+  if (n == 0) return PCC_OK;
+  PCC_CHECK_ARG(coords && keys);
+  k_keys_from_i32<<<blocks_for(n), kThreads, 0, as_stream(s)>>>((const int4*)coords, n, keys);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+int pcc_keys_from_coords_f32(const float* coords, int64_t n, uint64_t* keys, pcc_stream_t s) {
+  PCC_CHECK_ARG(n >= 0);
+  if (n == 0) return PCC_OK;
+  PCC_CHECK_ARG(coords && keys);
+  k_keys_from_f32<<<blocks_for(n), kThreads, 0, as_stream(s)>>>((const float4*)coords, n, keys);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+int pcc_ingest_frame(const int16_t* points, const double* colors, int64_t n, int32_t batch,
+                     uint64_t* keys, float* feats4, pcc_stream_t s) {
+  PCC_CHECK_ARG(n >= 0 && batch >= 0 && batch < 65535);
+  if (n == 0) return PCC_OK;
+  PCC_CHECK_ARG(points && colors && keys && feats4);
+  k_ingest<<<blocks_for(n), kThreads, 0, as_stream(s)>>>(points, colors, n, batch, keys,
+                                                         (float4*)feats4);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+int pcc_coords_from_keys(const uint64_t* keys, int64_t n, int32_t* coords, pcc_stream_t s) {
+  PCC_CHECK_ARG(n >= 0);
+  if (n == 0) return PCC_OK;
+  PCC_CHECK_ARG(coords && keys);
+  k_coords_from_keys<<<blocks_for(n), kThreads, 0, as_stream(s)>>>(keys, n, (int4*)coords);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+
+// ---- sort + unique ---------------------------------------------------------------------------
+static size_t cub_sort_pairs_bytes(int64_t n) {
+  size_t b = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, b, (const uint64_t*)nullptr, (uint64_t*)nullptr,
+                                  (const int32_t*)nullptr, (int32_t*)nullptr, (int)n);
+  return b;
+}
+static size_t cub_scan_bytes(int64_t n) {
+  size_t b = 0;
+  cub::DeviceScan::InclusiveSum(nullptr, b, (const int32_t*)nullptr, (int32_t*)nullptr, (int)n);
+  return b;
+}
+
+int64_t pcc_sort_unique_workspace_bytes(int64_t n) {
+  if (n <= 0) return 256;
+  int64_t b = 0;
+  b += align_up(n * 8, 256);  // sorted keys
+  b += align_up(n * 4, 256);  // iota
+  b += align_up(n * 4, 256);  // sorted rows
+  b += align_up(n * 4, 256);  // flags / scan
+  b += align_up((int64_t)cub_sort_pairs_bytes(n), 256);
+  b += align_up((int64_t)cub_scan_bytes(n), 256);
+  return b + 256;
+}
+
+int pcc_sort_unique(const uint64_t* keys_in, int64_t n, uint64_t* keys_out, int32_t* src_row,
+                    int32_t* n_out_dev, void* ws, int64_t ws_bytes, pcc_stream_t s) {
+  PCC_CHECK_ARG(n >= 0 && n < (1ll << 31) && n_out_dev);
+  cudaStream_t st = as_stream(s);
+  if (n == 0) {
+    PCC_CUDA(cudaMemsetAsync(n_out_dev, 0, 4, st));
+    return PCC_OK;
+  }
+  PCC_CHECK_ARG(keys_in && keys_out && ws);
+  WsCarver w(ws, ws_bytes);
+  uint64_t* skeys = (uint64_t*)w.take(n * 8);
+  int32_t* iota = (int32_t*)w.take(n * 4);
+  int32_t* srows = (int32_t*)w.take(n * 4);
+  int32_t* flags = (int32_t*)w.take(n * 4);
+  size_t sort_b = cub_sort_pairs_bytes(n), scan_b = cub_scan_bytes(n);
+  void* sort_ws = w.take((int64_t)sort_b);
+  void* scan_ws = w.take((int64_t)scan_b);
+  if (!skeys || !iota || !srows || !flags || !sort_ws || !scan_ws) {
+    set_error("pcc_sort_unique: workspace too small (%lld)", (long long)ws_bytes);
+    return PCC_E_WORKSPACE;
+  }
+  k_iota<<<blocks_for(n), kThreads, 0, st>>>(iota, n);
+  PCC_LAUNCHED();
+  // radix sort is stable: among equal keys the lowest input row comes first ("first wins")
+  PCC_CUDA(cub::DeviceRadixSort::SortPairs(sort_ws, sort_b, keys_in, skeys, iota, srows, (int)n, 0,
+                                           64, st));
+  g_launches.fetch_add(1);
+  k_run_flags<<<blocks_for(n), kThreads, 0, st>>>(skeys, n, ~0ull, flags);
+  PCC_LAUNCHED();
+  PCC_CUDA(cub::DeviceScan::InclusiveSum(scan_ws, scan_b, flags, flags, (int)n, st));
+  g_launches.fetch_add(1);
+  k_scatter_runs<<<blocks_for(n), kThreads, 0, st>>>(skeys, srows, flags, n, ~0ull, keys_out,
+                                                     src_row, nullptr, n_out_dev);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+
+// ---- stride-2 coarsening: sorted Morton keys stay sorted after masking low bits ----------------
+int64_t pcc_coords_downsample_workspace_bytes(int64_t n) {
+  if (n <= 0) return 256;
+  return align_up(n * 4, 256) + align_up((int64_t)cub_scan_bytes(n), 256) + 256;
+}
+
+int pcc_coords_downsample(const uint64_t* keys_in, int64_t n, int log2_stride, uint64_t* keys_out,
+                          int32_t* parent_row, int32_t* n_out_dev, void* ws, int64_t ws_bytes,
+                          pcc_stream_t s) {
+  PCC_CHECK_ARG(n >= 0 && n < (1ll << 31) && n_out_dev && log2_stride >= 1 && log2_stride <= 15);
+  cudaStream_t st = as_stream(s);
+  if (n == 0) {
+    PCC_CUDA(cudaMemsetAsync(n_out_dev, 0, 4, st));
+    return PCC_OK;
+  }
+  PCC_CHECK_ARG(keys_in && keys_out && ws);
+  WsCarver w(ws, ws_bytes);
+  int32_t* flags = (int32_t*)w.take(n * 4);
+  size_t scan_b = cub_scan_bytes(n);
+  void* scan_ws = w.take((int64_t)scan_b);
+  if (!flags || !scan_ws) {
+    set_error("pcc_coords_downsample: workspace too small");
+    return PCC_E_WORKSPACE;
+  }
+  uint64_t mask = ~((1ull << (3 * log2_stride)) - 1ull);
+  k_run_flags<<<blocks_for(n), kThreads, 0, st>>>(keys_in, n, mask, flags);
+  PCC_LAUNCHED();
+  PCC_CUDA(cub::DeviceScan::InclusiveSum(scan_ws, scan_b, flags, flags, (int)n, st));
+  g_launches.fetch_add(1);
+  k_scatter_runs<<<blocks_for(n), kThreads, 0, st>>>(keys_in, nullptr, flags, n, mask, keys_out,
+                                                     nullptr, parent_row, n_out_dev);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+
+int pcc_coords_children(const uint64_t* keys_in, int64_t n, int log2_stride, uint64_t* keys_out,
+                        pcc_stream_t s) {
+  PCC_CHECK_ARG(n >= 0 && 8 * n < (1ll << 31) && log2_stride >= 0 && log2_stride <= 14);
+  if (n == 0) return PCC_OK;
+  PCC_CHECK_ARG(keys_in && keys_out);
+  k_children<<<blocks_for(8 * n), kThreads, 0, as_stream(s)>>>(keys_in, n, 3 * log2_stride,
+                                                               keys_out);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+
+int pcc_frame_offsets(const uint64_t* keys, int64_t n, int32_t num_frames, int32_t* offsets,
+                      pcc_stream_t s) {
+  PCC_CHECK_ARG(n >= 0 && num_frames >= 0 && num_frames < 65535 && offsets);
+  PCC_CHECK_ARG(n == 0 || keys);
+  k_frame_offsets<<<blocks_for(num_frames + 1, 64), 64, 0, as_stream(s)>>>(keys, n, num_frames,
+                                                                           offsets);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+
+int64_t pcc_lex_order_workspace_bytes(int64_t n) {
+  if (n <= 0) return 256;
+  return 2 * align_up(n * 8, 256) + align_up(n * 4, 256) +
+         align_up((int64_t)cub_sort_pairs_bytes(n), 256) + 256;
+}
+int pcc_lex_order(const uint64_t* keys, int64_t n, int32_t* perm, void* ws, int64_t ws_bytes,
+                  pcc_stream_t s) {
+  PCC_CHECK_ARG(n >= 0 && n < (1ll << 31));
+  if (n == 0) return PCC_OK;
+  PCC_CHECK_ARG(keys && perm && ws);
+  cudaStream_t st = as_stream(s);
+  WsCarver w(ws, ws_bytes);
+  uint64_t* lex = (uint64_t*)w.take(n * 8);
+  uint64_t* lex_sorted = (uint64_t*)w.take(n * 8);
+  int32_t* row = (int32_t*)w.take(n * 4);
+  size_t sort_b = cub_sort_pairs_bytes(n);
+  void* sort_ws = w.take((int64_t)sort_b);
+  if (!lex || !lex_sorted || !row || !sort_ws) {
+    set_error("pcc_lex_order: workspace too small");
+    return PCC_E_WORKSPACE;
+  }
+  k_lex_keys<<<blocks_for(n), kThreads, 0, st>>>(keys, n, lex, row);
+  PCC_LAUNCHED();
+  PCC_CUDA(cub::DeviceRadixSort::SortPairs(sort_ws, sort_b, lex, lex_sorted, row, perm, (int)n, 0,
+                                           64, st));
+  g_launches.fetch_add(1);
+  return PCC_OK;
+}
+
+// ---- row utilities ---------------------------------------------------------------------------
+int pcc_rows_f32_to_bf16(const float* src, int c_src, const int32_t* src_row, int64_t n_out,
+                         void* dst_bf16, int c_dst, pcc_stream_t s) {
+  PCC_CHECK_ARG(n_out >= 0 && c_src > 0 && c_dst > 0);
+  if (n_out == 0) return PCC_OK;
+  PCC_CHECK_ARG(src && dst_bf16);
+  k_rows_f32_to_bf16<<<blocks_for(n_out * c_dst), kThreads, 0, as_stream(s)>>>(
+      src, c_src, src_row, n_out, (__nv_bfloat16*)dst_bf16, c_dst);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+int pcc_rows_bf16_to_f32(const void* src_bf16, int c_src, int64_t n, float* dst, int c_dst,
+                         pcc_stream_t s) {
+  PCC_CHECK_ARG(n >= 0 && c_src > 0 && c_dst > 0 && c_dst <= c_src);
+  if (n == 0) return PCC_OK;
+  PCC_CHECK_ARG(src_bf16 && dst);
+  k_rows_bf16_to_f32<<<blocks_for(n * c_dst), kThreads, 0, as_stream(s)>>>(
+      (const __nv_bfloat16*)src_bf16, c_src, n, dst, c_dst);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+int pcc_gather_rows_bf16(const void* src_bf16, int c, const int32_t* src_row, int64_t n_out,
+                         void* dst_bf16, pcc_stream_t s) {
+  PCC_CHECK_ARG(n_out >= 0 && c > 0 && c % 8 == 0);
+  if (n_out == 0) return PCC_OK;
+  PCC_CHECK_ARG(src_bf16 && dst_bf16 && src_row);
+  int chunks = c / 8;
+  k_gather_rows16<<<blocks_for(n_out * chunks), kThreads, 0, as_stream(s)>>>(
+      (const uint4*)src_bf16, chunks, src_row, n_out, (uint4*)dst_bf16);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+int pcc_gather_rows_f32(const float* src, int c, const int32_t* src_row, int64_t n_out, float* dst,
+                        pcc_stream_t s) {
+  PCC_CHECK_ARG(n_out >= 0 && c > 0);
+  if (n_out == 0) return PCC_OK;
+  PCC_CHECK_ARG(src && dst && src_row);
+  k_gather_rows_f32<<<blocks_for(n_out * c), kThreads, 0, as_stream(s)>>>(src, c, src_row, n_out,
+                                                                          dst);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+int pcc_gather_keys(const uint64_t* src, const int32_t* src_row, int64_t n_out, uint64_t* dst,
+                    pcc_stream_t s) {
+  PCC_CHECK_ARG(n_out >= 0);
+  if (n_out == 0) return PCC_OK;
+  PCC_CHECK_ARG(src && dst && src_row);
+  k_gather_keys<<<blocks_for(n_out), kThreads, 0, as_stream(s)>>>(src, src_row, n_out, dst);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,325 @@
+// (4) Interleaved multi-lane rANS ("PCL1" container).
+//
+// The symbol array is cut into segments of seg_size symbols; one warp codes one segment as 32
+// interleaved lanes (symbol i of the segment -> lane i % 32, round i / 32).  Each lane keeps a 32-bit
+// rANS state (L = 2^16, 16-bit probabilities, 16-bit renormalisation words).  Renormalisation words of
+// all lanes of a warp go to ONE shared word stream: in every coding step the lanes that must emit are
+// found with a ballot and placed with a popc prefix, so the decoder (which runs the steps in the
+// opposite order and reads the stream backwards) can recompute every position without side
+// information.  Symbol semantics are CompressAI's encode_with_indexes: values outside the table's
+// support take the table's last entry as an escape and the residual follows as a count nibble plus up
+// to 8 four-bit nibbles coded with a flat 2^12/2^16 model.
+//
+// Container:  "PCL1" | u32 n | u32 seg_size | u32 nseg | u32 seg_bytes[nseg] | segments...
+// Segment:    u32 nwords | u32 state[32] | u16 words[nwords] | pad to 4 bytes
+#include "common.cuh"
+
+namespace pcc {
+
+constexpr uint32_t kRansL = 1u << 16;
+constexpr uint32_t kMagic = 0x314c4350u;  // "PCL1" little endian
+
+struct Tables {
+  const uint32_t* cdf;
+  const int32_t* off;
+  const int32_t* size;
+  const int32_t* offset;
+  int32_t T;
+};
+
+__host__ __device__ inline int64_t seg_cap_words(int32_t seg_size) { return 4ll * seg_size + 64; }
+
+struct SymOps {
+  int32_t coff;   // start of the cdf row
+  int32_t v;      // table symbol (maxv = escape)
+  uint32_t raw;   // escape payload
+  int nnib;       // nibbles in raw
+  int nops;       // 1 or 2 + nnib
+};
+
+__device__ __forceinline__ SymOps make_ops(int32_t symbol, int32_t t, const Tables& T) {
+  SymOps o;
+  o.coff = T.off[t];
+  int32_t maxv = T.size[t] - 2;
+  int64_t v = (int64_t)symbol - (int64_t)T.offset[t];
+  o.raw = 0;
+  if (v < 0) {
+    o.raw = (uint32_t)(-2 * v - 1);
+    v = maxv;
+  } else if (v >= maxv) {
+    o.raw = (uint32_t)(2 * (v - maxv));
+    v = maxv;
+  }
+  o.v = (int32_t)v;
+  o.nnib = 0;
+  o.nops = 1;
+  if (v == maxv) {
+    o.nnib = o.raw ? (35 - __clz(o.raw)) / 4 : 0;  // ceil(bits/4)
+    o.nops = 2 + o.nnib;
+  }
+  return o;
+}
+
+__global__ void __launch_bounds__(32)
+k_rans_encode(const int32_t* __restrict__ sym, const uint16_t* __restrict__ idx, int64_t chan_len, int64_t n,
+              int32_t seg_size, Tables T, uint16_t* __restrict__ scratch, uint32_t* __restrict__ states,
+              int32_t* __restrict__ nwords) {
+  const int seg = blockIdx.x, lane = threadIdx.x;
+  const unsigned lt = (1u << lane) - 1u;
+  const int64_t start = (int64_t)seg * seg_size;
+  const int32_t cnt = (int32_t)((n - start) < seg_size ? (n - start) : seg_size);
+  const int32_t rounds = (cnt + 31) / 32;
+  uint16_t* out = scratch + (int64_t)seg * seg_cap_words(seg_size);
+  uint32_t x = kRansL;
+  int32_t wpos = 0;
+  for (int32_t r = rounds - 1; r >= 0; --r) {
+    const int32_t li = r * 32 + lane;
+    const bool active = li < cnt;
+    SymOps o;
+    o.nops = 0; o.coff = 0; o.v = 0; o.raw = 0; o.nnib = 0;
+    if (active) {
+      const int64_t i = start + li;
+      int32_t t = idx ? (int32_t)idx[i] : (int32_t)(i / chan_len);
+      t = t < T.T ? t : T.T - 1;
+      o = make_ops(sym[i], t, T);
+    }
+    const int maxops = __reduce_max_sync(0xffffffffu, o.nops);
+    for (int ts = maxops - 1; ts >= 0; --ts) {
+      const bool has = ts < o.nops;
+      uint32_t st = 0, fr = 1;
+      if (has) {
+        if (ts == 0) {
+          st = T.cdf[o.coff + o.v];
+          fr = T.cdf[o.coff + o.v + 1] - st;
+        } else {
+          uint32_t val = ts == 1 ? (uint32_t)o.nnib : ((o.raw >> (4 * (ts - 2))) & 15u);
+          st = val << 12;
+          fr = 1u << 12;
+        }
+      }
+      const bool emit = has && ((uint64_t)x >= ((uint64_t)fr << 16));
+      const unsigned m = __ballot_sync(0xffffffffu, emit);
+      if (emit) {
+        out[wpos + __popc(m & lt)] = (uint16_t)(x & 0xffffu);
+        x >>= 16;
+      }
+      wpos += __popc(m);
+      if (has) x = ((x / fr) << 16) + (x % fr) + st;
+    }
+  }
+  states[seg * 32 + lane] = x;
+  if (lane == 0) nwords[seg] = wpos;
+}
+
+__device__ __forceinline__ uint32_t seg_bytes_of(int32_t nw) { return 4u + 128u + ((2u * (uint32_t)nw + 3u) & ~3u); }
+
+__global__ void __launch_bounds__(256)
+k_rans_pack(const uint16_t* __restrict__ scratch, const uint32_t* __restrict__ states,
+            const int32_t* __restrict__ nwords, int32_t nseg, int32_t seg_size, uint32_t n,
+            uint8_t* __restrict__ out, int32_t* __restrict__ out_bytes) {
+  __shared__ uint32_t s_off;
+  __shared__ uint32_t red[256];
+  const int seg = blockIdx.x, tid = threadIdx.x;
+  uint32_t acc = 0;
+  for (int i = tid; i < seg; i += 256) acc += seg_bytes_of(nwords[i]);
+  red[tid] = acc;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (tid < s) red[tid] += red[tid + s];
+    __syncthreads();
+  }
+  if (tid == 0) s_off = red[0];
+  __syncthreads();
+  const uint32_t hdr = 16u + 4u * (uint32_t)nseg;
+  uint32_t* o32 = reinterpret_cast<uint32_t*>(out);
+  const int32_t nw = nwords[seg];
+  const uint32_t sb = seg_bytes_of(nw);
+  if (tid == 0) o32[4 + seg] = sb;
+  if (seg == 0 && tid == 0) {
+    o32[0] = kMagic;
+    o32[1] = n;
+    o32[2] = (uint32_t)seg_size;
+    o32[3] = (uint32_t)nseg;
+  }
+  if (seg == nseg - 1 && tid == 0) *out_bytes = (int32_t)(hdr + s_off + sb);
+  uint8_t* dst = out + hdr + s_off;
+  uint32_t* d32 = reinterpret_cast<uint32_t*>(dst);
+  if (tid == 0) d32[0] = (uint32_t)nw;
+  if (tid < 32) d32[1 + tid] = states[seg * 32 + tid];
+  uint16_t* dw = reinterpret_cast<uint16_t*>(dst + 132);
+  const uint16_t* src = scratch + (int64_t)seg * seg_cap_words(seg_size);
+  for (int i = tid; i < nw; i += 256) dw[i] = src[i];
+  if (tid == 0 && (nw & 1)) dw[nw] = 0;
+}
+
+__global__ void __launch_bounds__(32)
+k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, int32_t seg_size_arg,
+              const uint16_t* __restrict__ idx, int64_t chan_len, int64_t n, Tables T,
+              int32_t* __restrict__ sym, int32_t* __restrict__ status) {
+  const int seg = blockIdx.x, lane = threadIdx.x;
+  const unsigned lt = (1u << lane) - 1u;
+  const uint32_t* h32 = reinterpret_cast<const uint32_t*>(container);
+  const uint32_t seg_size = h32[2], nseg = h32[3];
+  if (h32[0] != kMagic || h32[1] != (uint32_t)n || seg_size != (uint32_t)seg_size_arg || nseg != gridDim.x) {
+    if (lane == 0) atomicExch(status, 3);
+    return;
+  }
+  uint32_t acc = 0;
+  for (int i = lane; i < seg; i += 32) acc += h32[4 + i];
+  acc = __reduce_add_sync(0xffffffffu, acc);
+  const uint64_t seg_off = 16ull + 4ull * nseg + acc;
+  if (seg_off + 132 > (uint64_t)container_bytes) {
+    if (lane == 0) atomicExch(status, 1);
+    return;
+  }
+  const uint32_t* s32 = reinterpret_cast<const uint32_t*>(container + seg_off);
+  int32_t wpos = (int32_t)s32[0];
+  if (seg_off + 132 + 2ull * (uint32_t)wpos > (uint64_t)container_bytes) {
+    if (lane == 0) atomicExch(status, 1);
+    return;
+  }
+  uint32_t x = s32[1 + lane];
+  const uint16_t* words = reinterpret_cast<const uint16_t*>(container + seg_off + 132);
+  const int64_t start = (int64_t)seg * seg_size;
+  const int32_t cnt = (int32_t)((n - start) < (int64_t)seg_size ? (n - start) : (int64_t)seg_size);
+  const int32_t rounds = (cnt + 31) / 32;
+  bool bad = false;
+  for (int32_t r = 0; r < rounds; ++r) {
+    const int32_t li = r * 32 + lane;
+    const bool active = li < cnt;
+    const int64_t i = start + li;
+    int32_t coff = 0, maxv = 0, offs = 0;
+    if (active) {
+      int32_t t = idx ? (int32_t)idx[i] : (int32_t)(i / chan_len);
+      t = t < T.T ? t : T.T - 1;
+      coff = T.off[t];
+      maxv = T.size[t] - 2;
+      offs = T.offset[t];
+    }
+    // step 0: table symbol
+    int32_t v = 0;
+    {
+      uint32_t cf = x & 0xffffu;
+      if (active) {
+        int32_t lo = 0, hi = maxv + 1;  // cdf[coff + maxv + 1] == 65536 > cf
+        while (hi - lo > 1) {
+          int32_t mid = (lo + hi) >> 1;
+          if (T.cdf[coff + mid] <= cf) lo = mid; else hi = mid;
+        }
+        v = lo;
+        uint32_t st = T.cdf[coff + v];
+        uint32_t fr = T.cdf[coff + v + 1] - st;
+        x = fr * (x >> 16) + cf - st;
+      }
+      const bool need = active && x < kRansL;
+      const unsigned m = __ballot_sync(0xffffffffu, need);
+      wpos -= __popc(m);
+      if (wpos < 0) { bad = true; wpos = 0; }
+      if (need) x = (x << 16) | (uint32_t)words[wpos + __popc(m & lt)];
+    }
+    const bool esc = active && v == maxv;
+    int nnib = 0;
+    uint32_t raw = 0;
+    if (__any_sync(0xffffffffu, esc)) {
+      int nops = esc ? 2 : 1;
+      for (int ts = 1;; ++ts) {
+        const bool has = ts < nops;
+        if (!__any_sync(0xffffffffu, has)) break;
+        if (has) {
+          uint32_t cf = x & 0xffffu;
+          uint32_t val = cf >> 12;
+          x = (x >> 16) * 4096u + (cf & 0xfffu);
+          if (ts == 1) {
+            nnib = (int)val;
+            if (nnib > 8) { nnib = 8; bad = true; }
+            nops = 2 + nnib;
+          } else {
+            raw |= val << (4 * (ts - 2));
+          }
+        }
+        const bool need = has && x < kRansL;
+        const unsigned m = __ballot_sync(0xffffffffu, need);
+        wpos -= __popc(m);
+        if (wpos < 0) { bad = true; wpos = 0; }
+        if (need) x = (x << 16) | (uint32_t)words[wpos + __popc(m & lt)];
+      }
+    }
+    if (active) {
+      int64_t val = v;
+      if (esc) {
+        val = (int64_t)(raw >> 1);
+        if (raw & 1u) val = -val - 1; else val += maxv;
+      }
+      sym[i] = (int32_t)(val + offs);
+    }
+  }
+  if (__any_sync(0xffffffffu, bad) && lane == 0) atomicExch(status, 2);
+}
+
+}  // namespace pcc
+
+using namespace pcc;
+
+static inline int32_t nseg_of(int64_t n, int32_t seg) { return (int32_t)((n + seg - 1) / seg); }
+
+extern "C" {
+
+int64_t pcc_rans_max_bytes(int64_t n, int32_t seg_size) {
+  if (n <= 0 || seg_size <= 0) return 64;
+  int64_t ns = nseg_of(n, seg_size);
+  return 16 + 4 * ns + ns * (132 + 2 * seg_cap_words(seg_size) + 4);
+}
+int64_t pcc_rans_workspace_bytes(int64_t n, int32_t seg_size) {
+  if (n <= 0 || seg_size <= 0) return 256;
+  int64_t ns = nseg_of(n, seg_size);
+  return align_up(ns * seg_cap_words(seg_size) * 2, 256) + align_up(ns * 128, 256) + align_up(ns * 4, 256) + 256;
+}
+
+int pcc_rans_encode(const int32_t* sym, const uint16_t* idx, int64_t chan_len, int64_t n,
+                    int32_t seg_size, const pcc_cdf_tables_t* tables, uint8_t* out,
+                    int32_t* out_bytes_dev, void* ws, int64_t ws_bytes, pcc_stream_t s) {
+  PCC_CHECK_ARG(n > 0 && n < (1ll << 31) && seg_size >= 32 && seg_size % 32 == 0 && tables && out &&
+                out_bytes_dev && ws && sym);
+  PCC_CHECK_ARG(idx || chan_len > 0);
+  PCC_CHECK_ARG(tables->cdf && tables->cdf_off && tables->cdf_size && tables->offset && tables->num_tables > 0);
+  if (ws_bytes < pcc_rans_workspace_bytes(n, seg_size)) {
+    set_error("pcc_rans_encode: workspace too small");
+    return PCC_E_WORKSPACE;
+  }
+  const int32_t ns = nseg_of(n, seg_size);
+  char* p = (char*)ws;
+  uint16_t* scratch = (uint16_t*)p;
+  p += align_up((int64_t)ns * seg_cap_words(seg_size) * 2, 256);
+  uint32_t* states = (uint32_t*)p;
+  p += align_up((int64_t)ns * 128, 256);
+  int32_t* nwords = (int32_t*)p;
+  Tables T{tables->cdf, tables->cdf_off, tables->cdf_size, tables->offset, tables->num_tables};
+  cudaStream_t st = as_stream(s);
+  k_rans_encode<<<ns, 32, 0, st>>>(sym, idx, chan_len > 0 ? chan_len : 1, n, seg_size, T, scratch, states,
+                                   nwords);
+  PCC_LAUNCHED();
+  k_rans_pack<<<ns, 256, 0, st>>>(scratch, states, nwords, ns, seg_size, (uint32_t)n, out, out_bytes_dev);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+
+int pcc_rans_decode(const uint8_t* container, int64_t container_bytes, int32_t seg_size,
+                    const uint16_t* idx, int64_t chan_len, int64_t n,
+                    const pcc_cdf_tables_t* tables, int32_t* sym, int32_t* status_dev,
+                    pcc_stream_t s) {
+  PCC_CHECK_ARG(n > 0 && n < (1ll << 31) && container && tables && sym && status_dev);
+  PCC_CHECK_ARG(seg_size >= 32 && seg_size % 32 == 0);
+  PCC_CHECK_ARG(idx || chan_len > 0);
+  PCC_CHECK_ARG(((uintptr_t)container % 4) == 0);
+  const int32_t ns = nseg_of(n, seg_size);
+  PCC_CHECK_ARG(container_bytes >= 16 + 4ll * ns);
+  Tables T{tables->cdf, tables->cdf_off, tables->cdf_size, tables->offset, tables->num_tables};
+  cudaStream_t st = as_stream(s);
+  PCC_CUDA(cudaMemsetAsync(status_dev, 0, 4, st));
+  k_rans_decode<<<ns, 32, 0, st>>>(container, container_bytes, seg_size, idx, chan_len > 0 ? chan_len : 1, n,
+                                   T, sym, status_dev);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,216 @@
+/*
+ * pcc_b200.h — C ABI of the B200-native learned point-cloud codec hot path.
+ *
+ * Every entry point is `extern "C"`, takes plain device pointers + element
+ * counts + a CUDA stream, never allocates, and returns 0 on success or a
+ * negative PCC_E_* code (message via pcc_last_error()).  Buffers whose size is
+ * data dependent are sized by the caller to a host-visible upper bound; the
+ * true count comes back through a device counter (int32_t*).
+ *
+ * Each function cites the reference call site (file:line under the reference
+ * tree) it replaces.  The reference reaches that arithmetic through
+ * MinkowskiEngine / CompressAI Python bindings; INTEGRATION.md shows the
+ * ctypes stub a maintainer would add on the reference side.
+ *
+ * Coordinate representation used across the ABI: a coordinate (b,x,y,z)
+ * (b >= 0, x,y,z in int16 range) is one uint64 "key":
+ *     key = b << 48 | morton3(x + 32768, y + 32768, z + 32768)
+ * where bit i of x lands on key bit 3i, y on 3i+1, z on 3i+2.  Coordinate sets
+ * are always stored sorted ascending by key and duplicate free; row r of a
+ * feature matrix belongs to keys[r].
+ */
+#ifndef PCC_B200_H
+#define PCC_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* pcc_stream_t; /* cudaStream_t */
+
+#define PCC_OK 0
+#define PCC_E_INVALID (-1)   /* bad argument */
+#define PCC_E_CUDA (-2)      /* CUDA runtime error (launch / copy) */
+#define PCC_E_WORKSPACE (-3) /* workspace too small */
+#define PCC_E_UNSUPPORTED (-4)
+
+int pcc_version(void);
+const char* pcc_last_error(void);
+/* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
+int64_t pcc_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------
+ * (1) coordinates, hash, kernel maps
+ * ------------------------------------------------------------------------------------------ */
+
+/* ME.SparseTensor(coordinates=float/int [N,4]) coordinate conversion: floor + pack.
+ * Replaces the coordinate quantisation of ME.SparseTensor at codec_pipeline.py:262-266,
+ * codec_parallel.py:296-301. */
+int pcc_keys_from_coords_i32(const int32_t* coords, int64_t n, uint64_t* keys, pcc_stream_t s);
+int pcc_keys_from_coords_f32(const float* coords, int64_t n, uint64_t* keys, pcc_stream_t s);
+/* Raw capturer frame (int16 points [n,3], float64 colours [n,3], one batch index) -> keys and
+ * (1,r,g,b) float features; fuses stack_tensors + the cat(ones, colors) of
+ * codec_pipeline.py:257-260 (shared/utils.py:10-42). */
+int pcc_ingest_frame(const int16_t* points, const double* colors, int64_t n, int32_t batch,
+                     uint64_t* keys, float* feats4, pcc_stream_t s);
+/* keys -> int32 [n,4] (b,x,y,z): the `.C` attribute. */
+int pcc_coords_from_keys(const uint64_t* keys, int64_t n, int32_t* coords, pcc_stream_t s);
+
+/* Sort + de-duplicate (first occurrence wins): the hash insert of ME.SparseTensor construction.
+ * src_row[i] (optional) = input row that output row i was taken from. */
+int64_t pcc_sort_unique_workspace_bytes(int64_t n);
+int pcc_sort_unique(const uint64_t* keys_in, int64_t n, uint64_t* keys_out, int32_t* src_row,
+                    int32_t* n_out_dev, void* ws, int64_t ws_bytes, pcc_stream_t s);
+
+/* Stride-2 convolution output coordinates: c' = floor(c / t') * t' (MinkowskiConvolution with
+ * stride 2 inside g_a / h_a / g_s.down_conv: codec_pipeline.py:273,287; codec_parallel.py:302-303).
+ * parent_row[i] = output row of input row i.  log2_stride = log2(t'). */
+int64_t pcc_coords_downsample_workspace_bytes(int64_t n);
+int pcc_coords_downsample(const uint64_t* keys_in, int64_t n, int log2_stride, uint64_t* keys_out,
+                          int32_t* parent_row, int32_t* n_out_dev, void* ws, int64_t ws_bytes,
+                          pcc_stream_t s);
+/* Generative transposed convolution coordinates (k=2, s=2): 8 children per input voxel; child row
+ * 8*p + j, j = dx + 2dy + 4dz  (MinkowskiGenerativeConvolutionTranspose inside g_s / h_s:
+ * codec_parallel.py:376,469).  log2_stride = log2 of the OUTPUT tensor stride. */
+int pcc_coords_children(const uint64_t* keys_in, int64_t n, int log2_stride, uint64_t* keys_out,
+                        pcc_stream_t s);
+
+/* Open-addressing hash (64-bit keys, windows of 4 slots probed by 4 cooperating lanes).
+ * capacity must be a power of two >= 2n. */
+int pcc_hash_build(const uint64_t* keys, int64_t n, uint64_t* table_keys, int32_t* table_vals,
+                   int64_t capacity, pcc_stream_t s);
+/* features_at_coordinates (codec_pipeline.py:401, codec_parallel.py:387): row of each query key or -1. */
+int pcc_hash_query(const uint64_t* queries, int64_t nq, const uint64_t* table_keys,
+                   const int32_t* table_vals, int64_t capacity, int32_t* rows, pcc_stream_t s);
+/* Kernel map of a k=3, stride-1 convolution on tensor stride 2^log2_stride:
+ * nbr[j*n + o] = row of (o + d_j) or -1, j = (dx+1) + 3(dy+1) + 9(dz+1). */
+int pcc_kmap_k3(const uint64_t* keys, int64_t n, int log2_stride, const uint64_t* table_keys,
+                const int32_t* table_vals, int64_t capacity, int32_t* nbr, pcc_stream_t s);
+/* Kernel map of a k=2, stride-2 convolution: nbr[j*n_parent + p] = child row with octant j or -1. */
+int pcc_kmap_down2(const uint64_t* child_keys, const int32_t* parent_row, int64_t n_child,
+                   int log2_child_stride, int32_t* nbr, int64_t n_parent, pcc_stream_t s);
+/* Per-frame row ranges: offsets[b] = first row with batch index >= b, b = 0..num_frames. */
+int pcc_frame_offsets(const uint64_t* keys, int64_t n, int32_t num_frames, int32_t* offsets,
+                      pcc_stream_t s);
+/* Canonical (b,x,y,z)-lexicographic order of shared/utils.py:116-165 (sort_tensor / sort_points):
+ * perm[r] = row holding lexicographic rank r. */
+int64_t pcc_lex_order_workspace_bytes(int64_t n);
+int pcc_lex_order(const uint64_t* keys, int64_t n, int32_t* perm, void* ws, int64_t ws_bytes,
+                  pcc_stream_t s);
+
+/* ------------------------------------------------------------------------------------------
+ * (2) sparse convolution
+ * ------------------------------------------------------------------------------------------ */
+
+/* Weight panel packing for pcc_spconv_umma: w [kvol, cin, cout] float32 (ME layout) ->
+ * bf16 panels in the UMMA K-major core-matrix layout, cin zero-padded to cin_pad. Host function. */
+int64_t pcc_spconv_packed_weight_bytes(int kvol, int cin_pad, int cout);
+int pcc_spconv_pack_weights(const float* w, int kvol, int cin, int cout, int cin_pad,
+                            void* packed_host);
+
+/* Output-stationary gather-GEMM on tcgen05 (MinkowskiConvolution / ConvolutionTranspose forward
+ * inside g_a, h_a, h_s, g_s).  out[o, col0 + n] = act(bias[n] + sum_j in[nbr[j][o]] @ W[j][:, n]
+ * (+ residual[o, n])).  nbr == NULL means kvol == 1 and identity rows (1x1 conv and the dense
+ * form of the k2/s2 generative transpose).  cin multiple of 16, cout multiple of 16 in [16,256].
+ * ldo / ldr = row strides (elements) of out / residual; either output pointer may be NULL. */
+int pcc_spconv_umma(const void* in_bf16, int64_t n_in, int cin, const int32_t* nbr, int64_t n_out,
+                    int kvol, const void* w_packed, const float* bias, int cout,
+                    const void* residual_bf16, int64_t ldr, int relu, void* out_bf16,
+                    float* out_f32, int64_t ldo, pcc_stream_t s);
+/* CUDA-core path for narrow outputs (cout <= 8: occupancy head, colour head, down_conv) and the
+ * test comparator for the tensor-core kernel.  w is plain bf16 [kvol, cin, cout]. */
+int pcc_spconv_simt(const void* in_bf16, int64_t n_in, int cin, const int32_t* nbr, int64_t n_out,
+                    int kvol, const void* w_bf16, const float* bias, int cout,
+                    const void* residual_bf16, int64_t ldr, int relu, void* out_bf16,
+                    float* out_f32, int64_t ldo, pcc_stream_t s);
+
+/* Row utilities. */
+int pcc_rows_f32_to_bf16(const float* src, int c_src, const int32_t* src_row, int64_t n_out,
+                         void* dst_bf16, int c_dst, pcc_stream_t s);
+int pcc_rows_bf16_to_f32(const void* src_bf16, int c_src, int64_t n, float* dst, int c_dst,
+                         pcc_stream_t s);
+int pcc_gather_rows_bf16(const void* src_bf16, int c, const int32_t* src_row, int64_t n_out,
+                         void* dst_bf16, pcc_stream_t s);
+int pcc_gather_rows_f32(const float* src, int c, const int32_t* src_row, int64_t n_out, float* dst,
+                        pcc_stream_t s);
+int pcc_gather_keys(const uint64_t* src, const int32_t* src_row, int64_t n_out, uint64_t* dst,
+                    pcc_stream_t s);
+
+/* Per-frame top-k occupancy selection + pruning (torch.topk + MinkowskiPruning inside
+ * g_s(y_hat, k=ks), codec_parallel.py:469).  Keeps, in frame b, the k[b] rows with the largest
+ * logits; ties -> lower row (= lower key).  keep_row = kept rows ascending, n_keep_dev = count. */
+int64_t pcc_topk_workspace_bytes(int64_t n);
+int pcc_topk_select(const float* logits, const uint64_t* keys, int64_t n,
+                    const int32_t* frame_offsets, const int32_t* k, int32_t num_frames,
+                    int32_t* keep_row, int32_t* n_keep_dev, void* ws, int64_t ws_bytes,
+                    pcc_stream_t s);
+
+/* ------------------------------------------------------------------------------------------
+ * (3) entropy-model kernels.  Latents are [n, C] row-major (rows in key order); symbols and
+ *     indexes are channel-major [C, n] with columns in canonical lexicographic order (perm),
+ *     the serialisation order of CompressAI (`y.F.t()`, codec_pipeline.py:427).
+ * ------------------------------------------------------------------------------------------ */
+
+/* EntropyBottleneck.compress quantisation + the encoder-side decompress round trip
+ * (codec_pipeline.py:305-306): sym = round(z - median_c); z_hat = sym + median_c. */
+int pcc_factorized_quant(const float* z, const int32_t* perm, const float* medians, int64_t n,
+                         int c, int32_t* sym, void* zhat_bf16, float* zhat_f32, pcc_stream_t s);
+/* EntropyBottleneck.decompress dequantisation (codec_parallel.py:307). */
+int pcc_factorized_dequant(const int32_t* sym, const int32_t* perm, const float* medians,
+                           int64_t n, int c, void* zhat_bf16, float* zhat_f32, pcc_stream_t s);
+/* Encoder: features_at_coordinates gather + scale gain + build_indexes + quantise for Q qualities
+ * at once (codec_pipeline.py:400-430).  params rows are [scales(C) | means(C)]; prow[i] = params
+ * row of latent row i (-1 -> zeros); scale is [Q, C]; sym / idx are [Q, C, n]. */
+int pcc_gauss_encode(const float* y, const float* params, const int32_t* prow, const int32_t* perm,
+                     const float* scale, const float* scale_table, int table_len, float scale_bound,
+                     int64_t n, int c, int q, int32_t* sym, uint16_t* idx, pcc_stream_t s);
+/* Decoder: indexes only (codec_parallel.py:386-398). */
+int pcc_gauss_indexes(const float* params, const int32_t* prow, const int32_t* perm,
+                      const float* scale, const float* scale_table, int table_len,
+                      float scale_bound, int64_t n, int c, uint16_t* idx, pcc_stream_t s);
+/* Decoder: dead-zone offset dequantisation (codec_parallel.py:401-409):
+ * y_hat = sign(q) * (|q| - off(max(sigma*s, bound), s)) / s + mu, off = 0 where |q| < 1e-4. */
+int pcc_gauss_dequant(const int32_t* sym, const float* params, const int32_t* prow,
+                      const int32_t* perm, const float* scale, const float* offset_gain,
+                      float scale_bound, int64_t n, int c, void* yhat_bf16, float* yhat_f32,
+                      pcc_stream_t s);
+
+/* CompressAI _CXX.pmf_to_quantized_cdf (host; used by update(), codec_pipeline.py:69).
+ * cdf_out has pmf_len + 1 entries. Returns PCC_E_INVALID if the pmf cannot be quantised. */
+int pcc_pmf_to_quantized_cdf(const float* pmf, int pmf_len, int precision, int32_t* cdf_out);
+
+/* ------------------------------------------------------------------------------------------
+ * (4) interleaved multi-lane rANS ("PCL1" container)
+ *     Symbol semantics follow CompressAI's encode_with_indexes / decode_with_indexes
+ *     (escape to 4-bit bypass nibbles for values outside the table support), so any int32
+ *     symbol round-trips.  One warp = one segment of seg_size symbols = 32 interleaved lanes.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  const uint32_t* cdf;      /* flat quantised CDFs, 16-bit precision (last entry of a row = 65536) */
+  const int32_t* cdf_off;   /* [T] start of table t in cdf */
+  const int32_t* cdf_size;  /* [T] entries in table t (= pmf_length + 2) */
+  const int32_t* offset;    /* [T] symbol offset of table t */
+  int32_t num_tables;
+} pcc_cdf_tables_t;
+
+/* Upper bound on container bytes for n symbols. */
+int64_t pcc_rans_max_bytes(int64_t n, int32_t seg_size);
+int64_t pcc_rans_workspace_bytes(int64_t n, int32_t seg_size);
+/* idx == NULL: table index = i / chan_len (EntropyBottleneck: index = channel).
+ * out: device buffer of pcc_rans_max_bytes; out_bytes_dev: total container size. */
+int pcc_rans_encode(const int32_t* sym, const uint16_t* idx, int64_t chan_len, int64_t n,
+                    int32_t seg_size, const pcc_cdf_tables_t* tables, uint8_t* out,
+                    int32_t* out_bytes_dev, void* ws, int64_t ws_bytes, pcc_stream_t s);
+/* seg_size = the container header's value (the caller holds the host copy of the bytes).
+ * status_dev: 0 ok, 1 truncated container, 2 corrupt stream, 3 header mismatch. */
+int pcc_rans_decode(const uint8_t* container, int64_t container_bytes, int32_t seg_size,
+                    const uint16_t* idx, int64_t chan_len, int64_t n,
+                    const pcc_cdf_tables_t* tables, int32_t* sym, int32_t* status_dev,
+                    pcc_stream_t s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PCC_B200_H */
