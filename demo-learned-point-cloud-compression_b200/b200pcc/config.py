@@ -53,7 +53,7 @@ def layer_specs(cfg):
             L.append((f"g_a.block{i}_{b}.conv0", 27, c, c, 9.0, relu))
             L.append((f"g_a.block{i}_{b}.conv1", 27, c, c, 9.0, 0.5))
         cprev = c
-    L.append(("g_a.head", 1, cprev, cfg["c_y"], 1.0, 3.0))
+    L.append(("g_a.head", 1, cprev, cfg["c_y"], 1.0, 1.0))
     # ---- g_s (mirror)
     L.append(("g_s.pre", 1, cfg["c_y"], w[-1], 1.0, relu))
     ups = [w[1], w[0], cfg["stem"]]
@@ -65,12 +65,12 @@ def layer_specs(cfg):
             L.append((f"g_s.block{i}_{b}.conv1", 27, c, c, 14.0, 0.5))
         L.append((f"g_s.occ{i}", 27, c, 1, 14.0, 1.0))
         cprev = c
-    L.append(("g_s.color", 27, cprev, 3, 9.0, 0.3))
+    L.append(("g_s.color", 27, cprev, 3, 9.0, 0.1))
     L.append(("g_s.down_conv", 8, 1, 1, 4.0, 1.0))
     # ---- hyper transforms
     ch = cfg["c_h"]
     L.append(("entropy_model.h_a.down0", 8, cfg["c_y"], ch, 4.0, 0.5))
-    L.append(("entropy_model.h_a.down1", 8, ch, cfg["c_z"], 4.0, 3.0))
+    L.append(("entropy_model.h_a.down1", 8, ch, cfg["c_z"], 4.0, 4.0))
     L.append(("entropy_model.h_s.up0", 8, cfg["c_z"], ch, 1.0, 0.5))
     L.append(("entropy_model.h_s.up1", 8, ch, ch, 1.0, relu))
     L.append(("entropy_model.h_s.head", 1, ch, 2 * cfg["c_y"], 1.0, 1.0))
@@ -89,8 +89,11 @@ def make_state_dict(cfg=SYNTH_SMALL, seed=DEFAULT_SEED):
     sd["g_s.color.bias"] = np.full(3, 0.5, dtype=np.float32)
     # h_s head: first c_y channels are scales (kept mostly positive), last c_y are means
     hb = sd["entropy_model.h_s.head.bias"]
-    hb[:cy] = 1.5
+    hb[:cy] = 2.5
     hb[cy:] = 0.0
+    hk = sd["entropy_model.h_s.head.kernel"]
+    hk[:, :, :cy] *= 0.5
+    hk[:, :, cy:] *= 0.3
     # scale_nn: MLP 2 -> H -> c_y, softplus output around 1
     H = cfg["scale_nn_hidden"]
     sd["entropy_model.scale_nn.w1"] = (rng.standard_normal((2, H)) * 0.7).astype(np.float32)

@@ -105,6 +105,8 @@ class CompressionPipeline:
         self._stager = _Stager()
         self.h2d_bytes = 0
         self.d2h_bytes = 0
+        self.keep_debug = False     # tests: keep stage tensors of the last call in self.debug
+        self.debug = {}
 
     # ---- reference-shaped steps -------------------------------------------------------------------------
     def unpack_batch(self, gop):
@@ -144,6 +146,8 @@ class CompressionPipeline:
         perm = z.cmap.lex_perm()
         z_strings, zhat = em.entropy_bottleneck.compress_rows(z._feats, perm)
         z_hat = SparseTensor(_cmap=z.cmap, _feats=zhat, _channels=z._channels)
+        if self.keep_debug:
+            self.debug.update(z=z, z_hat=z_hat)
         return z_hat, z_strings, [z.cmap.n]
 
     def hyper_synthesis_step(self, z_hat):
@@ -168,6 +172,8 @@ class CompressionPipeline:
         perm = y.cmap.lex_perm()
         scale = em.scale_for(settings, self.device)
         sym, idx = ops.gauss_encode(y._feats, gaussian_params._feats, prow, perm, scale, gc.table_d, gc.scale_bound)
+        if self.keep_debug:
+            self.debug.update(y=y, gaussian_params=gaussian_params, y_sym=sym, y_idx=idx, scale=scale)
         strings = []
         pending = []
         for qi in range(len(settings)):
@@ -236,6 +242,8 @@ class DecompressionPipeline:
         self._stager = _Stager()
         self.h2d_bytes = 0
         self.d2h_bytes = 0
+        self.keep_debug = False
+        self.debug = {}
 
     def read_bitstream_batched(self, compressed_data):
         return container.read_bitstream_batched(compressed_data)
@@ -278,6 +286,8 @@ class DecompressionPipeline:
         yb, _ = ops.gauss_dequant(sym.view(cy, ycm.n), gaussian_params._feats, prow, perm, scale[0].contiguous(),
                                   em.offset_gain_d, gc.scale_bound)
         y_hat = SparseTensor(_cmap=ycm, _feats=yb, _channels=cy)
+        if self.keep_debug:
+            self.debug.update(y_sym=sym.view(cy, ycm.n), y_idx=idx, y_hat=y_hat, gaussian_params=gaussian_params)
         return y_hat, status
 
     def hyper_synthesis(self, y_hat, ks):

@@ -1,0 +1,199 @@
+"""CPU suite: the oracle against properties and committed golden vectors, the host logic, and that the
+C-ABI library loads and exports every declared symbol (no kernel is launched here)."""
+import json
+import os
+import re
+
+import numpy as np
+import pytest
+
+from oracle import sparse_ref as S
+from oracle import entropy_ref as E
+from oracle import rans_ref as R
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_abi_library_exports_every_declared_symbol():
+    from b200pcc import _lib
+    hdr = open(os.path.join(ROOT, "include", "pcc_b200.h")).read()
+    declared = set(re.findall(r"\b(pcc_[a-z0-9_]+)\s*\(", hdr))
+    assert declared, "no declarations parsed"
+    assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
+    for name in declared:
+        assert hasattr(_lib.lib, name)
+    assert _lib.lib.pcc_version() >= 100
+
+
+def test_abi_host_functions_without_gpu():
+    from b200pcc import ops, _lib
+    pmf = np.array([0.1, 0.2, 0.4, 0.2, 0.1, 1e-9], np.float32)
+    got = ops.pmf_to_quantized_cdf(pmf)
+    assert np.array_equal(got, E.pmf_to_quantized_cdf(pmf))
+    assert got[-1] == 65536 and np.all(np.diff(got) > 0)
+    with pytest.raises(_lib.PccError):
+        ops.pmf_to_quantized_cdf(np.array([np.nan, 1.0], np.float32))
+    # weight packing: UMMA K-major core-matrix layout  byte = kc*cout*16 + co*16 + e*2
+    rng = np.random.default_rng(0)
+    w = rng.normal(0, 1, (2, 20, 16)).astype(np.float32)
+    packed = ops.pack_weights_umma(w, 32).numpy().view(np.uint16).reshape(2, 4, 16, 8)
+    ref = S.bf16_round(np.concatenate([w, np.zeros((2, 12, 16), np.float32)], axis=1))
+    ref16 = (ref.view(np.uint32) >> 16).astype(np.uint16)            # [j, ci, co]
+    assert np.array_equal(packed, ref16.reshape(2, 4, 8, 16).transpose(0, 1, 3, 2))
+
+
+def test_product_has_no_oracle_import_and_no_cpu_path():
+    pkg = os.path.join(ROOT, "demo-learned-point-cloud-compression_b200", "b200pcc")
+    for fn in os.listdir(pkg):
+        if fn.endswith(".py"):
+            src = open(os.path.join(pkg, fn)).read()
+            assert "oracle" not in src.replace("CPU oracle", ""), fn
+
+
+def test_canonical_sort_equals_reference_weights():
+    rng = np.random.default_rng(0)
+    C = np.concatenate([rng.integers(0, 4, (5000, 1)), rng.integers(-400, 400, (5000, 3))], axis=1)
+    C = np.unique(C, axis=0)
+    rng.shuffle(C)
+    assert np.array_equal(np.argsort(S.lex_key(C), kind="stable"), S.sort_order_reference(C))
+
+
+def test_sparse_tensor_floor_dedup_first_wins():
+    C = np.array([[0, 1.5, -0.5, 2.0], [0, 1.2, -0.9, 2.9], [0, -3.0, 0.0, 0.0]])
+    F = np.array([[1.0], [2.0], [3.0]], np.float32)
+    Co, Fo = S.sparse_tensor(C, F)
+    assert Co.tolist() == [[0, -3, 0, 0], [0, 1, -1, 2]] and Fo.ravel().tolist() == [3.0, 1.0]
+
+
+def test_stride_and_kernel_map_conventions():
+    C = np.array([[0, -1, 0, 3], [0, -2, 1, 2], [0, 2, 2, 2], [1, 0, 0, 0]], np.int32)
+    assert S.stride_coords(C, 2).tolist() == [[0, -2, 0, 2], [0, 2, 2, 2], [1, 0, 0, 0]]
+    o3 = S.region_offsets(3, 2)
+    assert o3[0].tolist() == [-2, -2, -2] and o3[1].tolist() == [0, -2, -2] and o3[13].tolist() == [0, 0, 0]
+    o2 = S.region_offsets(2, 4)
+    assert o2.tolist()[:3] == [[0, 0, 0], [4, 0, 0], [0, 4, 0]]
+    # forward/transposed maps are mirror images
+    Cs = S.sparse_tensor(np.random.default_rng(1).integers(-6, 6, (300, 4)).astype(float) * [0, 1, 1, 1])[0]
+    Cc = S.stride_coords(Cs, 2)
+    fwd = S.kernel_map(Cs, Cc, S.region_offsets(2, 1))
+    bwd = S.kernel_map(Cc, Cs, S.region_offsets(2, 1), transposed=True)
+    for j in range(8):
+        o = np.nonzero(fwd[j] >= 0)[0]
+        assert np.array_equal(bwd[j][fwd[j][o]], o)
+    # every fine voxel has exactly one parent/offset
+    assert np.array_equal((bwd >= 0).sum(axis=0), np.ones(len(Cs), int))
+    # generative coordinates: 8 disjoint children per voxel
+    assert len(S.generative_coords(Cc, 1)) == 8 * len(Cc)
+
+
+def test_conv_linearity_and_bf16_rounding():
+    rng = np.random.default_rng(2)
+    Cs = S.sparse_tensor(np.concatenate([np.zeros((400, 1)), rng.integers(-5, 5, (400, 3))], axis=1).astype(float))[0]
+    nbr = S.kernel_map(Cs, Cs, S.region_offsets(3, 1))
+    W = rng.normal(0, 1, (27, 8, 5)).astype(np.float32)
+    A, B = rng.normal(0, 1, (2, len(Cs), 8)).astype(np.float32)
+    lhs = S.conv_forward(A + B, nbr, W)
+    rhs = S.conv_forward(A, nbr, W) + S.conv_forward(B, nbr, W)
+    np.testing.assert_allclose(lhs, rhs, rtol=1e-4, atol=1e-4)
+    x = np.array([1.0, 1.00390625, 1.01171875, -3.3895314e38, 0.0], np.float32)
+    r = S.bf16_round(x)
+    assert r[0] == 1.0 and r[1] == 1.0 and r[2] == np.float32(1.015625)     # ties to even
+    assert np.all((r.view(np.uint32) & 0xFFFF) == 0)
+
+
+def test_topk_tie_rule_and_counts():
+    C = np.array([[0, 0, 0, 0], [0, 1, 0, 0], [0, 0, 1, 0], [0, 1, 1, 0], [1, 0, 0, 0]], np.int32)
+    logits = np.array([0.5, 0.5, 0.5, 0.9, -1.0], np.float32)
+    keep = S.topk_mask(logits, C, [2, 1])
+    assert keep.tolist() == [True, False, False, True, True]   # tie -> lowest Morton key (0,0,0)
+
+
+def test_gaussian_tables_shape_facts():
+    rows, lens, offs = E.gaussian_tables()
+    assert len(rows) == 64 and sum(len(r) for r in rows) == 27256 and max(lens) == 3133
+    assert all(r[0] == 0 and r[-1] == 65536 and np.all(np.diff(r) > 0) for r in rows)
+    t = E.scale_table()
+    assert abs(t[0] - 0.11) < 1e-6 and abs(t[-1] - 256) < 1e-3
+    idx = E.build_indexes(np.array([0.0, 0.11, 0.12, 1.0, 300.0], np.float32))
+    assert idx[0] == 0 and idx[1] == 0 and idx[-1] == 63 and np.all(np.diff(idx) >= 0)
+    assert E.quantize_symbols(np.array([0.5, 1.5, 2.5, -0.5], np.float32), 0).tolist() == [0, 2, 2, 0]
+
+
+@pytest.mark.parametrize("n,seg", [(1, 32), (31, 32), (1000, 64), (50_000, 4096)])
+def test_rans_oracles_roundtrip_any_int32(n, seg):
+    rows, lens, offs = E.gaussian_tables()
+    t = R.Tables(rows, offs)
+    rng = np.random.default_rng(n)
+    idx = rng.integers(0, 64, n)
+    sym = np.rint(rng.normal(0, 1, n) * E.scale_table()[idx]).astype(np.int32)
+    sym[:: max(n // 7, 1)] = rng.integers(-2 ** 30, 2 ** 30, len(sym[:: max(n // 7, 1)]))
+    b = R.ref64_encode(sym, idx, t)
+    assert len(b) % 4 == 0 and np.array_equal(R.ref64_decode(b, idx, t), sym)
+    c = R.pcl1_encode(sym, idx, 1, t, seg)
+    assert c[:4] == b"PCL1" and np.array_equal(R.pcl1_decode(c, idx, 1, n, t), sym)
+    with pytest.raises(RuntimeError):
+        R.pcl1_decode(c[: len(c) // 2], idx, 1, n, t)
+
+
+def test_geometry_stream_roundtrip():
+    from b200pcc import geometry, synth
+    p = synth.small_frame(seed=9, n_target=8000)["points"].astype(np.int64)
+    p8 = np.unique(np.floor_divide(p, 8) * 8, axis=0)
+    s = geometry.encode_points(p8, 8)
+    q = geometry.decode_points(s, 8)
+    assert sorted(map(tuple, q)) == sorted(map(tuple, p8))
+    assert len(s) < 3 * len(p8)                     # ~1-2 bytes per point
+    assert geometry.decode_points(geometry.encode_points(np.zeros((0, 3), int))).shape == (0, 3)
+    one = np.array([[-16, 8, 0]])
+    assert geometry.decode_points(geometry.encode_points(one)).tolist() == one.tolist()
+    with pytest.raises(ValueError):
+        geometry.decode_points(s[: len(s) - 5], 8)
+
+
+def test_container_roundtrip_and_layout():
+    from b200pcc import container
+    import struct
+    ks = [[3, 4], [30, 40], [300, 400]]
+    blob = container.make_bitstream_batched(b"YYYY", b"ZZ", 7, 2, [b"p0", b"pp1"], ks, (1.0, 0.25))
+    # App. B.1: int32 num_frames, float64 q_geo, float64 q_att, big endian
+    assert struct.unpack(">idd", blob[:20]) == (2, 1.0, 0.25)
+    assert struct.unpack(">iiii", blob[20:36]) == (7, 2, 4, 2)
+    y, z, ysh, zsh, pts, ks2, q = container.read_bitstream_batched(blob)
+    assert (y, z, ysh, zsh, pts, ks2, q) == ([b"YYYY"], [b"ZZ"], 7, 2, [b"p0", b"pp1"], ks, (1.0, 0.25))
+    with pytest.raises(ValueError):
+        container.read_bitstream_batched(blob[:-1])
+    b2 = container.make_bitstream([b"y0", b"y1"], [b"z0", b"z1"], [5, 6], [1, 2], [b"a", b"bb"], ks, (0.0, 1.0))
+    out = container.read_bitstream(b2)
+    assert out[0] == [b"y0", b"y1"] and out[1] == [b"z0", b"z1"] and out[2] == [5, 6] and out[5] == ks
+
+
+def test_scale_nn_host_matches_oracle():
+    from b200pcc import config as cfgmod
+    from b200pcc.model import ScaleNN
+    sd = cfgmod.make_state_dict()
+    nn = ScaleNN(64, 64)
+    nn.load(sd)
+    for q in ([1.0, 0.0], [0.0, 1.0], [1, 1], [0.3, 0.7]):
+        ref = E.scale_nn(q, sd["entropy_model.scale_nn.w1"], sd["entropy_model.scale_nn.b1"],
+                         sd["entropy_model.scale_nn.w2"], sd["entropy_model.scale_nn.b2"])
+        assert np.array_equal(nn.numpy([q])[0], ref) and np.all(ref > 0)
+
+
+def test_golden_vectors():
+    """Known-answer fixtures generated by tests/golden/make_golden.py (oracle output, committed)."""
+    path = os.path.join(ROOT, "tests", "golden", "oracle_small.npz")
+    g = np.load(path)
+    from b200pcc import config as cfgmod, synth
+    from oracle.codec_ref import RefCodec
+    frames = [synth.small_frame(seed=int(g["seed"]), n_target=int(g["n_target"]))]
+    assert np.array_equal(frames[0]["points"], g["points"])
+    codec = RefCodec(cfgmod.SYNTH_SMALL, cfgmod.make_state_dict(), bf16=True)
+    blob = codec.compress(frames, [[1.0, 1.0]])
+    assert np.array_equal(blob["y_coords"], g["y_coords"])
+    assert blob["k"] == g["k"].tolist()
+    assert np.array_equal(blob["debug"]["y_sym"][0], g["y_sym"])
+    assert np.frombuffer(blob["y_strings"][0], np.uint8).tobytes() == g["y_string"].tobytes()
+    assert np.frombuffer(blob["z_string"], np.uint8).tobytes() == g["z_string"].tobytes()
+    out, _ = codec.decompress(blob, 0)
+    assert np.array_equal(out[0]["points"], g["dec_points"])
+    np.testing.assert_allclose(out[0]["colors"], g["dec_colors"], atol=1e-6)

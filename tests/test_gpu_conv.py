@@ -1,0 +1,188 @@
+"""GPU parity: tcgen05 sparse convolution vs the CPU oracle and vs the CUDA-core comparator."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+from oracle import sparse_ref as S  # noqa: E402
+from helpers import stack_frames  # noqa: E402
+
+# bf16 operands, fp32 accumulation on both sides; only the summation order differs
+RTOL, ATOL = 2e-3, 2e-3
+
+
+@pytest.fixture(scope="module")
+def dev():
+    return torch.device("cuda:0")
+
+
+@pytest.fixture(scope="module")
+def cloud(dev):
+    from b200pcc import synth, ops
+    from b200pcc.sparse import CoordMap
+    C, _ = stack_frames([synth.small_frame(seed=5, n_target=12000)])
+    keys, _ = ops.sort_unique(ops.keys_from_coords(torch.from_numpy(C).to(dev)))
+    cm = CoordMap(keys, 0)
+    return cm, ops.coords_from_keys(keys).cpu().numpy()
+
+
+def _bf16_t(a, dev):
+    return torch.from_numpy(np.ascontiguousarray(a, np.float32)).to(dev).to(torch.bfloat16).contiguous()
+
+
+def _run_umma(ops, x, nbr, n_out, w, bias, relu=False, residual=None, f32=True):
+    kvol, cin, cout = w.shape
+    dev = x.device
+    wp = ops.pack_weights_umma(w, x.shape[1]).to(dev)
+    bd = torch.from_numpy(bias).to(dev)
+    ob = torch.empty((n_out, cout), dtype=torch.bfloat16, device=dev)
+    of = torch.empty((n_out, cout), dtype=torch.float32, device=dev) if f32 else None
+    ops.spconv_umma(x, nbr, n_out, kvol, wp, bd, cout, residual, relu, ob, of)
+    torch.cuda.synchronize()
+    return ob, of
+
+
+@pytest.mark.parametrize("cin,cout", [(16, 32), (32, 32), (64, 64), (128, 128), (64, 256), (32, 16)])
+def test_k3_conv_vs_oracle(cloud, dev, cin, cout):
+    from b200pcc import ops
+    cm, Cg = cloud
+    n = cm.n
+    rng = np.random.default_rng(cin * 1000 + cout)
+    F = rng.normal(0, 1, (n, cin)).astype(np.float32)
+    W = (rng.normal(0, 1, (27, cin, cout)) / np.sqrt(cin * 9)).astype(np.float32)
+    b = rng.normal(0, 0.1, cout).astype(np.float32)
+    R = rng.normal(0, 1, (n, cout)).astype(np.float32)
+    x = _bf16_t(F, dev)
+    r = _bf16_t(R, dev)
+    nbr = cm.nbr3()
+    ob, of = _run_umma(ops, x, nbr, n, W, b, relu=True, residual=r)
+    nbr_np = nbr.cpu().numpy()
+    ref = S.conv_forward(S.bf16_round(F), nbr_np, W, b, residual=S.bf16_round(R), relu=True, bf16=True)
+    got = of.cpu().numpy()
+    np.testing.assert_allclose(got, ref, rtol=RTOL, atol=ATOL)
+    # the bf16 output is the rounding of the fp32 output
+    assert torch.equal(ob, of.to(torch.bfloat16))
+    # independent CUDA-core comparator
+    wb = _bf16_t(W, dev)
+    of2 = torch.empty_like(of)
+    ops.spconv_simt(x, nbr, n, 27, wb, torch.from_numpy(b).to(dev), cout, r, True, None, of2)
+    np.testing.assert_allclose(got, of2.cpu().numpy(), rtol=RTOL, atol=ATOL)
+
+
+def test_conv_deterministic_and_row_order_invariant(cloud, dev):
+    """SURVEY 3.2 invariant 3: same result run to run and for any row order of the input set."""
+    from b200pcc import ops
+    cm, Cg = cloud
+    n, c = cm.n, 64
+    rng = np.random.default_rng(7)
+    F = rng.normal(0, 1, (n, c)).astype(np.float32)
+    W = (rng.normal(0, 1, (27, c, c)) / np.sqrt(c * 9)).astype(np.float32)
+    b = np.zeros(c, np.float32)
+    x = _bf16_t(F, dev)
+    nbr = cm.nbr3()
+    _, a = _run_umma(ops, x, nbr, n, W, b)
+    _, a2 = _run_umma(ops, x, nbr, n, W, b)
+    assert torch.equal(a, a2)
+    # permute the rows: features move with their coordinates, kernel map re-indexed accordingly
+    perm = torch.from_numpy(rng.permutation(n)).to(dev)            # new row i holds old row perm[i]
+    inv = torch.empty_like(perm)
+    inv[perm] = torch.arange(n, device=dev)
+    xp = x[perm].contiguous()
+    nbr_p = nbr[:, perm].long()
+    nbr_p = torch.where(nbr_p >= 0, inv[nbr_p.clamp_min(0)], nbr_p).int().contiguous()
+    _, ap = _run_umma(ops, xp, nbr_p, n, W, b)
+    assert torch.equal(ap, a[perm])
+
+
+def test_down_conv_and_1x1(cloud, dev):
+    from b200pcc import ops
+    cm, Cg = cloud
+    coarse = cm.downsample()
+    nbr = cm.nbr_down()
+    rng = np.random.default_rng(11)
+    cin, cout = 32, 64
+    F = rng.normal(0, 1, (cm.n, cin)).astype(np.float32)
+    W = (rng.normal(0, 1, (8, cin, cout)) / np.sqrt(cin * 4)).astype(np.float32)
+    b = rng.normal(0, 0.1, cout).astype(np.float32)
+    x = _bf16_t(F, dev)
+    _, of = _run_umma(ops, x, nbr, coarse.n, W, b, relu=True)
+    ref = S.conv_forward(S.bf16_round(F), nbr.cpu().numpy(), W, b, relu=True, bf16=True)
+    np.testing.assert_allclose(of.cpu().numpy(), ref, rtol=RTOL, atol=ATOL)
+    # 1x1 (identity rows), tail tile not a multiple of 128
+    W1 = (rng.normal(0, 1, (1, cin, 48)) / np.sqrt(cin)).astype(np.float32)
+    b1 = rng.normal(0, 0.1, 48).astype(np.float32)
+    _, o1 = _run_umma(ops, x, None, cm.n, W1, b1)
+    ref1 = S.conv_forward(S.bf16_round(F), None, W1, b1, bf16=True)
+    np.testing.assert_allclose(o1.cpu().numpy(), ref1, rtol=RTOL, atol=ATOL)
+
+
+def test_generative_transpose_dense_form(cloud, dev):
+    """GenUp (dense [n, 8*cout] GEMM) == oracle transposed-convolution kernel map semantics."""
+    from b200pcc import ops
+    from b200pcc.model import GenUp
+    from b200pcc.sparse import CoordMap
+    from helpers import to_canonical
+    cm, Cg = cloud
+    C8 = S.stride_coords(Cg, 8)
+    keys, _ = ops.sort_unique(ops.keys_from_coords(torch.from_numpy(C8).to(dev)))
+    pm = CoordMap(keys, 3)
+    Cp = ops.coords_from_keys(keys).cpu().numpy()
+    rng = np.random.default_rng(13)
+    for cin, cout in [(64, 32), (128, 64)]:
+        g = GenUp("t", cin, cout)
+        W = (rng.normal(0, 1, (8, cin, cout)) / np.sqrt(cin)).astype(np.float32)
+        b = rng.normal(0, 0.1, cout).astype(np.float32)
+        g.load({"t.kernel": W, "t.bias": b})
+        g.to(dev)
+        F = rng.normal(0, 1, (pm.n, cin)).astype(np.float32)
+        out = g(_bf16_t(F, dev), relu=True).float().cpu().numpy()
+        ch = pm.children()
+        Cc = ops.coords_from_keys(ch.keys).cpu().numpy()
+        # oracle: canonical order on both sides
+        Cp_c, F_c = to_canonical(Cp, F)
+        Co = S.generative_coords(Cp_c, 4)
+        nbr = S.kernel_map(Cp_c, Co, S.region_offsets(2, 4), transposed=True)
+        ref = S.bf16_round(S.conv_forward(S.bf16_round(F_c), nbr, W, b, relu=True, bf16=True))
+        Cc_c, out_c = to_canonical(Cc, out)
+        assert np.array_equal(Cc_c, Co)
+        np.testing.assert_allclose(out_c, ref, rtol=1e-2, atol=1e-2)
+
+
+def test_narrow_heads(cloud, dev):
+    from b200pcc import ops
+    cm, Cg = cloud
+    rng = np.random.default_rng(17)
+    n, cin = cm.n, 32
+    F = rng.normal(0, 1, (n, cin)).astype(np.float32)
+    x = _bf16_t(F, dev)
+    nbr = cm.nbr3()
+    for cout in (1, 3):
+        W = (rng.normal(0, 1, (27, cin, cout)) / np.sqrt(cin * 9)).astype(np.float32)
+        b = rng.normal(0, 0.1, cout).astype(np.float32)
+        out = torch.empty((n, cout), dtype=torch.float32, device=dev)
+        ops.spconv_simt(x, nbr, n, 27, _bf16_t(W, dev), torch.from_numpy(b).to(dev), cout, None, False, None, out)
+        ref = S.conv_forward(S.bf16_round(F), nbr.cpu().numpy(), W, b, bf16=True)
+        np.testing.assert_allclose(out.cpu().numpy(), ref, rtol=RTOL, atol=ATOL)
+
+
+def test_topk_select(cloud, dev):
+    from b200pcc import ops
+    cm, Cg = cloud
+    rng = np.random.default_rng(19)
+    C2 = np.concatenate([Cg, Cg * np.array([1, 1, 1, 1]) + np.array([1, 0, 0, 0])]).astype(np.int32)  # 2 frames
+    keys, _ = ops.sort_unique(ops.keys_from_coords(torch.from_numpy(C2).to(dev)))
+    Ck = ops.coords_from_keys(keys).cpu().numpy()
+    n = len(Ck)
+    logits = rng.normal(0, 1, n).astype(np.float32)
+    logits[::7] = 0.25          # many exact ties
+    logits[5::31] = -0.0
+    logits[6::31] = 0.0
+    ks = [n // 5, n // 3]
+    off = ops.frame_offsets(keys, 2)
+    keep = ops.topk_select(torch.from_numpy(logits).to(dev), keys, off,
+                           torch.tensor(ks, dtype=torch.int32, device=dev), 2).cpu().numpy()
+    ref = np.nonzero(S.topk_mask(logits, Ck, ks))[0]
+    assert np.array_equal(keep, ref)
+    assert len(keep) == sum(ks)
