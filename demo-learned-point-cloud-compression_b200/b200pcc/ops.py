@@ -15,6 +15,45 @@ from ._lib import lib, check, CdfTables
 _WS = {}
 
 
+class KernelProfiler:
+    """Optional per-family CUDA-event timing on the launching stream (bench.py's roofline leg).
+    A record is (family, algorithmic bytes, flops, start event, stop event)."""
+
+    def __init__(self):
+        self.records = []
+
+    def summary(self):
+        out = {}
+        for fam, nbytes, flops, e0, e1 in self.records:
+            d = out.setdefault(fam, {"launches": 0, "ms": 0.0, "bytes": 0, "flops": 0})
+            d["launches"] += 1
+            d["ms"] += e0.elapsed_time(e1)
+            d["bytes"] += nbytes
+            d["flops"] += flops
+        return out
+
+
+PROFILER = None
+
+
+class _prof:
+    def __init__(self, family, nbytes=0, flops=0):
+        self.family, self.nbytes, self.flops = family, int(nbytes), int(flops)
+
+    def __enter__(self):
+        if PROFILER is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+        return self
+
+    def __exit__(self, *exc):
+        if PROFILER is not None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            PROFILER.records.append((self.family, self.nbytes, self.flops, self.e0, e1))
+        return False
+
+
 def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
 
@@ -88,7 +127,8 @@ def sort_unique(keys: torch.Tensor, want_src: bool = True):
     cnt = torch.empty(1, dtype=torch.int32, device=dev)
     wsb = lib.pcc_sort_unique_workspace_bytes(n)
     ws = workspace(wsb, dev)
-    check(lib.pcc_sort_unique(_ptr(keys), n, _ptr(out), _ptr(src), _ptr(cnt), _ptr(ws), ws.numel(), _stream()))
+    with _prof("sort_unique", n * (16 + 12 + (8 if want_src else 0))):
+        check(lib.pcc_sort_unique(_ptr(keys), n, _ptr(out), _ptr(src), _ptr(cnt), _ptr(ws), ws.numel(), _stream()))
     m = int(cnt.item())
     return out[:m], (src[:m] if want_src else None)
 
@@ -130,7 +170,8 @@ def hash_build(keys: torch.Tensor):
     cap = hash_capacity(n)
     tk = torch.empty(cap, dtype=torch.int64, device=keys.device)
     tv = torch.empty(cap, dtype=torch.int32, device=keys.device)
-    check(lib.pcc_hash_build(_ptr(keys), n, _ptr(tk), _ptr(tv), cap, _stream()))
+    with _prof("hash_build", n * 28):      # 16 B/coord read-equivalent + 12 B/slot written
+        check(lib.pcc_hash_build(_ptr(keys), n, _ptr(tk), _ptr(tv), cap, _stream()))
     return tk, tv
 
 
@@ -147,7 +188,8 @@ def kmap_k3(keys: torch.Tensor, log2_stride: int, table) -> torch.Tensor:
     tk, tv = table
     n = keys.shape[0]
     nbr = torch.empty((27, n), dtype=torch.int32, device=keys.device)
-    check(lib.pcc_kmap_k3(_ptr(keys), n, log2_stride, _ptr(tk), _ptr(tv), tk.shape[0], _ptr(nbr), _stream()))
+    with _prof("kmap_k3", n * (8 + 27 * 4)):   # key read once + 27 map entries written per output row
+        check(lib.pcc_kmap_k3(_ptr(keys), n, log2_stride, _ptr(tk), _ptr(tv), tk.shape[0], _ptr(nbr), _stream()))
     return nbr
 
 
@@ -223,8 +265,9 @@ def topk_select(logits: torch.Tensor, keys: torch.Tensor, frame_off: torch.Tenso
     cnt = torch.empty(1, dtype=torch.int32, device=dev)
     wsb = lib.pcc_topk_workspace_bytes(n)
     ws = workspace(wsb, dev)
-    check(lib.pcc_topk_select(_ptr(logits), _ptr(keys), n, _ptr(frame_off), _ptr(k), num_frames, _ptr(keep),
-                              _ptr(cnt), _ptr(ws), ws.numel(), _stream()))
+    with _prof("topk_select", n * (4 + 8 + 4)):
+        check(lib.pcc_topk_select(_ptr(logits), _ptr(keys), n, _ptr(frame_off), _ptr(k), num_frames, _ptr(keep),
+                                  _ptr(cnt), _ptr(ws), ws.numel(), _stream()))
     m = int(cnt.item())
     return keep[:m]
 
@@ -256,8 +299,12 @@ def spconv_umma(x: torch.Tensor, nbr: Optional[torch.Tensor], n_out: int, kvol: 
     if residual is not None:
         rp = residual.data_ptr() + col0 * esz_b
         ldr = residual.shape[1]
-    check(lib.pcc_spconv_umma(_ptr(x), x.shape[0], x.shape[1], _ptr(nbr), n_out, kvol, _ptr(w_packed),
-                              _ptr(bias), cout, rp, ldr, int(relu), ob, of, ldo, _stream()))
+    cin = x.shape[1]
+    nbytes = 2 * x.shape[0] * cin + n_out * cout * ((2 if ob else 0) + (4 if of else 0) + (2 if rp else 0)) + \
+        (4 * kvol * n_out if nbr is not None else 0) + 2 * kvol * cin * cout
+    with _prof(f"spconv_umma_k{kvol}_c{cin}x{cout}", nbytes, 2 * kvol * n_out * cin * cout):
+        check(lib.pcc_spconv_umma(_ptr(x), x.shape[0], x.shape[1], _ptr(nbr), n_out, kvol, _ptr(w_packed),
+                                  _ptr(bias), cout, rp, ldr, int(relu), ob, of, ldo, _stream()))
 
 
 def spconv_simt(x: torch.Tensor, nbr: Optional[torch.Tensor], n_out: int, kvol: int, w_bf16: torch.Tensor,
@@ -267,9 +314,12 @@ def spconv_simt(x: torch.Tensor, nbr: Optional[torch.Tensor], n_out: int, kvol: 
     _need_cuda(x, torch.bfloat16)
     ldo = (out_bf16 if out_bf16 is not None else out_f32).shape[1]
     ldr = residual.shape[1] if residual is not None else 0
-    check(lib.pcc_spconv_simt(_ptr(x), x.shape[0], x.shape[1], _ptr(nbr), n_out, kvol, _ptr(w_bf16),
-                              _ptr(bias), cout, _ptr(residual), ldr, int(relu), _ptr(out_bf16), _ptr(out_f32),
-                              ldo, _stream()))
+    cin = x.shape[1]
+    nbytes = 2 * x.shape[0] * cin + n_out * cout * 4 + (4 * kvol * n_out if nbr is not None else 0)
+    with _prof(f"spconv_simt_k{kvol}_c{cin}x{cout}", nbytes, 2 * kvol * n_out * cin * cout):
+        check(lib.pcc_spconv_simt(_ptr(x), x.shape[0], x.shape[1], _ptr(nbr), n_out, kvol, _ptr(w_bf16),
+                                  _ptr(bias), cout, _ptr(residual), ldr, int(relu), _ptr(out_bf16), _ptr(out_f32),
+                                  ldo, _stream()))
 
 
 # ------------------------------------------------------------------------------------------------
@@ -303,8 +353,9 @@ def gauss_encode(y: torch.Tensor, params: torch.Tensor, prow: Optional[torch.Ten
     q = scale.shape[0]
     sym = torch.empty((q, c, n), dtype=torch.int32, device=y.device)
     idx = torch.empty((q, c, n), dtype=torch.int16, device=y.device)
-    check(lib.pcc_gauss_encode(_ptr(y), _ptr(params), _ptr(prow), _ptr(perm), _ptr(scale), _ptr(table),
-                               table.shape[0], bound, n, c, q, _ptr(sym), _ptr(idx), _stream()))
+    with _prof("gauss_encode", n * c * (12 + 6 * q)):   # y, sigma, mu read once; int32 sym + u16 idx per quality
+        check(lib.pcc_gauss_encode(_ptr(y), _ptr(params), _ptr(prow), _ptr(perm), _ptr(scale), _ptr(table),
+                                   table.shape[0], bound, n, c, q, _ptr(sym), _ptr(idx), _stream()))
     return sym, idx
 
 
@@ -363,8 +414,9 @@ def rans_encode(sym: torch.Tensor, idx: Optional[torch.Tensor], chan_len: int, t
     nbytes = torch.empty(1, dtype=torch.int32, device=dev)
     wsb = lib.pcc_rans_workspace_bytes(n, seg_size)
     ws = workspace(wsb, dev, "rans")
-    check(lib.pcc_rans_encode(_ptr(sym), _ptr(idx), chan_len, n, seg_size, C.byref(tables.struct), _ptr(out),
-                              _ptr(nbytes), _ptr(ws), ws.numel(), _stream()))
+    with _prof("rans_encode", n * 6):      # int32 symbol + u16 index per symbol (+ emitted bytes)
+        check(lib.pcc_rans_encode(_ptr(sym), _ptr(idx), chan_len, n, seg_size, C.byref(tables.struct), _ptr(out),
+                                  _ptr(nbytes), _ptr(ws), ws.numel(), _stream()))
     return out, nbytes
 
 
@@ -374,6 +426,7 @@ def rans_decode(container: torch.Tensor, seg_size: int, idx: Optional[torch.Tens
     dev = container.device
     sym = torch.empty(n, dtype=torch.int32, device=dev)
     status = torch.empty(1, dtype=torch.int32, device=dev)
-    check(lib.pcc_rans_decode(_ptr(container), container.numel(), seg_size, _ptr(idx), chan_len, n,
-                              C.byref(tables.struct), _ptr(sym), _ptr(status), _stream()))
+    with _prof("rans_decode", n * 6):
+        check(lib.pcc_rans_decode(_ptr(container), container.numel(), seg_size, _ptr(idx), chan_len, n,
+                                  C.byref(tables.struct), _ptr(sym), _ptr(status), _stream()))
     return sym, status

@@ -109,26 +109,35 @@ class CompressionPipeline:
         self.debug = {}
 
     # ---- reference-shaped steps -------------------------------------------------------------------------
-    def unpack_batch(self, gop):
-        """frames list -> batched sparse tensor (codec_pipeline.py:239-267, shared/utils.py:10-42)."""
-        frames = gop.pop("frames")
+    def stage_frames(self, frames):
+        """Host->device copy of the raw frames (pinned staging, async DMA).  Returns device tensors."""
         pts, cols = [], []
         for item in frames:
             if "points" not in item:      # "Sometimes we miss a frame?" (codec_pipeline.py:247-249)
                 continue
             pts.append(np.ascontiguousarray(item["points"], dtype=np.int16))
             cols.append(np.ascontiguousarray(item["colors"], dtype=np.float64))
+        staged = self._stager.to_device(pts + cols, self.device)
+        self.h2d_bytes += sum(a.nbytes for a in pts) + sum(a.nbytes for a in cols)
+        nf = len(pts)
+        return {"points": staged[:nf], "colors": staged[nf:]}
+
+    def unpack_batch(self, gop, staged=None):
+        """frames list -> batched sparse tensor (codec_pipeline.py:239-267, shared/utils.py:10-42).
+        `staged` (from stage_frames) skips the host->device copy: inputs already resident in HBM."""
+        frames = gop.pop("frames")
+        if staged is None:
+            staged = self.stage_frames(frames)
+        pts, cols = staged["points"], staged["colors"]
         dev = self.device
-        total = sum(p.shape[0] for p in pts)
+        total = sum(int(p.shape[0]) for p in pts)
         keys = torch.empty(total, dtype=torch.int64, device=dev)
         feats = torch.empty((total, 4), dtype=torch.float32, device=dev)
-        staged = self._stager.to_device(pts + cols, dev)
-        self.h2d_bytes += sum(a.nbytes for a in pts) + sum(a.nbytes for a in cols)
         pos = 0
         nf = len(pts)
         for b in range(nf):
-            n = pts[b].shape[0]
-            ops.ingest_frame(staged[b], staged[nf + b], b, keys[pos:pos + n], feats[pos:pos + n])
+            n = int(pts[b].shape[0])
+            ops.ingest_frame(pts[b], cols[b], b, keys[pos:pos + n], feats[pos:pos + n])
             pos += n
         ukeys, src = ops.sort_unique(keys, want_src=True)
         x = SparseTensor(_cmap=CoordMap(ukeys, 0), _feats=ops.rows_f32_to_bf16(feats, 16, src), _channels=4)
@@ -185,14 +194,14 @@ class CompressionPipeline:
         return strings, [y.cmap.n]
 
     # ---- entry point -----------------------------------------------------------------------------------------
-    def compress(self, data):
+    def compress(self, data, staged=None):
         """gop dict -> (compressed_data {0: raw frames, i+1: bytes for settings[i]}, sideinfo)."""
         with self._lock, torch.cuda.device(self.device):
             t_start = time.time()
             compressed_data = {0: data["frames"]}
             tm = _StageTimer()
             tm.mark("start")
-            x, sideinfo = self.unpack_batch(data)
+            x, sideinfo = self.unpack_batch(data, staged)
             num_points = x.cmap.n
             nf = x.num_frames
             tm.mark("unpack")
@@ -308,7 +317,9 @@ class DecompressionPipeline:
             batch.append({"points": pts, "colors": col})
         return batch
 
-    def decompress(self, compressed_data):
+    def decompress(self, compressed_data, to_host=True):
+        """bytes -> (frames, sideinfo).  to_host=False leaves the reconstruction on the device (returns
+        the SparseTensor instead of the per-frame numpy dicts)."""
         with self._lock, torch.cuda.device(self.device):
             t_start = time.time()
             tm = _StageTimer()
@@ -330,7 +341,7 @@ class DecompressionPipeline:
             tm.mark("guassian_model")
             x_hat = self.hyper_synthesis(y_hat, ks)
             tm.mark("synthesis_transform")
-            final_data = self.pack_batches(x_hat, nf)
+            final_data = self.pack_batches(x_hat, nf) if to_host else x_hat
             status = int(st_z.item()) | int(st_y.item())
             if status != 0:
                 raise ops._lib.PccError(f"entropy decode failed (status {status})")
