@@ -142,6 +142,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--points", type=int, default=800_000)
     ap.add_argument("--breakdown", action="store_true", help="print per-kernel-family table to stderr")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer arm (short runs under ncu)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -218,13 +219,13 @@ def main():
     # ---------------- end-to-end arm (public API, host buffers) ----------------
     enc2 = CompressionPipeline(settings, device=dev, model=model)
     dec2 = DecompressionPipeline(device=dev, model=model)
-    for i in range(2):
+    for i in range(0 if args.no_e2e else 2):
         c, _ = enc2.compress(gop(i))
         dec2.decompress(c[1])
     enc2.h2d_bytes = enc2.d2h_bytes = dec2.h2d_bytes = dec2.d2h_bytes = 0
     barrier()
     e2e_ms = []
-    e2e_steps = max(steps // 2, 3)
+    e2e_steps = 0 if args.no_e2e else max(steps // 2, 3)
     for i in range(e2e_steps):
         flush.fill_(i & 0xFF)
         torch.cuda.synchronize()
@@ -280,10 +281,11 @@ def main():
             "latency_ms": {"encode_p50": float(np.median(enc_ms)), "decode_p50": float(np.median(dec_ms)),
                            "step_p50": float(np.median(step_ms))},
             "fps": steps / total_s,
-            "e2e": {"value": e2e_pts / e2e_total / 1e6, "unit": UNIT,
-                    "h2d_bytes_per_step": int((enc2.h2d_bytes + dec2.h2d_bytes) / e2e_steps),
-                    "d2h_bytes_per_step": int((enc2.d2h_bytes + dec2.d2h_bytes) / e2e_steps),
-                    "ms_per_step": 1e3 * e2e_total / e2e_steps},
+            "e2e": None if not e2e_steps else {
+                "value": e2e_pts / e2e_total / 1e6, "unit": UNIT,
+                "h2d_bytes_per_step": int((enc2.h2d_bytes + dec2.h2d_bytes) / e2e_steps),
+                "d2h_bytes_per_step": int((enc2.d2h_bytes + dec2.d2h_bytes) / e2e_steps),
+                "ms_per_step": 1e3 * e2e_total / e2e_steps},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": roof,
