@@ -12,7 +12,7 @@ receiver/decoder/codec_parallel.py:302-307, 376, 394-409, 469):
           .decompress(strings, idx) / .lower_bound_scale(s)
 
 The layer graph is the canonical stand-in of config.py.  All sparse convolutions run through
-libpcc_b200.so: tcgen05 gather-GEMM for wide layers, the CUDA-core path for <= 8 output channels.
+libpcc_b200.so: the persistent tcgen05 gather-GEMM kernel (narrow heads zero-padded to N = 16).
 """
 import math
 from typing import List, Optional
@@ -39,8 +39,9 @@ def _pad16(c: int) -> int:
 class Conv:
     """One sparse convolution's parameters, prepared for the kernels on ``.to(device)``."""
 
-    def __init__(self, name: str, kvol: int, cin: int, cout: int):
+    def __init__(self, name: str, kvol: int, cin: int, cout: int, simt: bool = False):
         self.name, self.kvol, self.cin, self.cout = name, kvol, cin, cout
+        self.simt = simt            # CUDA-core path (only the 1->1 coordinate-only down_conv)
         self.kernel = np.zeros((kvol, cin, cout), dtype=np.float32)
         self.bias = np.zeros(cout, dtype=np.float32)
         self.device = None
@@ -57,10 +58,19 @@ class Conv:
     def to(self, device):
         self.device = device
         self.bias_d = torch.from_numpy(self.bias).to(device)
-        if self.narrow:
+        if self.simt:
             w = np.zeros((self.kvol, self.cin_pad, self.cout), dtype=np.float32)
             w[:, : self.cin] = self.kernel
             self.w_d = torch.from_numpy(w).to(device).to(torch.bfloat16).contiguous()
+        elif self.narrow:
+            # narrow heads (occupancy C->1, colour C->3) ride the tensor-core kernel with the output
+            # channels zero-padded to one UMMA N=16 tile; only `cout` columns are stored.
+            w = np.zeros((self.kvol, self.cin, 16), dtype=np.float32)
+            w[:, :, : self.cout] = self.kernel
+            b = np.zeros(16, dtype=np.float32)
+            b[: self.cout] = self.bias
+            self.w_d = ops.pack_weights_umma(w, self.cin_pad).to(device)
+            self.bias_d = torch.from_numpy(b).to(device)
         else:
             self.w_d = ops.pack_weights_umma(self.kernel, self.cin_pad).to(device)
         return self
@@ -69,9 +79,15 @@ class Conv:
                  residual: Optional[torch.Tensor] = None, out_f32=False):
         """x: bf16 [n_in, cin_pad].  Returns bf16 [n_out, cout] (or fp32 when out_f32)."""
         dev = x.device
-        if self.narrow:
+        if self.simt:
             out = torch.empty((n_out, self.cout), dtype=torch.float32, device=dev)
             ops.spconv_simt(x, nbr, n_out, self.kvol, self.w_d, self.bias_d, self.cout, residual, relu, None, out)
+            return out
+        if self.narrow:
+            assert residual is None
+            out = torch.empty((n_out, self.cout), dtype=torch.float32, device=dev)
+            ops.spconv_umma(x, nbr, n_out, self.kvol, self.w_d, self.bias_d, 16, None, relu, None, out,
+                            cstore=self.cout)
             return out
         ob = of = None
         if out_f32:
@@ -199,7 +215,7 @@ class SynthesisTransform(_Module):
             self.occ.append(Conv(f"g_s.occ{i}", 27, c, 1))
             cprev = c
         self.color = Conv("g_s.color", 27, cprev, 3)
-        self.down_conv_w = Conv("g_s.down_conv", 8, 1, 1)
+        self.down_conv_w = Conv("g_s.down_conv", 8, 1, 1, simt=True)
 
     def down_conv(self, t: SparseTensor) -> SparseTensor:
         """g_s.down_conv(t): MinkowskiConvolution(1,1,k=2,s=2) used by the decoder only for its output

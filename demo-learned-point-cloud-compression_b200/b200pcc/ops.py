@@ -188,8 +188,30 @@ def kmap_k3(keys: torch.Tensor, log2_stride: int, table) -> torch.Tensor:
     tk, tv = table
     n = keys.shape[0]
     nbr = torch.empty((27, n), dtype=torch.int32, device=keys.device)
-    with _prof("kmap_k3", n * (8 + 27 * 4)):   # key read once + 27 map entries written per output row
+    with _prof("kmap_k3_voxelhash", n * (8 + 27 * 4)):
         check(lib.pcc_kmap_k3(_ptr(keys), n, log2_stride, _ptr(tk), _ptr(tv), tk.shape[0], _ptr(nbr), _stream()))
+    return nbr
+
+
+def blockmap_build(keys: torch.Tensor, log2_stride: int):
+    """4x4x4-block table of a sorted key set -> (table keys, table values [cap, 2] int64)."""
+    _need_cuda(keys, torch.int64)
+    n = keys.shape[0]
+    cap = hash_capacity(n)
+    tk = torch.empty(cap, dtype=torch.int64, device=keys.device)
+    tv = torch.empty((cap, 2), dtype=torch.int64, device=keys.device)
+    with _prof("blockmap_build", n * 8 + cap * 8 + (n // 8) * 24):   # keys read, table cleared, ~n/8 entries
+        check(lib.pcc_blockmap_build(_ptr(keys), n, log2_stride, _ptr(tk), _ptr(tv), cap, _stream()))
+    return tk, tv
+
+
+def kmap_k3_blocks(keys: torch.Tensor, log2_stride: int, btable) -> torch.Tensor:
+    tk, tv = btable
+    n = keys.shape[0]
+    nbr = torch.empty((27, n), dtype=torch.int32, device=keys.device)
+    with _prof("kmap_k3", n * (8 + 27 * 4)):   # key read once + 27 map entries written per output row
+        check(lib.pcc_kmap_k3_blocks(_ptr(keys), n, log2_stride, _ptr(tk), _ptr(tv), tk.shape[0], _ptr(nbr),
+                                     _stream()))
     return nbr
 
 
@@ -288,8 +310,9 @@ def pack_weights_umma(w: np.ndarray, cin_pad: int) -> torch.Tensor:
 def spconv_umma(x: torch.Tensor, nbr: Optional[torch.Tensor], n_out: int, kvol: int, w_packed: torch.Tensor,
                 bias: Optional[torch.Tensor], cout: int, residual: Optional[torch.Tensor] = None,
                 relu: bool = False, out_bf16: Optional[torch.Tensor] = None,
-                out_f32: Optional[torch.Tensor] = None, col0: int = 0) -> None:
-    """Writes columns [col0, col0+cout) of the given output tensors."""
+                out_f32: Optional[torch.Tensor] = None, col0: int = 0, cstore: int = 0) -> None:
+    """Writes columns [col0, col0+cout) of the given output tensors (cstore in 1..15: narrow head, only
+    the first cstore columns exist in the output)."""
     _need_cuda(x, torch.bfloat16)
     esz_b = 2
     ob = None if out_bf16 is None else out_bf16.data_ptr() + col0 * esz_b
@@ -300,11 +323,12 @@ def spconv_umma(x: torch.Tensor, nbr: Optional[torch.Tensor], n_out: int, kvol: 
         rp = residual.data_ptr() + col0 * esz_b
         ldr = residual.shape[1]
     cin = x.shape[1]
-    nbytes = 2 * x.shape[0] * cin + n_out * cout * ((2 if ob else 0) + (4 if of else 0) + (2 if rp else 0)) + \
+    cw = cstore if 0 < cstore < cout else cout
+    nbytes = 2 * x.shape[0] * cin + n_out * (cw * ((2 if ob else 0) + (4 if of else 0)) + cout * (2 if rp else 0)) + \
         (4 * kvol * n_out if nbr is not None else 0) + 2 * kvol * cin * cout
     with _prof(f"spconv_umma_k{kvol}_c{cin}x{cout}", nbytes, 2 * kvol * n_out * cin * cout):
         check(lib.pcc_spconv_umma(_ptr(x), x.shape[0], x.shape[1], _ptr(nbr), n_out, kvol, _ptr(w_packed),
-                                  _ptr(bias), cout, rp, ldr, int(relu), ob, of, ldo, _stream()))
+                                  _ptr(bias), cout, rp, ldr, int(relu), ob, of, ldo, int(cstore), _stream()))
 
 
 def spconv_simt(x: torch.Tensor, nbr: Optional[torch.Tensor], n_out: int, kvol: int, w_bf16: torch.Tensor,

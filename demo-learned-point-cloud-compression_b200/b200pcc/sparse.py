@@ -44,9 +44,10 @@ class CoordMap:
         return self._table
 
     def nbr3(self) -> torch.Tensor:
-        """[27, n] kernel map of a k=3 stride-1 convolution on this map."""
+        """[27, n] kernel map of a k=3 stride-1 convolution on this map (block-table probing)."""
         if self._nbr3 is None:
-            self._nbr3 = ops.kmap_k3(self.keys, self.log2_stride, self.table())
+            bt = ops.blockmap_build(self.keys, self.log2_stride)
+            self._nbr3 = ops.kmap_k3_blocks(self.keys, self.log2_stride, bt)
         return self._nbr3
 
     def coords(self) -> torch.Tensor:

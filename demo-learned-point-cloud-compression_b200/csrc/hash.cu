@@ -123,6 +123,142 @@ __global__ void k_kmap_down2(const uint64_t* __restrict__ ckeys, const int32_t* 
   nbr[(int64_t)j * n_parent + parent[i]] = (int32_t)i;
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Block table: the sorted key set cut into 4x4x4-voxel Morton blocks.  Rows of one block are
+// contiguous (keys are sorted), so a block is described by its first row and a 64-bit occupancy
+// mask; the row of voxel `idx` (6 Morton bits) is base + popc(mask & ((1 << idx) - 1)).
+// The hash (same open addressing, windows of 4 keys = one 32-byte sector) is keyed on
+// key >> (3*log2_stride + 6); a 3x3x3 neighbourhood touches at most 2x2x2 blocks, so the k=3 kernel
+// map needs <= 8 probes per row instead of 26, all of them shared with the neighbouring rows
+// (L1 hits), and the table has ~n/12 entries on surface data.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_blockmap_insert(const uint64_t* __restrict__ keys, int64_t n, int shift, uint64_t* __restrict__ tk,
+                  ulonglong2* __restrict__ tv, uint64_t cap_mask) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint64_t k = keys[i];
+  const uint64_t bkey = k >> (shift + 6);
+  if (i > 0 && (keys[i - 1] >> (shift + 6)) == bkey) return;  // not the first row of its block
+  uint64_t mask = 1ull << ((k >> shift) & 63ull);
+  for (int64_t j = i + 1; j < n && j < i + 64; ++j) {
+    const uint64_t kj = keys[j];
+    if ((kj >> (shift + 6)) != bkey) break;
+    mask |= 1ull << ((kj >> shift) & 63ull);
+  }
+  uint64_t base = hash_key(bkey) & cap_mask & ~(uint64_t)(kWin - 1);
+  for (uint64_t probes = 0; probes <= cap_mask; probes += kWin) {
+#pragma unroll
+    for (int j = 0; j < kWin; ++j) {
+      const uint64_t slot = base + j;
+      const uint64_t prev = atomicCAS((unsigned long long*)&tk[slot], (unsigned long long)kEmptyKey,
+                                      (unsigned long long)bkey);
+      if (prev == kEmptyKey) {   // block keys are unique: no "already present" case
+        tv[slot] = make_ulonglong2(mask, (unsigned long long)i);
+        return;
+      }
+    }
+    base = (base + kWin) & cap_mask;
+  }
+}
+
+struct BlockEntry {
+  uint64_t mask;
+  int32_t base;
+};
+
+__device__ __forceinline__ BlockEntry block_lookup(uint64_t bkey, const uint64_t* __restrict__ tk,
+                                                   const ulonglong2* __restrict__ tv, uint64_t cap_mask) {
+  BlockEntry e;
+  e.mask = 0;
+  e.base = 0;
+  uint64_t base = hash_key(bkey) & cap_mask & ~(uint64_t)(kWin - 1);
+  for (uint64_t probes = 0; probes <= cap_mask; probes += kWin) {
+    const ulonglong2 k01 = __ldg(reinterpret_cast<const ulonglong2*>(tk + base));
+    const ulonglong2 k23 = __ldg(reinterpret_cast<const ulonglong2*>(tk + base + 2));
+    int hit = -1;
+    if (k01.x == bkey) hit = 0;
+    else if (k01.y == bkey) hit = 1;
+    else if (k23.x == bkey) hit = 2;
+    else if (k23.y == bkey) hit = 3;
+    if (hit >= 0) {
+      const ulonglong2 v = __ldg(tv + base + hit);
+      e.mask = v.x;
+      e.base = (int32_t)v.y;
+      return e;
+    }
+    if (k01.x == kEmptyKey || k01.y == kEmptyKey || k23.x == kEmptyKey || k23.y == kEmptyKey) return e;
+    base = (base + kWin) & cap_mask;
+  }
+  return e;
+}
+
+// 6-bit Morton index of (x,y,z) low 2 bits each: x0 y0 z0 x1 y1 z1 -> bits 0..5
+__device__ __forceinline__ int morton2(int x, int y, int z) {
+  return (x & 1) | ((y & 1) << 1) | ((z & 1) << 2) | ((x & 2) << 2) | ((y & 2) << 3) | ((z & 2) << 4);
+}
+
+__global__ void __launch_bounds__(256)
+k_kmap_k3_blocks(const uint64_t* __restrict__ keys, int64_t n, int l, const uint64_t* __restrict__ tk,
+                 const ulonglong2* __restrict__ tv, uint64_t cap_mask, int32_t* __restrict__ nbr) {
+  const int64_t o = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (o >= n) return;
+  int b, x, y, z;
+  unpack_key(keys[o], b, x, y, z);
+  const int step = 1 << l;
+  // voxel coordinates in units of `step`, biased to be non-negative (17 bits incl. the +-1 halo)
+  const int ux = (x + 32768) >> l, uy = (y + 32768) >> l, uz = (z + 32768) >> l;
+  const int umax = (65536 >> l) - 1;
+  const int lx = (ux - 1) >> 2, hx = (ux + 1) >> 2;
+  const int ly = (uy - 1) >> 2, hy = (uy + 1) >> 2;
+  const int lz = (uz - 1) >> 2, hz = (uz + 1) >> 2;
+  (void)step;
+  uint64_t bm[8];
+  int32_t bb[8];
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    const int ax = c & 1, ay = (c >> 1) & 1, az = c >> 2;
+    // duplicates (lo == hi along an axis) reuse the entry already fetched
+    if (ax && hx == lx) { bm[c] = bm[c ^ 1]; bb[c] = bb[c ^ 1]; continue; }
+    if (ay && hy == ly) { bm[c] = bm[c ^ 2]; bb[c] = bb[c ^ 2]; continue; }
+    if (az && hz == lz) { bm[c] = bm[c ^ 4]; bb[c] = bb[c ^ 4]; continue; }
+    const int bx = ax ? hx : lx, by = ay ? hy : ly, bz = az ? hz : lz;
+    bm[c] = 0;
+    bb[c] = 0;
+    const int bmax = umax >> 2;
+    if (bx >= 0 && by >= 0 && bz >= 0 && bx <= bmax && by <= bmax && bz <= bmax) {
+      // block key = pack_key(b, block corner) >> (3l + 6) = frame bits | morton(bx, by, bz)
+      const uint64_t bkey = (((uint64_t)(uint32_t)b << 48) >> (3 * l + 6)) | spread3_16((uint32_t)bx) |
+                            (spread3_16((uint32_t)by) << 1) | (spread3_16((uint32_t)bz) << 2);
+      const BlockEntry e = block_lookup(bkey, tk, tv, cap_mask);
+      bm[c] = e.mask;
+      bb[c] = e.base;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 27; ++j) {
+    const int dx = j % 3 - 1, dy = (j / 3) % 3 - 1, dz = j / 9 - 1;
+    int32_t r = -1;
+    if (j == 13) {
+      r = (int32_t)o;
+    } else {
+      const int nx = ux + dx, ny = uy + dy, nz = uz + dz;
+      const bool sx = (nx >> 2) != lx, sy = (ny >> 2) != ly, sz = (nz >> 2) != lz;
+      // 8-way select without dynamic register indexing
+      const uint64_t m0 = sx ? bm[1] : bm[0], m1 = sx ? bm[3] : bm[2], m2 = sx ? bm[5] : bm[4], m3 = sx ? bm[7] : bm[6];
+      const int32_t b0 = sx ? bb[1] : bb[0], b1 = sx ? bb[3] : bb[2], b2 = sx ? bb[5] : bb[4], b3 = sx ? bb[7] : bb[6];
+      const uint64_t mm0 = sy ? m1 : m0, mm1 = sy ? m3 : m2;
+      const int32_t bb0 = sy ? b1 : b0, bb1 = sy ? b3 : b2;
+      const uint64_t m = sz ? mm1 : mm0;
+      const int32_t base = sz ? bb1 : bb0;
+      const int idx = morton2(nx, ny, nz);
+      if ((m >> idx) & 1ull) r = base + __popcll(m & ((1ull << idx) - 1ull));
+    }
+    nbr[(int64_t)j * n + o] = r;
+  }
+}
+
 }  // namespace pcc
 
 using namespace pcc;
@@ -180,6 +316,36 @@ int pcc_kmap_down2(const uint64_t* child_keys, const int32_t* parent_row, int64_
   if (n_child == 0) return PCC_OK;
   k_kmap_down2<<<(unsigned)((n_child + 255) / 256), 256, 0, st>>>(
       child_keys, parent_row, n_child, 3 * log2_child_stride, nbr, n_parent);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+
+int pcc_blockmap_build(const uint64_t* keys, int64_t n, int log2_stride, uint64_t* table_keys,
+                       void* table_vals16, int64_t capacity, pcc_stream_t s) {
+  PCC_CHECK_ARG(n >= 0 && log2_stride >= 0 && log2_stride <= 13);
+  PCC_CHECK_ARG(capacity >= 8 && (capacity & (capacity - 1)) == 0 && capacity >= 2 * n);
+  PCC_CHECK_ARG(table_keys && table_vals16 && ((uintptr_t)table_vals16 % 16) == 0 &&
+                ((uintptr_t)table_keys % 32) == 0);
+  cudaStream_t st = as_stream(s);
+  k_hash_clear<<<(unsigned)((capacity + 255) / 256), 256, 0, st>>>(table_keys, capacity);
+  PCC_LAUNCHED();
+  if (n == 0) return PCC_OK;
+  PCC_CHECK_ARG(keys);
+  k_blockmap_insert<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(keys, n, 3 * log2_stride, table_keys,
+                                                                (ulonglong2*)table_vals16,
+                                                                (uint64_t)capacity - 1);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+
+int pcc_kmap_k3_blocks(const uint64_t* keys, int64_t n, int log2_stride, const uint64_t* table_keys,
+                       const void* table_vals16, int64_t capacity, int32_t* nbr, pcc_stream_t s) {
+  PCC_CHECK_ARG(n >= 0 && log2_stride >= 0 && log2_stride <= 13);
+  PCC_CHECK_ARG(capacity >= 8 && (capacity & (capacity - 1)) == 0);
+  if (n == 0) return PCC_OK;
+  PCC_CHECK_ARG(keys && table_keys && table_vals16 && nbr);
+  k_kmap_k3_blocks<<<(unsigned)((n + 255) / 256), 256, 0, as_stream(s)>>>(
+      keys, n, log2_stride, table_keys, (const ulonglong2*)table_vals16, (uint64_t)capacity - 1, nbr);
   PCC_LAUNCHED();
   return PCC_OK;
 }

@@ -88,6 +88,16 @@ int pcc_hash_query(const uint64_t* queries, int64_t nq, const uint64_t* table_ke
  * nbr[j*n + o] = row of (o + d_j) or -1, j = (dx+1) + 3(dy+1) + 9(dz+1). */
 int pcc_kmap_k3(const uint64_t* keys, int64_t n, int log2_stride, const uint64_t* table_keys,
                 const int32_t* table_vals, int64_t capacity, int32_t* nbr, pcc_stream_t s);
+/* Block table: the same open-addressing hash keyed on 4x4x4-voxel Morton blocks
+ * (key >> (3*log2_stride + 6)); value = {64-bit occupancy mask, first row}.  Rows of a block are
+ * contiguous in the sorted key set, so row(voxel idx) = base + popc(mask & ((1 << idx) - 1)).
+ * table_vals16: capacity x 16 bytes.  capacity: power of two >= 2n.
+ * pcc_kmap_k3_blocks builds the same [27, n] kernel map as pcc_kmap_k3 with <= 8 block probes per
+ * row (a 3x3x3 neighbourhood spans at most 2x2x2 blocks). */
+int pcc_blockmap_build(const uint64_t* keys, int64_t n, int log2_stride, uint64_t* table_keys,
+                       void* table_vals16, int64_t capacity, pcc_stream_t s);
+int pcc_kmap_k3_blocks(const uint64_t* keys, int64_t n, int log2_stride, const uint64_t* table_keys,
+                       const void* table_vals16, int64_t capacity, int32_t* nbr, pcc_stream_t s);
 /* Kernel map of a k=2, stride-2 convolution: nbr[j*n_parent + p] = child row with octant j or -1. */
 int pcc_kmap_down2(const uint64_t* child_keys, const int32_t* parent_row, int64_t n_child,
                    int log2_child_stride, int32_t* nbr, int64_t n_parent, pcc_stream_t s);
@@ -113,14 +123,23 @@ int pcc_spconv_pack_weights(const float* w, int kvol, int cin, int cout, int cin
 /* Output-stationary gather-GEMM on tcgen05 (MinkowskiConvolution / ConvolutionTranspose forward
  * inside g_a, h_a, h_s, g_s).  out[o, col0 + n] = act(bias[n] + sum_j in[nbr[j][o]] @ W[j][:, n]
  * (+ residual[o, n])).  nbr == NULL means kvol == 1 and identity rows (1x1 conv and the dense
- * form of the k2/s2 generative transpose).  cin multiple of 16, cout multiple of 16 in [16,256].
- * ldo / ldr = row strides (elements) of out / residual; either output pointer may be NULL. */
+ * form of the k2/s2 generative transpose).  cin in {16,32,64,128,256} (pad channels with zeros),
+ * cout multiple of 16 in [16,256].  ldo / ldr = row strides (elements) of out / residual; either
+ * output pointer may be NULL.  cstore: 0 or cout = store all columns; 1..15 = narrow head
+ * (occupancy logits C->1, colour head C->3: weights zero-padded to cout = 16, only the first
+ * cstore columns are written, ldo >= cstore).
+ * Kernel: persistent (one CTA per SM), warp specialised (4 gather warps, 1 MMA warp, 4 epilogue
+ * warps), cp.async gather into a multi-stage ring, tcgen05.mma into double-buffered TMEM
+ * accumulators; kernel offsets with no neighbour in a 128-row tile are skipped. */
 int pcc_spconv_umma(const void* in_bf16, int64_t n_in, int cin, const int32_t* nbr, int64_t n_out,
                     int kvol, const void* w_packed, const float* bias, int cout,
                     const void* residual_bf16, int64_t ldr, int relu, void* out_bf16,
-                    float* out_f32, int64_t ldo, pcc_stream_t s);
-/* CUDA-core path for narrow outputs (cout <= 8: occupancy head, colour head, down_conv) and the
- * test comparator for the tensor-core kernel.  w is plain bf16 [kvol, cin, cout]. */
+                    float* out_f32, int64_t ldo, int cstore, pcc_stream_t s);
+/* Tuning knobs of pcc_spconv_umma (process wide; defaults 16, 2, 0): maximum ring depth, how many
+ * stages the full-barrier signal trails the ring depth by, and cp.async.cg (L2 only) instead of .ca. */
+int pcc_spconv_set_tuning(int max_stages, int lag_slack, int use_cg);
+/* CUDA-core sparse convolution: independent comparator of the tensor-core kernel in the tests
+ * (any cin / cout); the product path only uses it for the 1->1 coordinate-only g_s.down_conv.  w is plain bf16 [kvol, cin, cout]. */
 int pcc_spconv_simt(const void* in_bf16, int64_t n_in, int cin, const int32_t* nbr, int64_t n_out,
                     int kvol, const void* w_bf16, const float* bias, int cout,
                     const void* residual_bf16, int64_t ldr, int relu, void* out_bf16,

@@ -152,6 +152,7 @@ def test_generative_transpose_dense_form(cloud, dev):
 
 def test_narrow_heads(cloud, dev):
     from b200pcc import ops
+    from b200pcc.model import Conv
     cm, Cg = cloud
     rng = np.random.default_rng(17)
     n, cin = cm.n, 32
@@ -165,6 +166,41 @@ def test_narrow_heads(cloud, dev):
         ops.spconv_simt(x, nbr, n, 27, _bf16_t(W, dev), torch.from_numpy(b).to(dev), cout, None, False, None, out)
         ref = S.conv_forward(S.bf16_round(F), nbr.cpu().numpy(), W, b, bf16=True)
         np.testing.assert_allclose(out.cpu().numpy(), ref, rtol=RTOL, atol=ATOL)
+        # product path: the same head on the tensor-core kernel, output channels zero-padded to N=16
+        conv = Conv(f"head{cout}", 27, cin, cout)
+        conv.load({f"head{cout}.kernel": W, f"head{cout}.bias": b})
+        conv.to(dev)
+        out2 = conv(x, nbr, n)
+        assert out2.shape == (n, cout) and out2.dtype == torch.float32
+        np.testing.assert_allclose(out2.cpu().numpy(), ref, rtol=RTOL, atol=ATOL)
+
+
+def test_persistent_kernel_many_tiles_and_sparse_offsets(dev):
+    """More tiles than SMs (every CTA walks several tiles through both TMEM accumulators) on a cloud
+    thin enough that whole kernel offsets are absent from some 128-row tiles (offset skipping)."""
+    from b200pcc import ops
+    from b200pcc.sparse import CoordMap
+    rng = np.random.default_rng(23)
+    # a single-voxel-thick plane z = 0 plus a few scattered points: 18 of 27 offsets are mostly empty
+    xy = np.stack(np.meshgrid(np.arange(-200, 200), np.arange(-160, 160), indexing="ij"), -1).reshape(-1, 2)
+    C = np.concatenate([np.zeros((len(xy), 1), np.int64), xy, np.zeros((len(xy), 1), np.int64)], axis=1)
+    extra = np.concatenate([np.zeros((500, 1), np.int64), rng.integers(-200, 200, (500, 3))], axis=1)
+    C = np.concatenate([C, extra]).astype(np.int32)
+    keys, _ = ops.sort_unique(ops.keys_from_coords(torch.from_numpy(C).to(dev)))
+    cm = CoordMap(keys, 0)
+    n = cm.n
+    assert n > 128 * 148 * 3
+    for cin, cout in ((32, 32), (64, 64)):
+        F = rng.normal(0, 1, (n, cin)).astype(np.float32)
+        W = (rng.normal(0, 1, (27, cin, cout)) / np.sqrt(cin * 9)).astype(np.float32)
+        b = rng.normal(0, 0.1, cout).astype(np.float32)
+        x = _bf16_t(F, dev)
+        nbr = cm.nbr3()
+        _, of = _run_umma(ops, x, nbr, n, W, b, relu=False)
+        ref = S.conv_forward(S.bf16_round(F), nbr.cpu().numpy(), W, b, bf16=True)
+        np.testing.assert_allclose(of.cpu().numpy(), ref, rtol=RTOL, atol=ATOL)
+        _, of2 = _run_umma(ops, x, nbr, n, W, b, relu=False)
+        assert torch.equal(of, of2)
 
 
 def test_topk_select(cloud, dev):

@@ -106,6 +106,9 @@ def test_kmap_k3_and_hash_query(frames, dev, log2s):
     Cg = ops.coords_from_keys(keys).cpu().numpy()
     ref = S.kernel_map(Cg, Cg, S.region_offsets(3, t))   # oracle on the product's row order
     assert np.array_equal(nbr, ref)
+    # product path: 4x4x4 block table (<= 8 probes per row) must give the identical map
+    nbr_b = ops.kmap_k3_blocks(keys, log2s, ops.blockmap_build(keys, log2s)).cpu().numpy()
+    assert np.array_equal(nbr_b, ref)
     pairs = (nbr >= 0).sum() / len(Cg)
     assert 3.0 < pairs < 27.0
     # queries: half present, half absent
@@ -114,6 +117,29 @@ def test_kmap_k3_and_hash_query(frames, dev, log2s):
     q[2000:, 1] += 1 if t == 1 else 1   # off-grid / probably absent
     rows = ops.hash_query(ops.keys_from_coords(torch.from_numpy(q).to(dev)), table).cpu().numpy()
     assert np.array_equal(rows, S.lookup_rows(Cg, q))
+
+
+def test_block_kmap_edges_of_the_coordinate_range(dev):
+    """Voxels on the int16 borders, several frames, isolated voxels and dense 8-children slabs."""
+    from b200pcc import ops
+    rng = np.random.default_rng(5)
+    pts = [np.array([[0, -32768, -32768, -32768], [0, 32767, 32767, 32767], [0, -32768, 32767, 0],
+                     [1, -32768, -32768, -32768], [2, 0, 0, 0], [2, 3, 3, 3], [2, 4, 4, 4], [2, -1, -1, -1]])]
+    dense = np.stack(np.meshgrid(np.arange(-9, 7), np.arange(30, 41), np.arange(-3, 2), indexing="ij"), -1).reshape(-1, 3)
+    pts.append(np.concatenate([np.full((len(dense), 1), 1), dense], axis=1))
+    iso = rng.integers(-3000, 3000, (3000, 3))
+    pts.append(np.concatenate([np.full((len(iso), 1), 3), iso], axis=1))
+    C = np.unique(np.concatenate(pts).astype(np.int32), axis=0)
+    for log2s in (0, 1, 3):
+        t = 1 << log2s
+        Ct = C.copy()
+        Ct[:, 1:] = (Ct[:, 1:] // t) * t          # floor to the stride-t grid (borders stay in int16 range)
+        Ct = np.unique(Ct, axis=0)
+        keys, _ = _keys(Ct, dev)
+        Cg = ops.coords_from_keys(keys).cpu().numpy()
+        ref = S.kernel_map(Cg, Cg, S.region_offsets(3, t))
+        nbr_b = ops.kmap_k3_blocks(keys, log2s, ops.blockmap_build(keys, log2s)).cpu().numpy()
+        assert np.array_equal(nbr_b, ref), log2s
 
 
 def test_children_and_frame_offsets(frames, dev):
