@@ -52,15 +52,15 @@ SIGNATURES = {
     "pcc_hash_query": (INT, [P, I64, P, P, I64, P, P]),
     "pcc_kmap_k3": (INT, [P, I64, INT, P, P, I64, P, P]),
     "pcc_blockmap_build": (INT, [P, I64, INT, P, P, I64, P]),
-    "pcc_kmap_k3_blocks": (INT, [P, I64, INT, P, P, I64, P, P]),
-    "pcc_kmap_down2": (INT, [P, P, I64, INT, P, I64, P]),
+    "pcc_kmap_k3_blocks": (INT, [P, I64, INT, P, P, I64, P, I64, P]),
+    "pcc_kmap_down2": (INT, [P, P, I64, INT, P, I64, I64, P]),
     "pcc_frame_offsets": (INT, [P, I64, I32, P, P]),
     "pcc_lex_order_workspace_bytes": (I64, [I64]),
     "pcc_lex_order": (INT, [P, I64, P, P, I64, P]),
     "pcc_spconv_packed_weight_bytes": (I64, [INT, INT, INT]),
     "pcc_spconv_pack_weights": (INT, [P, INT, INT, INT, INT, P]),
-    "pcc_spconv_umma": (INT, [P, I64, INT, P, I64, INT, P, P, INT, P, I64, INT, P, P, I64, INT, P]),
-    "pcc_spconv_set_tuning": (INT, [INT, INT, INT]),
+    "pcc_spconv_umma": (INT, [P, I64, INT, P, I64, I64, INT, P, P, INT, P, I64, INT, P, P, I64, INT, P]),
+    "pcc_spconv_set_tuning": (INT, [INT, INT]),
     "pcc_spconv_simt": (INT, [P, I64, INT, P, I64, INT, P, P, INT, P, I64, INT, P, P, I64, P]),
     "pcc_rows_f32_to_bf16": (INT, [P, INT, P, I64, P, INT, P]),
     "pcc_rows_bf16_to_f32": (INT, [P, INT, I64, P, INT, P]),

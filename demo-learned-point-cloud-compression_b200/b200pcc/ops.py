@@ -205,21 +205,28 @@ def blockmap_build(keys: torch.Tensor, log2_stride: int):
     return tk, tv
 
 
+def _padded_map(kvol: int, n: int, device) -> torch.Tensor:
+    """[kvol, n] int32 view of a buffer whose row pitch is padded to the 128-row tile of the conv
+    kernel (its kernel-map loader then fetches a tile's rows with one bulk copy per offset)."""
+    ld = max((n + 127) // 128 * 128, 128)
+    return torch.empty((kvol, ld), dtype=torch.int32, device=device)[:, :n]
+
+
 def kmap_k3_blocks(keys: torch.Tensor, log2_stride: int, btable) -> torch.Tensor:
     tk, tv = btable
     n = keys.shape[0]
-    nbr = torch.empty((27, n), dtype=torch.int32, device=keys.device)
+    nbr = _padded_map(27, n, keys.device)
     with _prof("kmap_k3", n * (8 + 27 * 4)):   # key read once + 27 map entries written per output row
         check(lib.pcc_kmap_k3_blocks(_ptr(keys), n, log2_stride, _ptr(tk), _ptr(tv), tk.shape[0], _ptr(nbr),
-                                     _stream()))
+                                     nbr.stride(0), _stream()))
     return nbr
 
 
 def kmap_down2(child_keys: torch.Tensor, parent_row: torch.Tensor, log2_child_stride: int, n_parent: int):
     n = child_keys.shape[0]
-    nbr = torch.empty((8, n_parent), dtype=torch.int32, device=child_keys.device)
+    nbr = _padded_map(8, n_parent, child_keys.device)
     check(lib.pcc_kmap_down2(_ptr(child_keys), _ptr(parent_row), n, log2_child_stride, _ptr(nbr), n_parent,
-                             _stream()))
+                             nbr.stride(0), _stream()))
     return nbr
 
 
@@ -327,7 +334,12 @@ def spconv_umma(x: torch.Tensor, nbr: Optional[torch.Tensor], n_out: int, kvol: 
     nbytes = 2 * x.shape[0] * cin + n_out * (cw * ((2 if ob else 0) + (4 if of else 0)) + cout * (2 if rp else 0)) + \
         (4 * kvol * n_out if nbr is not None else 0) + 2 * kvol * cin * cout
     with _prof(f"spconv_umma_k{kvol}_c{cin}x{cout}", nbytes, 2 * kvol * n_out * cin * cout):
-        check(lib.pcc_spconv_umma(_ptr(x), x.shape[0], x.shape[1], _ptr(nbr), n_out, kvol, _ptr(w_packed),
+        nbr_ld = 0
+        if nbr is not None:
+            if nbr.stride(1) != 1 or nbr.dtype != torch.int32:
+                raise _lib.PccError("kernel map must be int32 [kvol, n] with unit column stride")
+            nbr_ld = nbr.stride(0)
+        check(lib.pcc_spconv_umma(_ptr(x), x.shape[0], x.shape[1], _ptr(nbr), nbr_ld, n_out, kvol, _ptr(w_packed),
                                   _ptr(bias), cout, rp, ldr, int(relu), ob, of, ldo, int(cstore), _stream()))
 
 
@@ -336,6 +348,8 @@ def spconv_simt(x: torch.Tensor, nbr: Optional[torch.Tensor], n_out: int, kvol: 
                 relu: bool = False, out_bf16: Optional[torch.Tensor] = None,
                 out_f32: Optional[torch.Tensor] = None) -> None:
     _need_cuda(x, torch.bfloat16)
+    if nbr is not None and not nbr.is_contiguous():
+        nbr = nbr.contiguous()          # this comparator kernel takes an unpadded [kvol, n_out] map
     ldo = (out_bf16 if out_bf16 is not None else out_f32).shape[1]
     ldr = residual.shape[1] if residual is not None else 0
     cin = x.shape[1]

@@ -116,11 +116,11 @@ __global__ void k_fill_i32(int32_t* __restrict__ p, int64_t n, int32_t v) {
 }
 
 __global__ void k_kmap_down2(const uint64_t* __restrict__ ckeys, const int32_t* __restrict__ parent,
-                             int64_t n_child, int shift, int32_t* __restrict__ nbr, int64_t n_parent) {
+                             int64_t n_child, int shift, int32_t* __restrict__ nbr, int64_t ld) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n_child) return;
   int j = (int)((ckeys[i] >> shift) & 7ull);
-  nbr[(int64_t)j * n_parent + parent[i]] = (int32_t)i;
+  nbr[(int64_t)j * ld + parent[i]] = (int32_t)i;
 }
 
 
@@ -201,7 +201,8 @@ __device__ __forceinline__ int morton2(int x, int y, int z) {
 
 __global__ void __launch_bounds__(256)
 k_kmap_k3_blocks(const uint64_t* __restrict__ keys, int64_t n, int l, const uint64_t* __restrict__ tk,
-                 const ulonglong2* __restrict__ tv, uint64_t cap_mask, int32_t* __restrict__ nbr) {
+                 const ulonglong2* __restrict__ tv, uint64_t cap_mask, int32_t* __restrict__ nbr,
+                 int64_t ld) {
   const int64_t o = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (o >= n) return;
   int b, x, y, z;
@@ -255,7 +256,7 @@ k_kmap_k3_blocks(const uint64_t* __restrict__ keys, int64_t n, int l, const uint
       const int idx = morton2(nx, ny, nz);
       if ((m >> idx) & 1ull) r = base + __popcll(m & ((1ull << idx) - 1ull));
     }
-    nbr[(int64_t)j * n + o] = r;
+    nbr[(int64_t)j * ld + o] = r;
   }
 }
 
@@ -305,17 +306,19 @@ int pcc_kmap_k3(const uint64_t* keys, int64_t n, int log2_stride, const uint64_t
 }
 
 int pcc_kmap_down2(const uint64_t* child_keys, const int32_t* parent_row, int64_t n_child,
-                   int log2_child_stride, int32_t* nbr, int64_t n_parent, pcc_stream_t s) {
+                   int log2_child_stride, int32_t* nbr, int64_t n_parent, int64_t nbr_ld,
+                   pcc_stream_t s) {
   PCC_CHECK_ARG(n_child >= 0 && n_parent >= 0 && log2_child_stride >= 0 && log2_child_stride <= 14);
+  PCC_CHECK_ARG(nbr_ld >= n_parent);
   if (n_parent == 0) return PCC_OK;
   PCC_CHECK_ARG(child_keys && parent_row && nbr);
   cudaStream_t st = as_stream(s);
-  int64_t tot = 8 * n_parent;
+  int64_t tot = 8 * nbr_ld;
   k_fill_i32<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(nbr, tot, -1);
   PCC_LAUNCHED();
   if (n_child == 0) return PCC_OK;
   k_kmap_down2<<<(unsigned)((n_child + 255) / 256), 256, 0, st>>>(
-      child_keys, parent_row, n_child, 3 * log2_child_stride, nbr, n_parent);
+      child_keys, parent_row, n_child, 3 * log2_child_stride, nbr, nbr_ld);
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -339,13 +342,15 @@ int pcc_blockmap_build(const uint64_t* keys, int64_t n, int log2_stride, uint64_
 }
 
 int pcc_kmap_k3_blocks(const uint64_t* keys, int64_t n, int log2_stride, const uint64_t* table_keys,
-                       const void* table_vals16, int64_t capacity, int32_t* nbr, pcc_stream_t s) {
-  PCC_CHECK_ARG(n >= 0 && log2_stride >= 0 && log2_stride <= 13);
+                       const void* table_vals16, int64_t capacity, int32_t* nbr, int64_t nbr_ld,
+                       pcc_stream_t s) {
+  PCC_CHECK_ARG(n >= 0 && log2_stride >= 0 && log2_stride <= 13 && nbr_ld >= n);
   PCC_CHECK_ARG(capacity >= 8 && (capacity & (capacity - 1)) == 0);
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(keys && table_keys && table_vals16 && nbr);
   k_kmap_k3_blocks<<<(unsigned)((n + 255) / 256), 256, 0, as_stream(s)>>>(
-      keys, n, log2_stride, table_keys, (const ulonglong2*)table_vals16, (uint64_t)capacity - 1, nbr);
+      keys, n, log2_stride, table_keys, (const ulonglong2*)table_vals16, (uint64_t)capacity - 1, nbr,
+      nbr_ld);
   PCC_LAUNCHED();
   return PCC_OK;
 }

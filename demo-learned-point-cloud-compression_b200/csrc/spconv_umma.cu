@@ -123,100 +123,96 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo, uint
 
 struct UmmaParams {
   const __nv_bfloat16* in;
-  const int32_t* nbr;  // [kvol][n_out] or null (kvol == 1: row o reads input row o)
+  const int32_t* nbr;  // [kvol][nbr_ld] or null (kvol == 1: row o reads input row o)
   const uint8_t* w;    // packed panels
   const float* bias;
   const __nv_bfloat16* residual;
   __nv_bfloat16* out_bf16;
   float* out_f32;
-  int64_t n_in, n_out, ldr, ldo;
+  int64_t n_in, n_out, ldr, ldo, nbr_ld;
   int cout, kvol, relu, cstore;
-  int stages, lag, wres, ntiles;
+  int wres, ntiles, nbr_bulk;
+  int lt;              // log2(T): tiles gathered / accumulated together per stage
+  int nrounds_total;   // ceil(ntiles / T)
+  int jc;              // kernel offsets per kernel-map unit (divides kvol)
   uint32_t tmem_cols, acc_cols;
 };
 
-constexpr int kEpiWarps = 4, kMmaWarp = 4, kProdWarp0 = 5;
-constexpr int kThreadsP = 32 * (kProdWarp0 + 4);  // 288
+constexpr int kMmaWarp = 4, kLoaderWarp = 5, kProdWarp0 = 6;
+constexpr int kNbrBufs = 3;   // kernel-map ring depth (units)
 
-template <bool CA>
-__device__ __forceinline__ void cp_async16x(uint32_t dst, const void* src, uint32_t src_bytes) {
-  if (CA)
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
-  else
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
-}
-__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_dyn(int n) {
-  switch (n) {
-    case 0: cp_async_wait<0>(); break;
-    case 1: cp_async_wait<1>(); break;
-    case 2: cp_async_wait<2>(); break;
-    case 3: cp_async_wait<3>(); break;
-    case 4: cp_async_wait<4>(); break;
-    case 5: cp_async_wait<5>(); break;
-    case 6: cp_async_wait<6>(); break;
-    case 7: cp_async_wait<7>(); break;
-    case 8: cp_async_wait<8>(); break;
-    case 9: cp_async_wait<9>(); break;
-    case 10: cp_async_wait<10>(); break;
-    case 11: cp_async_wait<11>(); break;
-    case 12: cp_async_wait<12>(); break;
-    case 13: cp_async_wait<13>(); break;
-    case 14: cp_async_wait<14>(); break;
-    default: cp_async_wait<15>(); break;
-  }
-}
-__device__ __forceinline__ void st_shared_u32(uint32_t addr, uint32_t v) {
-  asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+__device__ __forceinline__ void cp_async16_ca(uint32_t dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
 }
 __device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr) {
   uint32_t v;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
   return v;
 }
-__device__ __forceinline__ void producer_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
-// Persistent, warp-specialised: warps 0-3 epilogue (TMEM lane quarter = warp), warp 4 MMA issuer +
-// TMEM owner, warps 5-8 gather producers.  One CTA per SM walks tiles blockIdx.x, +gridDim.x, ...
-// Shared memory: [weights: all kvol panels (resident) | per stage][A stages][nbr 2 x kvol x 128]
-//                [stage meta][wmask 2x4][barriers].
-template <int CIN, bool CA>
-__global__ void __launch_bounds__(kThreadsP, 1)
+// Persistent (one CTA per SM), warp specialised.  A CTA works in rounds: round r of CTA b covers the
+// super-tile of T = 2^lt consecutive 128-row tiles starting at tile T*(b + r*gridDim.x).  One pipeline
+// stage = (round, kernel offset j): the gathered rows of all T tiles for that offset.  The T tiles
+// have their own TMEM accumulators and the MMAs of a stage are interleaved over them, because with
+// N = cout as small as 32 a chain of accumulating tcgen05.mma into ONE accumulator runs at the MMA
+// pipeline latency, not at its throughput; the per-stage hand-off cost is amortised over T tiles.
+//   warps 0-3   epilogue (TMEM lane quarter = warp): TMEM -> bias/residual/ReLU -> global, per round
+//   warp  4     MMA issuer + TMEM owner (2 x T accumulators: round r+1 accumulates while r drains)
+//   warp  5     kernel-map loader: units of jc offsets x T tiles, one 512-byte cp.async.bulk per
+//               (offset, tile) into a 3-deep ring; resident weight panels
+//   warps 6..   G gather groups of 4 warps.  Group i owns ring slot i and the stages g = i (mod G):
+//               wait slot free -> cp.async all T x 128 rows (zero fill for absent neighbours) into
+//               the no-swizzle K-major core-matrix layout -> wait landed -> proxy fence -> signal.
+//               While one group waits for its rows the other groups issue theirs.
+// All hand-offs are mbarriers: groups never wait for one another.
+// Shared memory: [weights: all kvol panels (resident) | one panel per slot][A: G slots x T tiles]
+//                [kernel-map ring 3 x jc x T x 128 x 4][barriers].
+template <int CIN, int G>
+__global__ void __launch_bounds__(32 * (kProdWarp0 + 4 * G), 1)
 k_spconv_umma(const UmmaParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   constexpr int CPR = CIN / 8;     // 16-byte chunks per row
   constexpr int RPI = 32 / CPR;    // rows covered by one warp-wide cp.async
-  constexpr uint32_t a_bytes = (uint32_t)kTileM * CIN * 2u;
-  constexpr uint32_t lbo_a = kTileM * 16u;  // one K-chunk plane: 128 rows x 16 B
+  // A tile layout (no-swizzle K-major core matrices of 8 rows x 16 B): chunk (row, kc) sits at
+  // (row >> 3) * sbo_a + kc * lbo_a + (row & 7) * 16.  lbo_a = 144 (not 128) rotates the banks by one
+  // 16-byte slot per K chunk, so the chunks of one gathered row -- which return from L1/L2 together,
+  // one sector or line at a time -- are written to shared memory without bank conflicts.
+  constexpr uint32_t lbo_a = 144u;
+  constexpr uint32_t sbo_a = (uint32_t)CPR * lbo_a;
+  constexpr uint32_t a_tile = (kTileM / 8) * sbo_a;
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
   const int lane = tid & 31;
-  const int cout = p.cout, kvol = p.kvol, S = p.stages, lag = p.lag;
+  const int cout = p.cout, kvol = p.kvol;
+  const int lt = p.lt, T = 1 << lt;
   const uint32_t b_bytes = (uint32_t)CIN * cout * 2u;
+  const uint32_t a_bytes = a_tile << lt;    // one stage: T tiles
   uint32_t base = smem_u32(smem_raw);
   base = (base + 127u) & ~127u;
   const uint32_t w0 = base;
-  const uint32_t w_total = p.wres ? (uint32_t)kvol * b_bytes : (uint32_t)S * b_bytes;
+  const uint32_t w_total = p.wres ? (uint32_t)kvol * b_bytes : (uint32_t)G * b_bytes;
   const uint32_t a0 = w0 + w_total;
-  const uint32_t nbr0 = a0 + (uint32_t)S * a_bytes;
-  const uint32_t nbr_buf_bytes = p.nbr ? (uint32_t)kvol * kTileM * 4u : 0u;
-  const uint32_t meta0 = nbr0 + 2u * nbr_buf_bytes;
-  const uint32_t wmask0 = meta0 + 4u * S;
-  const uint32_t bar0 = (wmask0 + 32u + 7u) & ~7u;
-  const uint32_t full0 = bar0, empty0 = bar0 + 8u * S, tfull0 = bar0 + 16u * S, tempty0 = tfull0 + 16u,
-                 wfull = tempty0 + 16u, tmem_slot = wfull + 8u;
+  const uint32_t nbr0 = a0 + (uint32_t)G * a_bytes;
+  const uint32_t unit_bytes = p.nbr ? (uint32_t)((p.jc << lt) * kTileM * 4) : 0u;
+  const uint32_t bar0 = (nbr0 + kNbrBufs * unit_bytes + 7u) & ~7u;
+  const uint32_t full0 = bar0, empty0 = bar0 + 8u * G, tfull0 = bar0 + 16u * G, tempty0 = tfull0 + 16u,
+                 wfull = tempty0 + 16u, nfull0 = wfull + 8u, nempty0 = nfull0 + 8u * kNbrBufs,
+                 tmem_slot = nempty0 + 8u * kNbrBufs;
+  const uint32_t nunits = (uint32_t)(kvol / p.jc);   // kernel-map units per round
 
   if (tid == 0) {
-    for (int s = 0; s < S; ++s) {
-      mbar_init(full0 + 8u * s, 128);
+    for (int s = 0; s < G; ++s) {
+      mbar_init(full0 + 8u * s, 4);
       mbar_init(empty0 + 8u * s, 1);
     }
-    mbar_init(tfull0, 1);
-    mbar_init(tfull0 + 8u, 1);
-    mbar_init(tempty0, 128);
-    mbar_init(tempty0 + 8u, 128);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(tfull0 + 8u * i, 1);
+      mbar_init(tempty0 + 8u * i, 4);
+    }
+    for (int i = 0; i < kNbrBufs; ++i) {
+      mbar_init(nfull0 + 8u * i, 1);
+      mbar_init(nempty0 + 8u * i, 4 * p.jc);   // every stage of the unit releases it once per warp
+    }
     mbar_init(wfull, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -227,97 +223,109 @@ k_spconv_umma(const UmmaParams p) {
   const uint32_t tmem_base = ld_shared_u32(tmem_slot);
 
   if (warp >= kProdWarp0) {
-    // ---------------- gather producers ----------------
-    const int pw = warp - kProdWarp0;
+    // ---------------- gather groups ----------------
+    const int gi = (warp - kProdWarp0) >> 2;   // group = ring slot
+    const int pw = (warp - kProdWarp0) & 3;    // row quarter inside a tile
     const int sub = lane % CPR, rl0 = lane / CPR;
-    if (p.wres && pw == 0 && lane == 0) {
-      mbar_arrive_expect_tx(wfull, w_total);
-      for (int j = 0; j < kvol; ++j) bulk_g2s(w0 + (uint32_t)j * b_bytes, p.w + (size_t)j * b_bytes, b_bytes, wfull);
+    const uint32_t n_in32 = (uint32_t)p.n_in;
+    const char* in_b = reinterpret_cast<const char*>(p.in) + sub * 16;
+    uint32_t dst_c[CPR];   // per-thread constant part of the destination address
+#pragma unroll
+    for (int it = 0; it < CPR; ++it) {
+      const int row = 32 * pw + it * RPI + rl0;
+      dst_c[it] = (uint32_t)sub * lbo_a + (uint32_t)(row >> 3) * sbo_a + (uint32_t)(row & 7) * 16u;
     }
-    auto prefetch_nbr = [&](int64_t tile, int buf) {
-      const int64_t o = tile * kTileM + 32 * pw + lane;
-      const uint32_t d0 = nbr0 + (uint32_t)buf * nbr_buf_bytes + (uint32_t)(32 * pw + lane) * 4u;
-      if (o < p.n_out) {
-        for (int j = 0; j < kvol; ++j) cp_async4(d0 + (uint32_t)j * (kTileM * 4u), p.nbr + (int64_t)j * p.n_out + o);
-      } else {
-        for (int j = 0; j < kvol; ++j) st_shared_u32(d0 + (uint32_t)j * (kTileM * 4u), 0xffffffffu);
-      }
-    };
-    uint32_t g = 0, s = 0, ph = 0;        // stage counter, ring slot, ring pass
-    uint32_t sig_s = 0;                   // ring slot of the next stage to signal
-    int prev_nst = 1 << 30;
-    if (p.nbr && (int64_t)blockIdx.x < p.ntiles) {
-      prefetch_nbr(blockIdx.x, 0);
-      cp_async_commit();
-      cp_async_wait<0>();
-      __syncwarp();
-    }
-    int ti = 0;
-    for (int64_t tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++ti) {
-      const int buf = ti & 1;
-      const int64_t row0 = tile * kTileM;
-      uint32_t mask = 1u;
-      const uint32_t nb_base = nbr0 + (uint32_t)buf * nbr_buf_bytes;
+    const uint32_t a_s = a0 + (uint32_t)gi * a_bytes;
+    const uint32_t fullb = full0 + 8u * gi, emptyb = empty0 + 8u * gi;
+    uint32_t use = 0;               // times this slot has been filled
+    uint32_t j = (uint32_t)gi;      // kernel offset of the next stage
+    uint32_t r = 0;                 // local round
+    int64_t rg = blockIdx.x;        // global round (super-tile index)
+    while (j >= (uint32_t)kvol) { j -= kvol; ++r; rg += gridDim.x; }
+    while (rg < p.nrounds_total) {
+      uint32_t nb_addr = 0, nb_bar = 0;
       if (p.nbr) {
-        if (ti > 0) {
-          if (prev_nst <= lag) cp_async_wait<0>();
-          __syncwarp();
-        }
-        uint32_t wm = 0;
-        for (int j = 0; j < kvol; ++j) {
-          const int v = (int)ld_shared_u32(nb_base + (uint32_t)(j * kTileM + 32 * pw + lane) * 4u);
-          if (__any_sync(0xffffffffu, v >= 0)) wm |= 1u << j;
-        }
-        if (lane == 0) st_shared_u32(wmask0 + (uint32_t)(buf * 4 + pw) * 4u, wm);
-        producer_bar();
-        mask = ld_shared_u32(wmask0 + (uint32_t)(buf * 4) * 4u) | ld_shared_u32(wmask0 + (uint32_t)(buf * 4 + 1) * 4u) |
-               ld_shared_u32(wmask0 + (uint32_t)(buf * 4 + 2) * 4u) | ld_shared_u32(wmask0 + (uint32_t)(buf * 4 + 3) * 4u);
-        if (mask == 0) mask = 1u;  // a tile always issues at least one (all-zero) stage
-        const int64_t next = tile + gridDim.x;
-        if (next < p.ntiles) prefetch_nbr(next, buf ^ 1);
+        const uint32_t c = j / (uint32_t)p.jc;
+        const uint32_t unit = r * nunits + c;
+        const uint32_t nbuf = unit % kNbrBufs;
+        mbar_wait(nfull0 + 8u * nbuf, (unit / kNbrBufs) & 1u);
+        nb_addr = nbr0 + nbuf * unit_bytes + (((j - c * p.jc) << lt) * kTileM) * 4u;
+        nb_bar = nempty0 + 8u * nbuf;
       }
-      const int first_j = __ffs(mask) - 1, last_j = 31 - __clz(mask);
-      for (uint32_t m = mask; m; m &= m - 1) {
-        const int j = __ffs(m) - 1;
-        if (ph > 0) mbar_wait(empty0 + 8u * s, (ph - 1) & 1u);
-        const uint32_t a_s = a0 + s * a_bytes;
-        if (pw == 0 && lane == 0) {
-          if (!p.wres) {
-            mbar_expect_tx(full0 + 8u * s, b_bytes);
-            bulk_g2s(w0 + s * b_bytes, p.w + (size_t)j * b_bytes, b_bytes, full0 + 8u * s);
-          }
-          st_shared_u32(meta0 + 4u * s, (uint32_t)j | (j == first_j ? 256u : 0u) | (j == last_j ? 512u : 0u));
-        }
+      if (use > 0) mbar_wait(emptyb, (use - 1) & 1u);
+      if (!p.wres && pw == 0 && lane == 0) {
+        mbar_expect_tx(fullb, b_bytes);
+        bulk_g2s(w0 + (uint32_t)gi * b_bytes, p.w + (size_t)j * b_bytes, b_bytes, fullb);
+      }
+      for (int t = 0; t < T; ++t) {
+        const int64_t tile = (rg << lt) + t;
+        const int64_t row0 = tile * kTileM;
+        const bool tile_ok = tile < p.ntiles;
 #pragma unroll
         for (int it = 0; it < CPR; ++it) {
           const int row = 32 * pw + it * RPI + rl0;
-          int64_t r;
-          if (p.nbr) r = (int)ld_shared_u32(nb_base + (uint32_t)(j * kTileM + row) * 4u);
-          else r = (row0 + row < p.n_out) ? row0 + row : -1;
-          const bool ok = r >= 0 && r < p.n_in;
-          const void* src = ok ? (const void*)(p.in + r * CIN + sub * 8) : (const void*)p.in;
-          const uint32_t dst = a_s + (uint32_t)sub * lbo_a + (uint32_t)(row >> 3) * 128u + (uint32_t)(row & 7) * 16u;
-          cp_async16x<CA>(dst, src, ok ? 16u : 0u);
+          uint32_t rr = 0xffffffffu;
+          if (tile_ok) {
+            if (p.nbr) rr = ld_shared_u32(nb_addr + (uint32_t)(t * kTileM + row) * 4u);
+            else if (row0 + row < p.n_out) rr = (uint32_t)(row0 + row);
+          }
+          const bool ok = rr < n_in32;
+          const char* src = in_b + (ok ? (size_t)rr * (CIN * 2) : (size_t)0);
+          cp_async16_ca(a_s + (uint32_t)t * a_tile + dst_c[it], src, ok ? 16u : 0u);
         }
-        cp_async_commit();
-        if (g >= (uint32_t)lag) {
-          cp_async_wait_dyn(lag);
-          fence_proxy_async();
-          mbar_arrive(full0 + 8u * sig_s);
-          if (++sig_s == (uint32_t)S) sig_s = 0;
-        }
-        ++g;
-        if (++s == (uint32_t)S) { s = 0; ++ph; }
       }
-      prev_nst = __popc(mask);
+      cp_async_commit();
+      if (p.nbr) {          // kernel-map reads of this stage are done
+        __syncwarp();
+        if (lane == 0) mbar_arrive(nb_bar);
+      }
+      cp_async_wait<0>();
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(fullb);
+      ++use;
+      j += G;
+      while (j >= (uint32_t)kvol) { j -= kvol; ++r; rg += gridDim.x; }
     }
-    // drain: everything landed, signal the stages not yet signalled
-    cp_async_wait<0>();
-    fence_proxy_async();
-    const uint32_t pending = g < (uint32_t)lag ? g : (uint32_t)lag;
-    for (uint32_t i = 0; i < pending; ++i) {
-      mbar_arrive(full0 + 8u * sig_s);
-      if (++sig_s == (uint32_t)S) sig_s = 0;
+  } else if (warp == kLoaderWarp) {
+    // ---------------- kernel-map loader + resident weights ----------------
+    if (lane == 0 && p.wres) {
+      mbar_arrive_expect_tx(wfull, w_total);
+      for (int j = 0; j < kvol; ++j) bulk_g2s(w0 + (uint32_t)j * b_bytes, p.w + (size_t)j * b_bytes, b_bytes, wfull);
+    }
+    if (p.nbr) {
+      uint32_t unit = 0;
+      const int jc = p.jc;
+      for (int64_t rg = blockIdx.x; rg < p.nrounds_total; rg += gridDim.x) {
+        int64_t tv = p.ntiles - (rg << lt);       // valid tiles in this round
+        if (tv > T) tv = T;
+        for (uint32_t c = 0; c < nunits; ++c, ++unit) {
+          const uint32_t nb = unit % kNbrBufs;
+          if (unit >= kNbrBufs) mbar_wait(nempty0 + 8u * nb, ((unit / kNbrBufs) - 1u) & 1u);
+          const uint32_t dst = nbr0 + nb * unit_bytes;
+          if (p.nbr_bulk) {
+            if (lane == 0) {
+              mbar_arrive_expect_tx(nfull0 + 8u * nb, (uint32_t)(jc * tv * kTileM * 4));
+              for (int jj = 0; jj < jc; ++jj)
+                for (int t = 0; t < (int)tv; ++t)
+                  bulk_g2s(dst + (uint32_t)(((jj << lt) + t) * kTileM * 4),
+                           p.nbr + (int64_t)(c * jc + jj) * p.nbr_ld + ((rg << lt) + t) * kTileM, kTileM * 4u,
+                           nfull0 + 8u * nb);
+            }
+          } else {
+            // arbitrary pitch / unpadded tail: guarded loads by the whole warp
+            for (int e = lane; e < jc * T * kTileM; e += 32) {
+              const int rr = e & (kTileM - 1), t = (e >> 7) & (T - 1), jj = e >> (7 + lt);
+              const int64_t o = (((rg << lt) + t) * kTileM) + rr;
+              const int32_t v = o < p.n_out ? __ldg(p.nbr + (int64_t)(c * jc + jj) * p.nbr_ld + o) : -1;
+              asm volatile("st.shared.b32 [%0], %1;" ::"r"(dst + (uint32_t)e * 4u), "r"(v) : "memory");
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(nfull0 + 8u * nb);
+          }
+          __syncwarp();
+        }
+      }
     }
   } else if (warp == kMmaWarp) {
     // ---------------- MMA issuer ----------------
@@ -328,103 +336,105 @@ k_spconv_umma(const UmmaParams p) {
     constexpr int ksteps = CIN >> 4;
     if (p.wres) mbar_wait(wfull, 0);
     uint32_t s = 0, ph = 0;
-    int ti = 0;
-    for (int64_t tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++ti) {
-      const uint32_t acc = (uint32_t)(ti & 1);
-      if (ti >= 2) mbar_wait(tempty0 + 8u * acc, (uint32_t)(((ti >> 1) - 1) & 1));
+    int r = 0;
+    for (int64_t rg = blockIdx.x; rg < p.nrounds_total; rg += gridDim.x, ++r) {
+      const uint32_t par = (uint32_t)(r & 1);
+      if (r >= 2) mbar_wait(tempty0 + 8u * par, (uint32_t)(((r >> 1) - 1) & 1));
       tc_fence_after();
-      const uint32_t tmem_d = tmem_base + acc * p.acc_cols;
-      bool last = false;
-      while (!last) {
+      const uint32_t tmem_d0 = tmem_base + (par << lt) * p.acc_cols;
+      for (int j = 0; j < kvol; ++j) {
         mbar_wait(full0 + 8u * s, ph & 1u);
         tc_fence_after();
-        const uint32_t meta = ld_shared_u32(meta0 + 4u * s);
-        const uint32_t j = meta & 0xffu;
-        const bool first = (meta & 256u) != 0;
-        last = (meta & 512u) != 0;
         if (lane == 0) {
           const uint32_t a_s = a0 + s * a_bytes;
-          const uint32_t b_s = p.wres ? w0 + j * b_bytes : w0 + s * b_bytes;
+          const uint32_t b_s = p.wres ? w0 + (uint32_t)j * b_bytes : w0 + s * b_bytes;
 #pragma unroll
           for (int ks = 0; ks < ksteps; ++ks) {
-            const uint64_t adesc = make_desc(a_s + (uint32_t)ks * 2u * lbo_a, lbo_a, 128u);
             const uint64_t bdesc = make_desc(b_s + (uint32_t)ks * 2u * lbo_b, lbo_b, 128u);
-            umma_bf16(tmem_d, adesc, bdesc, idesc, (first && ks == 0) ? 0u : 1u);
+            for (int t = 0; t < T; ++t) {
+              const uint64_t adesc = make_desc(a_s + (uint32_t)t * a_tile + (uint32_t)ks * 2u * lbo_a, lbo_a, sbo_a);
+              umma_bf16(tmem_d0 + (uint32_t)t * p.acc_cols, adesc, bdesc, idesc, (j == 0 && ks == 0) ? 0u : 1u);
+            }
           }
           umma_commit(empty0 + 8u * s);
-          if (last) umma_commit(tfull0 + 8u * acc);
+          if (j == kvol - 1) umma_commit(tfull0 + 8u * par);
         }
         __syncwarp();
-        if (++s == (uint32_t)S) { s = 0; ++ph; }
+        if (++s == (uint32_t)G) { s = 0; ++ph; }
       }
     }
   } else {
     // ---------------- epilogue (warps 0-3; TMEM lane = tile row) ----------------
-    int ti = 0;
+    int r = 0;
     const int cstore = p.cstore > 0 ? p.cstore : cout;
-    for (int64_t tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++ti) {
-      const uint32_t acc = (uint32_t)(ti & 1);
-      mbar_wait(tfull0 + 8u * acc, (uint32_t)((ti >> 1) & 1));
+    for (int64_t rg = blockIdx.x; rg < p.nrounds_total; rg += gridDim.x, ++r) {
+      const uint32_t par = (uint32_t)(r & 1);
+      mbar_wait(tfull0 + 8u * par, (uint32_t)((r >> 1) & 1));
       tc_fence_after();
-      const int64_t o = tile * kTileM + tid;
-      const bool rowok = o < p.n_out;
-      const uint32_t taddr = tmem_base + acc * p.acc_cols + ((uint32_t)(warp * 32) << 16);
-      for (int c0 = 0; c0 < cout; c0 += 16) {
-        uint32_t v[16];
-        tmem_ld16(taddr + (uint32_t)c0, v);
-        if (rowok && c0 < cstore) {
-          float f[16];
+      for (int t = 0; t < T; ++t) {
+        const int64_t tile = (rg << lt) + t;
+        if (tile >= p.ntiles) break;
+        const int64_t o = tile * kTileM + tid;
+        const bool rowok = o < p.n_out;
+        const uint32_t taddr = tmem_base + ((par << lt) + (uint32_t)t) * p.acc_cols + ((uint32_t)(warp * 32) << 16);
+        for (int c0 = 0; c0 < cout; c0 += 16) {
+          uint32_t v[16];
+          tmem_ld16(taddr + (uint32_t)c0, v);
+          if (rowok && c0 < cstore) {
+            float f[16];
 #pragma unroll
-          for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
-          if (p.bias) {
+            for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+            if (p.bias) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) f[i] += __ldg(p.bias + c0 + i);
-          }
-          if (p.residual) {
-            const uint4* rp = reinterpret_cast<const uint4*>(p.residual + o * p.ldr + c0);
-            uint4 r0 = __ldg(rp), r1 = __ldg(rp + 1);
-            uint32_t rw[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              f[2 * i] += __uint_as_float(rw[i] << 16);
-              f[2 * i + 1] += __uint_as_float(rw[i] & 0xffff0000u);
+              for (int i = 0; i < 16; ++i) f[i] += __ldg(p.bias + c0 + i);
             }
-          }
-          if (p.relu) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
-          }
-          if (cstore < cout) {
-            // narrow head: only the first cstore (< 16) columns exist in the output
-#pragma unroll
-            for (int i = 0; i < 15; ++i) {
-              if (i < cstore) {
-                if (p.out_f32) p.out_f32[o * p.ldo + i] = f[i];
-                if (p.out_bf16) p.out_bf16[o * p.ldo + i] = __float2bfloat16_rn(f[i]);
-              }
-            }
-          } else {
-            if (p.out_f32) {
-              float4* op = reinterpret_cast<float4*>(p.out_f32 + o * p.ldo + c0);
-#pragma unroll
-              for (int i = 0; i < 4; ++i) op[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
-            }
-            if (p.out_bf16) {
-              uint32_t pk[8];
+            if (p.residual) {
+              const uint4* rp = reinterpret_cast<const uint4*>(p.residual + o * p.ldr + c0);
+              uint4 r0 = __ldg(rp), r1 = __ldg(rp + 1);
+              uint32_t rw[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
 #pragma unroll
               for (int i = 0; i < 8; ++i) {
-                __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
-                pk[i] = *reinterpret_cast<uint32_t*>(&h);
+                f[2 * i] += __uint_as_float(rw[i] << 16);
+                f[2 * i + 1] += __uint_as_float(rw[i] & 0xffff0000u);
               }
-              uint4* op = reinterpret_cast<uint4*>(p.out_bf16 + o * p.ldo + c0);
-              op[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-              op[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+            }
+            if (p.relu) {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
+            }
+            if (cstore < cout) {
+              // narrow head: only the first cstore (< 16) columns exist in the output
+#pragma unroll
+              for (int i = 0; i < 15; ++i) {
+                if (i < cstore) {
+                  if (p.out_f32) p.out_f32[o * p.ldo + i] = f[i];
+                  if (p.out_bf16) p.out_bf16[o * p.ldo + i] = __float2bfloat16_rn(f[i]);
+                }
+              }
+            } else {
+              if (p.out_f32) {
+                float4* op = reinterpret_cast<float4*>(p.out_f32 + o * p.ldo + c0);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) op[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+              }
+              if (p.out_bf16) {
+                uint32_t pk[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                  __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+                  pk[i] = *reinterpret_cast<uint32_t*>(&h);
+                }
+                uint4* op = reinterpret_cast<uint4*>(p.out_bf16 + o * p.ldo + c0);
+                op[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                op[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+              }
             }
           }
         }
       }
       tc_fence_before();
-      mbar_arrive(tempty0 + 8u * acc);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty0 + 8u * par);
     }
   }
   tc_fence_before();
@@ -469,50 +479,46 @@ int pcc_spconv_pack_weights(const float* w, int kvol, int cin, int cout, int cin
 }
 
 extern "C++" {
-static int g_spconv_cg = -1;  // PCC_SPCONV_CG=1: gather with cp.async.cg (L2 only) instead of .ca
-static int g_max_stages = 16, g_lag_slack = 2;
+static int g_groups = 0, g_max_t = 4;  // g_groups 0 = by channel count
 
-template <int CIN>
-static int launch_umma(const UmmaParams& p, size_t smem, unsigned grid, cudaStream_t st) {
-  if (g_spconv_cg < 0) {
-    const char* e = getenv("PCC_SPCONV_CG");
-    g_spconv_cg = (e && e[0] == '1') ? 1 : 0;
+template <int CIN, int G>
+static int launch_umma_g(const UmmaParams& p, size_t smem, unsigned grid, cudaStream_t st) {
+  static bool configured = false;
+  if (!configured) {
+    PCC_CUDA(cudaFuncSetAttribute(k_spconv_umma<CIN, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
+    configured = true;
   }
-  static bool configured[2] = {false, false};
-  if (g_spconv_cg) {
-    if (!configured[0]) {
-      PCC_CUDA(cudaFuncSetAttribute(k_spconv_umma<CIN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
-      configured[0] = true;
-    }
-    k_spconv_umma<CIN, false><<<grid, kThreadsP, smem, st>>>(p);
-  } else {
-    if (!configured[1]) {
-      PCC_CUDA(cudaFuncSetAttribute(k_spconv_umma<CIN, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
-      configured[1] = true;
-    }
-    k_spconv_umma<CIN, true><<<grid, kThreadsP, smem, st>>>(p);
-  }
+  k_spconv_umma<CIN, G><<<grid, 32 * (kProdWarp0 + 4 * G), smem, st>>>(p);
   PCC_LAUNCHED();
   return PCC_OK;
 }
+template <int CIN>
+static int launch_umma(const UmmaParams& p, int groups, size_t smem, unsigned grid, cudaStream_t st) {
+  switch (groups) {
+    case 4: return launch_umma_g<CIN, 4>(p, smem, grid, st);
+    case 2: return launch_umma_g<CIN, 2>(p, smem, grid, st);
+    default: return launch_umma_g<CIN, 1>(p, smem, grid, st);
+  }
+}
 }  // extern "C++"
 
-int pcc_spconv_set_tuning(int max_stages, int lag_slack, int use_cg) {
-  PCC_CHECK_ARG(max_stages >= 1 && max_stages <= 16 && lag_slack >= 1 && lag_slack <= 8);
-  g_max_stages = max_stages;
-  g_lag_slack = lag_slack;
-  g_spconv_cg = use_cg ? 1 : 0;
+int pcc_spconv_set_tuning(int groups, int max_tiles) {
+  PCC_CHECK_ARG(max_tiles == 1 || max_tiles == 2 || max_tiles == 4 || max_tiles == 8);
+  g_max_t = max_tiles;
+  PCC_CHECK_ARG(groups == 0 || groups == 1 || groups == 2 || groups == 4);
+  g_groups = groups;
   return PCC_OK;
 }
 
-int pcc_spconv_umma(const void* in_bf16, int64_t n_in, int cin, const int32_t* nbr, int64_t n_out,
-                    int kvol, const void* w_packed, const float* bias, int cout,
+int pcc_spconv_umma(const void* in_bf16, int64_t n_in, int cin, const int32_t* nbr, int64_t nbr_ld,
+                    int64_t n_out, int kvol, const void* w_packed, const float* bias, int cout,
                     const void* residual_bf16, int64_t ldr, int relu, void* out_bf16,
                     float* out_f32, int64_t ldo, int cstore, pcc_stream_t s) {
-  PCC_CHECK_ARG(n_out >= 0 && n_in >= 0 && kvol >= 1 && kvol <= 32);
-  PCC_CHECK_ARG(cin == 16 || cin == 32 || cin == 64 || cin == 128 || cin == 256);
+  PCC_CHECK_ARG(n_out >= 0 && n_in >= 0 && n_in < (1ll << 31) && kvol >= 1 && kvol <= 32);
+  PCC_CHECK_ARG(cin == 16 || cin == 32 || cin == 64 || cin == 128);
   PCC_CHECK_ARG(cout >= 16 && cout % 16 == 0 && cout <= 256);
   PCC_CHECK_ARG(nbr || kvol == 1);
+  PCC_CHECK_ARG(!nbr || nbr_ld >= n_out);
   PCC_CHECK_ARG(out_bf16 || out_f32);
   PCC_CHECK_ARG(cstore >= 0 && cstore <= cout && (cstore == 0 || cstore == cout || cstore < 16));
   const int cs = (cstore > 0 && cstore < cout) ? cstore : cout;
@@ -528,6 +534,7 @@ int pcc_spconv_umma(const void* in_bf16, int64_t n_in, int cin, const int32_t* n
   UmmaParams p;
   p.in = (const __nv_bfloat16*)in_bf16;
   p.nbr = nbr;
+  p.nbr_ld = nbr_ld;
   p.w = (const uint8_t*)w_packed;
   p.bias = bias;
   p.residual = (const __nv_bfloat16*)residual_bf16;
@@ -541,44 +548,55 @@ int pcc_spconv_umma(const void* in_bf16, int64_t n_in, int cin, const int32_t* n
   p.kvol = kvol;
   p.relu = relu;
   p.cstore = cs;
-  // shared-memory plan: resident weights when all panels fit in 72 KB, else one panel per stage
-  const int64_t a_bytes = (int64_t)kTileM * cin * 2, b_bytes = (int64_t)cin * cout * 2;
-  const int64_t budget = 227 * 1024 - 1024;
-  const int64_t nbr_bytes = nbr ? 2ll * kvol * kTileM * 4 : 0;
-  p.wres = (kvol * b_bytes <= 72 * 1024) ? 1 : 0;
-  const int64_t fixed = (p.wres ? kvol * b_bytes : 0) + nbr_bytes + 512;
-  const int64_t stage_bytes = a_bytes + (p.wres ? 0 : b_bytes);
-  int stages = (int)((budget - fixed) / (stage_bytes + 20));
-  if (stages > g_max_stages) stages = g_max_stages;
-  if (stages < 1) {
-    set_error("pcc_spconv_umma: cin %d cout %d kvol %d does not fit shared memory", cin, cout, kvol);
-    return PCC_E_UNSUPPORTED;
-  }
-  p.stages = stages;
-  p.lag = stages <= 4 ? stages - 1 : stages - g_lag_slack;
-  if (p.lag > 15) p.lag = 15;
-  if (p.lag < 0) p.lag = 0;
-  p.acc_cols = (uint32_t)((cout + 31) / 32 * 32);
-  uint32_t cols = 32;
-  while (cols < 2 * p.acc_cols) cols <<= 1;
-  p.tmem_cols = cols;
   const int64_t ntiles = (n_out + kTileM - 1) / kTileM;
   p.ntiles = (int)ntiles;
-  const size_t smem = (size_t)(fixed + (int64_t)stages * (stage_bytes + 20) + 256);
+  p.nbr_bulk = (nbr && nbr_ld % 4 == 0 && nbr_ld >= ntiles * kTileM && ((uintptr_t)nbr % 16) == 0) ? 1 : 0;
   static int sms = 0;
   if (!sms) {
     int dev = 0;
     PCC_CUDA(cudaGetDevice(&dev));
     PCC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   }
-  const unsigned grid = (unsigned)(ntiles < sms ? ntiles : sms);
+  // gather groups (= ring slots) and T tiles per stage.  T is bounded by TMEM (2 x T accumulators of
+  // acc_cols columns in 512), by shared memory (G slots of T tiles), by the tuning cap and by the
+  // tile count (keep >= 2 rounds per SM so the persistent grid stays balanced).
+  int groups = g_groups ? g_groups : (cin <= 64 ? 4 : 2);
+  p.acc_cols = (uint32_t)((cout + 31) / 32 * 32);
+  const int64_t a_tile = (int64_t)(kTileM / 8) * (cin / 8) * 144, b_bytes = (int64_t)cin * cout * 2;
+  const int64_t budget = 227 * 1024 - 1024;
+  p.wres = (kvol * b_bytes <= 72 * 1024) ? 1 : 0;
+  p.jc = 1;
+  for (int d = 2; d <= 4; ++d)
+    if (kvol % d == 0) p.jc = d;
+  auto smem_need = [&](int G, int T) -> int64_t {
+    const int64_t w = p.wres ? kvol * b_bytes : G * b_bytes;
+    const int64_t nb = nbr ? (int64_t)kNbrBufs * p.jc * T * kTileM * 4 : 0;
+    return w + (int64_t)G * T * a_tile + nb + 1024;
+  };
+  while (groups > 1 && smem_need(groups, 1) > budget) groups >>= 1;
+  if (smem_need(groups, 1) > budget) {
+    set_error("pcc_spconv_umma: cin %d cout %d kvol %d does not fit shared memory", cin, cout, kvol);
+    return PCC_E_UNSUPPORTED;
+  }
+  int T = 1, lt = 0;
+  while (2 * T <= g_max_t && (uint32_t)(2 * (2 * T)) * p.acc_cols <= 512u && ntiles / (2 * T) >= 2 * sms &&
+         smem_need(groups, 2 * T) <= budget) {
+    T *= 2;
+    ++lt;
+  }
+  p.lt = lt;
+  p.nrounds_total = (int)((ntiles + T - 1) / T);
+  uint32_t cols = 32;
+  while (cols < 2u * T * p.acc_cols) cols <<= 1;
+  p.tmem_cols = cols;
+  const size_t smem = (size_t)smem_need(groups, T);
+  const unsigned grid = (unsigned)(p.nrounds_total < sms ? p.nrounds_total : sms);
   cudaStream_t st = as_stream(s);
   switch (cin) {
-    case 16: return launch_umma<16>(p, smem, grid, st);
-    case 32: return launch_umma<32>(p, smem, grid, st);
-    case 64: return launch_umma<64>(p, smem, grid, st);
-    case 128: return launch_umma<128>(p, smem, grid, st);
-    default: return launch_umma<256>(p, smem, grid, st);
+    case 16: return launch_umma<16>(p, groups, smem, grid, st);
+    case 32: return launch_umma<32>(p, groups, smem, grid, st);
+    case 64: return launch_umma<64>(p, groups, smem, grid, st);
+    default: return launch_umma<128>(p, groups, smem, grid, st);
   }
 }
 

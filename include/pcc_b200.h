@@ -85,7 +85,8 @@ int pcc_hash_build(const uint64_t* keys, int64_t n, uint64_t* table_keys, int32_
 int pcc_hash_query(const uint64_t* queries, int64_t nq, const uint64_t* table_keys,
                    const int32_t* table_vals, int64_t capacity, int32_t* rows, pcc_stream_t s);
 /* Kernel map of a k=3, stride-1 convolution on tensor stride 2^log2_stride:
- * nbr[j*n + o] = row of (o + d_j) or -1, j = (dx+1) + 3(dy+1) + 9(dz+1). */
+ * nbr[j*n + o] = row of (o + d_j) or -1, j = (dx+1) + 3(dy+1) + 9(dz+1).  Voxel-hash version
+ * (26 cooperative probes per row); kept as the independent comparator of pcc_kmap_k3_blocks. */
 int pcc_kmap_k3(const uint64_t* keys, int64_t n, int log2_stride, const uint64_t* table_keys,
                 const int32_t* table_vals, int64_t capacity, int32_t* nbr, pcc_stream_t s);
 /* Block table: the same open-addressing hash keyed on 4x4x4-voxel Morton blocks
@@ -97,10 +98,13 @@ int pcc_kmap_k3(const uint64_t* keys, int64_t n, int log2_stride, const uint64_t
 int pcc_blockmap_build(const uint64_t* keys, int64_t n, int log2_stride, uint64_t* table_keys,
                        void* table_vals16, int64_t capacity, pcc_stream_t s);
 int pcc_kmap_k3_blocks(const uint64_t* keys, int64_t n, int log2_stride, const uint64_t* table_keys,
-                       const void* table_vals16, int64_t capacity, int32_t* nbr, pcc_stream_t s);
-/* Kernel map of a k=2, stride-2 convolution: nbr[j*n_parent + p] = child row with octant j or -1. */
+                       const void* table_vals16, int64_t capacity, int32_t* nbr, int64_t nbr_ld,
+                       pcc_stream_t s);
+/* Kernel map of a k=2, stride-2 convolution: nbr[j*nbr_ld + p] = child row with octant j or -1
+ * (row pitch nbr_ld >= n_parent; see pcc_spconv_umma for why the pitch is padded). */
 int pcc_kmap_down2(const uint64_t* child_keys, const int32_t* parent_row, int64_t n_child,
-                   int log2_child_stride, int32_t* nbr, int64_t n_parent, pcc_stream_t s);
+                   int log2_child_stride, int32_t* nbr, int64_t n_parent, int64_t nbr_ld,
+                   pcc_stream_t s);
 /* Per-frame row ranges: offsets[b] = first row with batch index >= b, b = 0..num_frames. */
 int pcc_frame_offsets(const uint64_t* keys, int64_t n, int32_t num_frames, int32_t* offsets,
                       pcc_stream_t s);
@@ -128,16 +132,22 @@ int pcc_spconv_pack_weights(const float* w, int kvol, int cin, int cout, int cin
  * output pointer may be NULL.  cstore: 0 or cout = store all columns; 1..15 = narrow head
  * (occupancy logits C->1, colour head C->3: weights zero-padded to cout = 16, only the first
  * cstore columns are written, ldo >= cstore).
- * Kernel: persistent (one CTA per SM), warp specialised (4 gather warps, 1 MMA warp, 4 epilogue
- * warps), cp.async gather into a multi-stage ring, tcgen05.mma into double-buffered TMEM
- * accumulators; kernel offsets with no neighbour in a 128-row tile are skipped. */
-int pcc_spconv_umma(const void* in_bf16, int64_t n_in, int cin, const int32_t* nbr, int64_t n_out,
-                    int kvol, const void* w_packed, const float* bias, int cout,
+ * nbr is [kvol][nbr_ld] (row pitch nbr_ld >= n_out elements); with the pitch padded to a multiple
+ * of 128 (and of 4) each tile's map rows are fetched by one 512-byte cp.async.bulk per offset,
+ * entries at columns >= n_out are never used for stores and may hold anything.
+ * Kernel: persistent (one CTA per SM), warp specialised (4 epilogue warps, 1 MMA warp, 1 kernel-map
+ * loader warp, G groups of 4 gather warps each owning one ring slot); a stage is one kernel offset
+ * of a super-tile of T x 128 rows, gathered with cp.async; the MMAs of a stage are interleaved over
+ * the T tiles' TMEM accumulators (2 x T accumulators, double buffered against the epilogue); all
+ * hand-offs by mbarrier. */
+int pcc_spconv_umma(const void* in_bf16, int64_t n_in, int cin, const int32_t* nbr, int64_t nbr_ld,
+                    int64_t n_out, int kvol, const void* w_packed, const float* bias, int cout,
                     const void* residual_bf16, int64_t ldr, int relu, void* out_bf16,
                     float* out_f32, int64_t ldo, int cstore, pcc_stream_t s);
-/* Tuning knobs of pcc_spconv_umma (process wide; defaults 16, 2, 0): maximum ring depth, how many
- * stages the full-barrier signal trails the ring depth by, and cp.async.cg (L2 only) instead of .ca. */
-int pcc_spconv_set_tuning(int max_stages, int lag_slack, int use_cg);
+/* Tuning knobs of pcc_spconv_umma (process wide; defaults 0, 4): number of gather groups = ring
+ * slots (0 = chosen from the channel count, else 1, 2 or 4) and the maximum number T of 128-row
+ * tiles gathered per stage and accumulated concurrently (1, 2, 4 or 8). */
+int pcc_spconv_set_tuning(int groups, int max_tiles);
 /* CUDA-core sparse convolution: independent comparator of the tensor-core kernel in the tests
  * (any cin / cout); the product path only uses it for the 1->1 coordinate-only g_s.down_conv.  w is plain bf16 [kvol, cin, cout]. */
 int pcc_spconv_simt(const void* in_bf16, int64_t n_in, int cin, const int32_t* nbr, int64_t n_out,

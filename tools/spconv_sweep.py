@@ -43,9 +43,9 @@ def main():
         out = torch.empty(n, args.cout, dtype=torch.bfloat16, device=dev)
         alg = 2 * n * args.cin + 2 * n * args.cout + 4 * 27 * n
         print(f"{name}: n={n} pairs/row={pairs:.2f} algorithmic MB={alg / 1e6:.1f}")
-        for cg in ((0,) if args.one else (0, 1)):
-            for stages, slack in (((8, 2),) if args.one else ((4, 1), (8, 2), (12, 2), (16, 2), (16, 4), (16, 1))):
-                _lib.check(_lib.lib.pcc_spconv_set_tuning(stages, slack, cg))
+        for groups, mt in (((0, 4),) if args.one else ((1, 1), (2, 1), (4, 1), (4, 2), (4, 4), (2, 4), (2, 8), (1, 8))):
+            if True:
+                _lib.check(_lib.lib.pcc_spconv_set_tuning(groups, mt))
                 ts = []
                 for r in range(args.reps + 2):
                     flush.fill_(r)
@@ -56,7 +56,7 @@ def main():
                     e1.synchronize()
                     ts.append(e0.elapsed_time(e1))
                 t = float(np.median(ts[2:]))
-                print(f"  cg={cg} stages<={stages:2d} slack={slack}: {t * 1e3:8.1f} us  {alg / t / 1e6:8.1f} GB/s "
+                print(f"  groups={groups} T<={mt}: {t * 1e3:8.1f} us  {alg / t / 1e6:8.1f} GB/s "
                       f"{2 * pairs * n * args.cin * args.cout / t / 1e9:7.1f} TF/s(real pairs)")
         # kernel-map timings
         for r in range(3):
