@@ -52,6 +52,24 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   }
   __trap();
 }
+// Same, for waiters that are not on the critical path: the suspend-time hint keeps the polling
+// (one shared-memory wavefront per try) off the L1/shared data pipe the gather is bound by.
+__device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity) {
+  uint32_t ok = 0;
+  for (uint32_t spin = 0; spin < (1u << 22); ++spin) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity), "r"(2000u)
+        : "memory");
+    if (ok) return;
+  }
+  __trap();
+}
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes)
                : "memory");
@@ -141,8 +159,12 @@ struct UmmaParams {
 constexpr int kMmaWarp = 4, kLoaderWarp = 5, kProdWarp0 = 6;
 constexpr int kNbrBufs = 3;   // kernel-map ring depth (units)
 
-__device__ __forceinline__ void cp_async16_ca(uint32_t dst, const void* src, uint32_t src_bytes) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+template <bool CG>
+__device__ __forceinline__ void cp_async16_x(uint32_t dst, const void* src, uint32_t src_bytes) {
+  if (CG)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+  else
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
 }
 __device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr) {
   uint32_t v;
@@ -167,7 +189,7 @@ __device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr) {
 // All hand-offs are mbarriers: groups never wait for one another.
 // Shared memory: [weights: all kvol panels (resident) | one panel per slot][A: G slots x T tiles]
 //                [kernel-map ring 3 x jc x T x 128 x 4][barriers].
-template <int CIN, int G>
+template <int CIN, int G, bool CG>
 __global__ void __launch_bounds__(32 * (kProdWarp0 + 4 * G), 1)
 k_spconv_umma(const UmmaParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -229,14 +251,20 @@ k_spconv_umma(const UmmaParams p) {
     const int sub = lane % CPR, rl0 = lane / CPR;
     const uint32_t n_in32 = (uint32_t)p.n_in;
     const char* in_b = reinterpret_cast<const char*>(p.in) + sub * 16;
+    // lane -> (row group rg4 = lane / CPR, chunk sub): the thread copies chunk `sub` of the CPR
+    // consecutive rows 32*pw + rg4*CPR + it, so their CPR kernel-map entries are one vector load
     uint32_t dst_c[CPR];   // per-thread constant part of the destination address
 #pragma unroll
     for (int it = 0; it < CPR; ++it) {
-      const int row = 32 * pw + it * RPI + rl0;
+      const int row = 32 * pw + rl0 * CPR + it;
       dst_c[it] = (uint32_t)sub * lbo_a + (uint32_t)(row >> 3) * sbo_a + (uint32_t)(row & 7) * 16u;
     }
+    const int rowb = 32 * pw + rl0 * CPR;   // first of this thread's rows
     const uint32_t a_s = a0 + (uint32_t)gi * a_bytes;
     const uint32_t fullb = full0 + 8u * gi, emptyb = empty0 + 8u * gi;
+    // chunks this thread wrote non-zero data to at the previous use of its slot (bit t*CPR + it).
+    // A chunk that was zero and stays zero needs no copy at all; all ones forces the first fill.
+    uint64_t dirty = ~0ull;
     uint32_t use = 0;               // times this slot has been filled
     uint32_t j = (uint32_t)gi;      // kernel offset of the next stage
     uint32_t r = 0;                 // local round
@@ -257,23 +285,45 @@ k_spconv_umma(const UmmaParams p) {
         mbar_expect_tx(fullb, b_bytes);
         bulk_g2s(w0 + (uint32_t)gi * b_bytes, p.w + (size_t)j * b_bytes, b_bytes, fullb);
       }
+      uint64_t now = 0;
       for (int t = 0; t < T; ++t) {
         const int64_t tile = (rg << lt) + t;
         const int64_t row0 = tile * kTileM;
         const bool tile_ok = tile < p.ntiles;
+        uint32_t rr[CPR];
+#pragma unroll
+        for (int it = 0; it < CPR; ++it) rr[it] = 0xffffffffu;
+        if (tile_ok) {
+          if (p.nbr) {
+            const uint32_t ia = nb_addr + (uint32_t)(t * kTileM + rowb) * 4u;
+            if (CPR >= 4) {
+#pragma unroll
+              for (int v4 = 0; v4 < CPR / 4; ++v4)
+                asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                             : "=r"(rr[4 * v4]), "=r"(rr[4 * v4 + 1]), "=r"(rr[4 * v4 + 2]), "=r"(rr[4 * v4 + 3])
+                             : "r"(ia + 16u * v4)
+                             : "memory");
+            } else {
+              asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(rr[0]), "=r"(rr[1]) : "r"(ia) : "memory");
+            }
+          } else {
+#pragma unroll
+            for (int it = 0; it < CPR; ++it)
+              if (row0 + rowb + it < p.n_out) rr[it] = (uint32_t)(row0 + rowb + it);
+          }
+        }
 #pragma unroll
         for (int it = 0; it < CPR; ++it) {
-          const int row = 32 * pw + it * RPI + rl0;
-          uint32_t rr = 0xffffffffu;
-          if (tile_ok) {
-            if (p.nbr) rr = ld_shared_u32(nb_addr + (uint32_t)(t * kTileM + row) * 4u);
-            else if (row0 + row < p.n_out) rr = (uint32_t)(row0 + row);
+          const bool ok = rr[it] < n_in32;
+          const uint64_t bit = 1ull << (t * CPR + it);
+          if (ok) now |= bit;
+          if (ok || (dirty & bit)) {
+            const char* src = in_b + (ok ? (size_t)rr[it] * (CIN * 2) : (size_t)0);
+            cp_async16_x<CG>(a_s + (uint32_t)t * a_tile + dst_c[it], src, ok ? 16u : 0u);
           }
-          const bool ok = rr < n_in32;
-          const char* src = in_b + (ok ? (size_t)rr * (CIN * 2) : (size_t)0);
-          cp_async16_ca(a_s + (uint32_t)t * a_tile + dst_c[it], src, ok ? 16u : 0u);
         }
       }
+      dirty = now;
       cp_async_commit();
       if (p.nbr) {          // kernel-map reads of this stage are done
         __syncwarp();
@@ -301,7 +351,7 @@ k_spconv_umma(const UmmaParams p) {
         if (tv > T) tv = T;
         for (uint32_t c = 0; c < nunits; ++c, ++unit) {
           const uint32_t nb = unit % kNbrBufs;
-          if (unit >= kNbrBufs) mbar_wait(nempty0 + 8u * nb, ((unit / kNbrBufs) - 1u) & 1u);
+          if (unit >= kNbrBufs) mbar_wait_relaxed(nempty0 + 8u * nb, ((unit / kNbrBufs) - 1u) & 1u);
           const uint32_t dst = nbr0 + nb * unit_bytes;
           if (p.nbr_bulk) {
             if (lane == 0) {
@@ -369,7 +419,7 @@ k_spconv_umma(const UmmaParams p) {
     const int cstore = p.cstore > 0 ? p.cstore : cout;
     for (int64_t rg = blockIdx.x; rg < p.nrounds_total; rg += gridDim.x, ++r) {
       const uint32_t par = (uint32_t)(r & 1);
-      mbar_wait(tfull0 + 8u * par, (uint32_t)((r >> 1) & 1));
+      mbar_wait_relaxed(tfull0 + 8u * par, (uint32_t)((r >> 1) & 1));
       tc_fence_after();
       for (int t = 0; t < T; ++t) {
         const int64_t tile = (rg << lt) + t;
@@ -479,18 +529,22 @@ int pcc_spconv_pack_weights(const float* w, int kvol, int cin, int cout, int cin
 }
 
 extern "C++" {
-static int g_groups = 0, g_max_t = 4;  // g_groups 0 = by channel count
+static int g_groups = 0, g_max_t = 4, g_cg = 0;  // g_groups 0 = by channel count
 
-template <int CIN, int G>
-static int launch_umma_g(const UmmaParams& p, size_t smem, unsigned grid, cudaStream_t st) {
+template <int CIN, int G, bool CG>
+static int launch_umma_gc(const UmmaParams& p, size_t smem, unsigned grid, cudaStream_t st) {
   static bool configured = false;
   if (!configured) {
-    PCC_CUDA(cudaFuncSetAttribute(k_spconv_umma<CIN, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
+    PCC_CUDA(cudaFuncSetAttribute(k_spconv_umma<CIN, G, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
     configured = true;
   }
-  k_spconv_umma<CIN, G><<<grid, 32 * (kProdWarp0 + 4 * G), smem, st>>>(p);
+  k_spconv_umma<CIN, G, CG><<<grid, 32 * (kProdWarp0 + 4 * G), smem, st>>>(p);
   PCC_LAUNCHED();
   return PCC_OK;
+}
+template <int CIN, int G>
+static int launch_umma_g(const UmmaParams& p, size_t smem, unsigned grid, cudaStream_t st) {
+  return g_cg ? launch_umma_gc<CIN, G, true>(p, smem, grid, st) : launch_umma_gc<CIN, G, false>(p, smem, grid, st);
 }
 template <int CIN>
 static int launch_umma(const UmmaParams& p, int groups, size_t smem, unsigned grid, cudaStream_t st) {
@@ -502,9 +556,10 @@ static int launch_umma(const UmmaParams& p, int groups, size_t smem, unsigned gr
 }
 }  // extern "C++"
 
-int pcc_spconv_set_tuning(int groups, int max_tiles) {
+int pcc_spconv_set_tuning(int groups, int max_tiles, int use_cg) {
   PCC_CHECK_ARG(max_tiles == 1 || max_tiles == 2 || max_tiles == 4 || max_tiles == 8);
   g_max_t = max_tiles;
+  g_cg = use_cg ? 1 : 0;
   PCC_CHECK_ARG(groups == 0 || groups == 1 || groups == 2 || groups == 4);
   g_groups = groups;
   return PCC_OK;
@@ -580,6 +635,7 @@ int pcc_spconv_umma(const void* in_bf16, int64_t n_in, int cin, const int32_t* n
   }
   int T = 1, lt = 0;
   while (2 * T <= g_max_t && (uint32_t)(2 * (2 * T)) * p.acc_cols <= 512u && ntiles / (2 * T) >= 2 * sms &&
+         2 * T * (cin / 8) <= 64 &&
          smem_need(groups, 2 * T) <= budget) {
     T *= 2;
     ++lt;

@@ -43,9 +43,10 @@ def main():
         out = torch.empty(n, args.cout, dtype=torch.bfloat16, device=dev)
         alg = 2 * n * args.cin + 2 * n * args.cout + 4 * 27 * n
         print(f"{name}: n={n} pairs/row={pairs:.2f} algorithmic MB={alg / 1e6:.1f}")
-        for groups, mt in (((0, 4),) if args.one else ((1, 1), (2, 1), (4, 1), (4, 2), (4, 4), (2, 4), (2, 8), (1, 8))):
+        for groups, mt, cg in (((0, 4, 0),) if args.one else
+                               ((4, 1, 0), (4, 2, 0), (4, 4, 0), (2, 4, 0), (2, 8, 0), (4, 2, 1), (4, 4, 1), (2, 8, 1))):
             if True:
-                _lib.check(_lib.lib.pcc_spconv_set_tuning(groups, mt))
+                _lib.check(_lib.lib.pcc_spconv_set_tuning(groups, mt, cg))
                 ts = []
                 for r in range(args.reps + 2):
                     flush.fill_(r)
@@ -56,7 +57,7 @@ def main():
                     e1.synchronize()
                     ts.append(e0.elapsed_time(e1))
                 t = float(np.median(ts[2:]))
-                print(f"  groups={groups} T<={mt}: {t * 1e3:8.1f} us  {alg / t / 1e6:8.1f} GB/s "
+                print(f"  groups={groups} T<={mt} cg={cg}: {t * 1e3:8.1f} us  {alg / t / 1e6:8.1f} GB/s "
                       f"{2 * pairs * n * args.cin * args.cout / t / 1e9:7.1f} TF/s(real pairs)")
         # kernel-map timings
         for r in range(3):
