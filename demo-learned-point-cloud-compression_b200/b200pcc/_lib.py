@@ -31,7 +31,7 @@ F32 = C.c_float
 
 
 class CdfTables(C.Structure):
-    _fields_ = [("cdf", P), ("cdf_off", P), ("cdf_size", P), ("offset", P), ("num_tables", I32)]
+    _fields_ = [("cdf", P), ("cdf_off", P), ("cdf_size", P), ("offset", P), ("lut", P), ("num_tables", I32)]
 
 
 # name -> (restype, argtypes); must list every symbol include/pcc_b200.h declares
@@ -77,6 +77,8 @@ SIGNATURES = {
     "pcc_pmf_to_quantized_cdf": (INT, [P, INT, INT, P]),
     "pcc_rans_max_bytes": (I64, [I64, I32]),
     "pcc_rans_workspace_bytes": (I64, [I64, I32]),
+    "pcc_rans_lut_entries": (I64, [I32]),
+    "pcc_rans_build_lut": (INT, [C.POINTER(CdfTables), P, P]),
     "pcc_rans_encode": (INT, [P, P, I64, I64, I32, C.POINTER(CdfTables), P, P, P, I64, P]),
     "pcc_rans_decode": (INT, [P, I64, I32, P, I64, I64, C.POINTER(CdfTables), P, P, P]),
 }

@@ -436,7 +436,13 @@ class DeviceCdfTables:
         self.cdf_size = torch.from_numpy(sizes).to(device)
         self.offset = torch.from_numpy(np.asarray(offsets, dtype=np.int32)).to(device)
         self.struct = CdfTables(self.cdf.data_ptr(), self.cdf_off.data_ptr(), self.cdf_size.data_ptr(),
-                                self.offset.data_ptr(), self.num_tables)
+                                self.offset.data_ptr(), None, self.num_tables)
+        # decode search windows (built on the device once per table set)
+        self.lut = torch.empty(lib.pcc_rans_lut_entries(self.num_tables), dtype=torch.int16, device=device)
+        with torch.cuda.device(device):
+            check(lib.pcc_rans_build_lut(C.byref(self.struct), self.lut.data_ptr(), _stream()))
+        self.struct = CdfTables(self.cdf.data_ptr(), self.cdf_off.data_ptr(), self.cdf_size.data_ptr(),
+                                self.offset.data_ptr(), self.lut.data_ptr(), self.num_tables)
 
 
 DEFAULT_SEG = 1 << 15

@@ -24,8 +24,21 @@ struct Tables {
   const int32_t* off;
   const int32_t* size;
   const int32_t* offset;
+  const uint16_t* lut;   // [T][kLutN + 1] or null
   int32_t T;
 };
+
+constexpr int kLutBits = 7, kLutN = 1 << kLutBits, kLutShift = 16 - kLutBits;
+
+// q = x / fr, rem = x % fr for x < fr * 2^16 (so q < 2^16): one float multiply gives q within +-1
+// (relative error 2^-22 on a quotient below 2^16), one correction step makes it exact.
+__device__ __forceinline__ void divmod_small_q(uint32_t x, uint32_t fr, uint32_t& q, uint32_t& rem) {
+  q = __float2uint_rz(__uint2float_rn(x) * __frcp_rn(__uint2float_rn(fr)));
+  int32_t r = (int32_t)(x - q * fr);
+  if (r < 0) { --q; r += (int32_t)fr; }
+  else if ((uint32_t)r >= fr) { ++q; r -= (int32_t)fr; }
+  rem = (uint32_t)r;
+}
 
 __host__ __device__ inline int64_t seg_cap_words(int32_t seg_size) { return 4ll * seg_size + 64; }
 
@@ -60,52 +73,117 @@ __device__ __forceinline__ SymOps make_ops(int32_t symbol, int32_t t, const Tabl
   return o;
 }
 
-__global__ void __launch_bounds__(32)
-k_rans_encode(const int32_t* __restrict__ sym, const uint16_t* __restrict__ idx, int64_t chan_len, int64_t n,
-              int32_t seg_size, Tables T, uint16_t* __restrict__ scratch, uint32_t* __restrict__ states,
-              int32_t* __restrict__ nwords) {
-  const int seg = blockIdx.x, lane = threadIdx.x;
+// Pass A (fully parallel): per symbol the packed (start | freq << 16) of its table entry, 0 for a
+// symbol outside the table support (escape; the coder then takes the multi-operation path).
+__global__ void __launch_bounds__(256)
+k_rans_prepare(const int32_t* __restrict__ sym, const uint16_t* __restrict__ idx, int64_t chan_len, int64_t n,
+               Tables T, uint32_t* __restrict__ packed) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int32_t t = idx ? (int32_t)idx[i] : (int32_t)(i / chan_len);
+  t = t < T.T ? t : T.T - 1;
+  const int32_t coff = T.off[t], maxv = T.size[t] - 2;
+  const int64_t v = (int64_t)sym[i] - (int64_t)T.offset[t];
+  uint32_t pk = 0;
+  if (v >= 0 && v < maxv) {
+    const uint32_t st = T.cdf[coff + v];
+    const uint32_t fr = T.cdf[coff + v + 1] - st;
+    pk = st | (fr << 16);
+  }
+  packed[i] = pk;
+}
+
+constexpr int kEncWarps = 4;      // segments per CTA
+constexpr int kChunk = 8;         // rounds whose inputs are prefetched together
+constexpr uint32_t kInactive = 0xffffffffu;
+
+// Pass B: one warp per segment, rounds in reverse.  State update only; the table look-ups were done
+// in pass A and arrive through a double-buffered register prefetch.
+__global__ void __launch_bounds__(32 * kEncWarps)
+k_rans_encode(const int32_t* __restrict__ sym, const uint16_t* __restrict__ idx, const uint32_t* __restrict__ packed,
+              int64_t chan_len, int64_t n, int32_t seg_size, int32_t nseg, Tables T, uint16_t* __restrict__ scratch,
+              uint32_t* __restrict__ states, int32_t* __restrict__ nwords) {
+  const int seg = blockIdx.x * kEncWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (seg >= nseg) return;
   const unsigned lt = (1u << lane) - 1u;
   const int64_t start = (int64_t)seg * seg_size;
   const int32_t cnt = (int32_t)((n - start) < seg_size ? (n - start) : seg_size);
   const int32_t rounds = (cnt + 31) / 32;
   uint16_t* out = scratch + (int64_t)seg * seg_cap_words(seg_size);
+  const uint32_t* pk_seg = packed + start;
   uint32_t x = kRansL;
   int32_t wpos = 0;
-  for (int32_t r = rounds - 1; r >= 0; --r) {
-    const int32_t li = r * 32 + lane;
-    const bool active = li < cnt;
-    SymOps o;
-    o.nops = 0; o.coff = 0; o.v = 0; o.raw = 0; o.nnib = 0;
-    if (active) {
-      const int64_t i = start + li;
-      int32_t t = idx ? (int32_t)idx[i] : (int32_t)(i / chan_len);
-      t = t < T.T ? t : T.T - 1;
-      o = make_ops(sym[i], t, T);
+  uint32_t cur[kChunk], nxt[kChunk];
+  auto load_chunk = [&](int32_t rb, uint32_t (&buf)[kChunk]) {   // rounds rb-1 ... rb-kChunk
+#pragma unroll
+    for (int k = 0; k < kChunk; ++k) {
+      const int32_t r = rb - 1 - k;
+      const int32_t li = r * 32 + lane;
+      buf[k] = (r >= 0 && li < cnt) ? __ldg(pk_seg + li) : kInactive;
     }
-    const int maxops = __reduce_max_sync(0xffffffffu, o.nops);
-    for (int ts = maxops - 1; ts >= 0; --ts) {
-      const bool has = ts < o.nops;
-      uint32_t st = 0, fr = 1;
-      if (has) {
-        if (ts == 0) {
-          st = T.cdf[o.coff + o.v];
-          fr = T.cdf[o.coff + o.v + 1] - st;
-        } else {
-          uint32_t val = ts == 1 ? (uint32_t)o.nnib : ((o.raw >> (4 * (ts - 2))) & 15u);
-          st = val << 12;
-          fr = 1u << 12;
+  };
+  load_chunk(rounds, cur);
+  for (int32_t rb = rounds; rb > 0; rb -= kChunk) {
+    load_chunk(rb - kChunk, nxt);
+#pragma unroll
+    for (int k = 0; k < kChunk; ++k) {
+      const int32_t r = rb - 1 - k;
+      if (r < 0) break;
+      const uint32_t pk = cur[k];
+      const bool active = pk != kInactive;
+      const bool esc = active && pk == 0u;
+      if (!__any_sync(0xffffffffu, esc)) {
+        // ---- fast path: every lane has exactly one table operation
+        const uint32_t fr = active ? (pk >> 16) : 1u, st = pk & 0xffffu;
+        const bool emit = active && x >= (fr << 16);
+        const unsigned m = __ballot_sync(0xffffffffu, emit);
+        if (emit) {
+          out[wpos + __popc(m & lt)] = (uint16_t)(x & 0xffffu);
+          x >>= 16;
+        }
+        wpos += __popc(m);
+        if (active) {
+          uint32_t q, rem;
+          divmod_small_q(x, fr, q, rem);
+          x = (q << 16) + rem + st;
+        }
+      } else {
+        // ---- general path: lanes with an escape code a count nibble + payload nibbles first
+        SymOps o;
+        o.nops = 0; o.coff = 0; o.v = 0; o.raw = 0; o.nnib = 0;
+        if (active) {
+          const int64_t i = start + r * 32 + lane;
+          int32_t t = idx ? (int32_t)idx[i] : (int32_t)(i / chan_len);
+          t = t < T.T ? t : T.T - 1;
+          o = make_ops(sym[i], t, T);
+        }
+        const int maxops = __reduce_max_sync(0xffffffffu, o.nops);
+        for (int ts = maxops - 1; ts >= 0; --ts) {
+          const bool has = ts < o.nops;
+          uint32_t st = 0, fr = 1;
+          if (has) {
+            if (ts == 0) {
+              st = T.cdf[o.coff + o.v];
+              fr = T.cdf[o.coff + o.v + 1] - st;
+            } else {
+              uint32_t val = ts == 1 ? (uint32_t)o.nnib : ((o.raw >> (4 * (ts - 2))) & 15u);
+              st = val << 12;
+              fr = 1u << 12;
+            }
+          }
+          const bool emit = has && ((uint64_t)x >= ((uint64_t)fr << 16));
+          const unsigned m = __ballot_sync(0xffffffffu, emit);
+          if (emit) {
+            out[wpos + __popc(m & lt)] = (uint16_t)(x & 0xffffu);
+            x >>= 16;
+          }
+          wpos += __popc(m);
+          if (has) x = ((x / fr) << 16) + (x % fr) + st;
         }
       }
-      const bool emit = has && ((uint64_t)x >= ((uint64_t)fr << 16));
-      const unsigned m = __ballot_sync(0xffffffffu, emit);
-      if (emit) {
-        out[wpos + __popc(m & lt)] = (uint16_t)(x & 0xffffu);
-        x >>= 16;
-      }
-      wpos += __popc(m);
-      if (has) x = ((x / fr) << 16) + (x % fr) + st;
     }
+#pragma unroll
+    for (int k = 0; k < kChunk; ++k) cur[k] = nxt[k];
   }
   states[seg * 32 + lane] = x;
   if (lane == 0) nwords[seg] = wpos;
@@ -152,15 +230,39 @@ k_rans_pack(const uint16_t* __restrict__ scratch, const uint32_t* __restrict__ s
   if (tid == 0 && (nw & 1)) dw[nw] = 0;
 }
 
-__global__ void __launch_bounds__(32)
+// lut[t][b] = largest s in [0, maxv] with cdf_t[s] <= b << kLutShift (b = 0..kLutN-1), lut[t][kLutN] = maxv:
+// the symbol of cumulative frequency cf lies in [lut[t][cf >> kLutShift], lut[t][(cf >> kLutShift) + 1]].
+__global__ void k_rans_build_lut(Tables T, uint16_t* __restrict__ lut) {
+  const int t = blockIdx.x;
+  const int32_t coff = T.off[t], maxv = T.size[t] - 2;
+  for (int b = threadIdx.x; b <= kLutN; b += blockDim.x) {
+    int32_t lo = 0;
+    if (b == kLutN) {
+      lo = maxv;
+    } else {
+      const uint32_t target = (uint32_t)b << kLutShift;
+      int32_t hi = maxv + 1;
+      while (hi - lo > 1) {
+        const int32_t mid = (lo + hi) >> 1;
+        if (T.cdf[coff + mid] <= target) lo = mid; else hi = mid;
+      }
+    }
+    lut[(int64_t)t * (kLutN + 1) + b] = (uint16_t)lo;
+  }
+}
+
+constexpr int kDecWarps = 4;      // segments per CTA
+
+__global__ void __launch_bounds__(32 * kDecWarps)
 k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, int32_t seg_size_arg,
-              const uint16_t* __restrict__ idx, int64_t chan_len, int64_t n, Tables T,
+              const uint16_t* __restrict__ idx, int64_t chan_len, int64_t n, int32_t nseg_arg, Tables T,
               int32_t* __restrict__ sym, int32_t* __restrict__ status) {
-  const int seg = blockIdx.x, lane = threadIdx.x;
+  const int seg = blockIdx.x * kDecWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (seg >= nseg_arg) return;
   const unsigned lt = (1u << lane) - 1u;
   const uint32_t* h32 = reinterpret_cast<const uint32_t*>(container);
   const uint32_t seg_size = h32[2], nseg = h32[3];
-  if (h32[0] != kMagic || h32[1] != (uint32_t)n || seg_size != (uint32_t)seg_size_arg || nseg != gridDim.x) {
+  if (h32[0] != kMagic || h32[1] != (uint32_t)n || seg_size != (uint32_t)seg_size_arg || nseg != (uint32_t)nseg_arg) {
     if (lane == 0) atomicExch(status, 3);
     return;
   }
@@ -184,74 +286,101 @@ k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, in
   const int32_t cnt = (int32_t)((n - start) < (int64_t)seg_size ? (n - start) : (int64_t)seg_size);
   const int32_t rounds = (cnt + 31) / 32;
   bool bad = false;
-  for (int32_t r = 0; r < rounds; ++r) {
-    const int32_t li = r * 32 + lane;
-    const bool active = li < cnt;
-    const int64_t i = start + li;
-    int32_t coff = 0, maxv = 0, offs = 0;
-    if (active) {
-      int32_t t = idx ? (int32_t)idx[i] : (int32_t)(i / chan_len);
-      t = t < T.T ? t : T.T - 1;
-      coff = T.off[t];
-      maxv = T.size[t] - 2;
-      offs = T.offset[t];
-    }
-    // step 0: table symbol
-    int32_t v = 0;
-    {
-      uint32_t cf = x & 0xffffu;
-      if (active) {
-        int32_t lo = 0, hi = maxv + 1;  // cdf[coff + maxv + 1] == 65536 > cf
-        while (hi - lo > 1) {
-          int32_t mid = (lo + hi) >> 1;
-          if (T.cdf[coff + mid] <= cf) lo = mid; else hi = mid;
-        }
-        v = lo;
-        uint32_t st = T.cdf[coff + v];
-        uint32_t fr = T.cdf[coff + v + 1] - st;
-        x = fr * (x >> 16) + cf - st;
+  // table index of each round, prefetched kChunk rounds ahead (double buffered in registers)
+  int32_t cur[kChunk], nxt[kChunk];
+  auto load_chunk = [&](int32_t r0, int32_t (&buf)[kChunk]) {   // rounds r0 ... r0+kChunk-1
+#pragma unroll
+    for (int k = 0; k < kChunk; ++k) {
+      const int32_t li = (r0 + k) * 32 + lane;
+      int32_t t = -1;
+      if (r0 + k < rounds && li < cnt) {
+        const int64_t i = start + li;
+        t = idx ? (int32_t)__ldg(idx + i) : (int32_t)(i / chan_len);
+        t = t < T.T ? t : T.T - 1;
       }
-      const bool need = active && x < kRansL;
-      const unsigned m = __ballot_sync(0xffffffffu, need);
-      wpos -= __popc(m);
-      if (wpos < 0) { bad = true; wpos = 0; }
-      if (need) x = (x << 16) | (uint32_t)words[wpos + __popc(m & lt)];
+      buf[k] = t;
     }
-    const bool esc = active && v == maxv;
-    int nnib = 0;
-    uint32_t raw = 0;
-    if (__any_sync(0xffffffffu, esc)) {
-      int nops = esc ? 2 : 1;
-      for (int ts = 1;; ++ts) {
-        const bool has = ts < nops;
-        if (!__any_sync(0xffffffffu, has)) break;
-        if (has) {
-          uint32_t cf = x & 0xffffu;
-          uint32_t val = cf >> 12;
-          x = (x >> 16) * 4096u + (cf & 0xfffu);
-          if (ts == 1) {
-            nnib = (int)val;
-            if (nnib > 8) { nnib = 8; bad = true; }
-            nops = 2 + nnib;
-          } else {
-            raw |= val << (4 * (ts - 2));
+  };
+  load_chunk(0, cur);
+  for (int32_t r0 = 0; r0 < rounds; r0 += kChunk) {
+    load_chunk(r0 + kChunk, nxt);
+#pragma unroll
+    for (int k = 0; k < kChunk; ++k) {
+      const int32_t r = r0 + k;
+      if (r >= rounds) break;
+      const int32_t t = cur[k];
+      const bool active = t >= 0;
+      const int64_t i = start + r * 32 + lane;
+      int32_t coff = 0, maxv = 0, offs = 0;
+      if (active) {
+        coff = __ldg(T.off + t);
+        maxv = __ldg(T.size + t) - 2;
+        offs = __ldg(T.offset + t);
+      }
+      // step 0: table symbol
+      int32_t v = 0;
+      {
+        const uint32_t cf = x & 0xffffu;
+        if (active) {
+          int32_t lo = 0, hi = maxv + 1;  // cdf[coff + maxv + 1] == 65536 > cf
+          if (T.lut) {
+            const uint16_t* lp = T.lut + (int64_t)t * (kLutN + 1) + (cf >> kLutShift);
+            lo = (int32_t)__ldg(lp);
+            hi = (int32_t)__ldg(lp + 1) + 1;
           }
+          while (hi - lo > 1) {
+            const int32_t mid = (lo + hi) >> 1;
+            if (__ldg(T.cdf + coff + mid) <= cf) lo = mid; else hi = mid;
+          }
+          v = lo;
+          const uint32_t st = __ldg(T.cdf + coff + v);
+          const uint32_t fr = __ldg(T.cdf + coff + v + 1) - st;
+          x = fr * (x >> 16) + cf - st;
         }
-        const bool need = has && x < kRansL;
+        const bool need = active && x < kRansL;
         const unsigned m = __ballot_sync(0xffffffffu, need);
         wpos -= __popc(m);
         if (wpos < 0) { bad = true; wpos = 0; }
         if (need) x = (x << 16) | (uint32_t)words[wpos + __popc(m & lt)];
       }
-    }
-    if (active) {
-      int64_t val = v;
-      if (esc) {
-        val = (int64_t)(raw >> 1);
-        if (raw & 1u) val = -val - 1; else val += maxv;
+      const bool esc = active && v == maxv;
+      int nnib = 0;
+      uint32_t raw = 0;
+      if (__any_sync(0xffffffffu, esc)) {
+        int nops = esc ? 2 : 1;
+        for (int ts = 1;; ++ts) {
+          const bool has = ts < nops;
+          if (!__any_sync(0xffffffffu, has)) break;
+          if (has) {
+            uint32_t cf = x & 0xffffu;
+            uint32_t val = cf >> 12;
+            x = (x >> 16) * 4096u + (cf & 0xfffu);
+            if (ts == 1) {
+              nnib = (int)val;
+              if (nnib > 8) { nnib = 8; bad = true; }
+              nops = 2 + nnib;
+            } else {
+              raw |= val << (4 * (ts - 2));
+            }
+          }
+          const bool need = has && x < kRansL;
+          const unsigned m = __ballot_sync(0xffffffffu, need);
+          wpos -= __popc(m);
+          if (wpos < 0) { bad = true; wpos = 0; }
+          if (need) x = (x << 16) | (uint32_t)words[wpos + __popc(m & lt)];
+        }
       }
-      sym[i] = (int32_t)(val + offs);
+      if (active) {
+        int64_t val = v;
+        if (esc) {
+          val = (int64_t)(raw >> 1);
+          if (raw & 1u) val = -val - 1; else val += maxv;
+        }
+        sym[i] = (int32_t)(val + offs);
+      }
     }
+#pragma unroll
+    for (int k = 0; k < kChunk; ++k) cur[k] = nxt[k];
   }
   if (__any_sync(0xffffffffu, bad) && lane == 0) atomicExch(status, 2);
 }
@@ -272,7 +401,8 @@ int64_t pcc_rans_max_bytes(int64_t n, int32_t seg_size) {
 int64_t pcc_rans_workspace_bytes(int64_t n, int32_t seg_size) {
   if (n <= 0 || seg_size <= 0) return 256;
   int64_t ns = nseg_of(n, seg_size);
-  return align_up(ns * seg_cap_words(seg_size) * 2, 256) + align_up(ns * 128, 256) + align_up(ns * 4, 256) + 256;
+  return align_up(ns * seg_cap_words(seg_size) * 2, 256) + align_up(ns * 128, 256) + align_up(ns * 4, 256) +
+         align_up(n * 4, 256) + 256;
 }
 
 int pcc_rans_encode(const int32_t* sym, const uint16_t* idx, int64_t chan_len, int64_t n,
@@ -293,10 +423,15 @@ int pcc_rans_encode(const int32_t* sym, const uint16_t* idx, int64_t chan_len, i
   uint32_t* states = (uint32_t*)p;
   p += align_up((int64_t)ns * 128, 256);
   int32_t* nwords = (int32_t*)p;
-  Tables T{tables->cdf, tables->cdf_off, tables->cdf_size, tables->offset, tables->num_tables};
+  p += align_up((int64_t)ns * 4, 256);
+  uint32_t* packed = (uint32_t*)p;
+  Tables T{tables->cdf, tables->cdf_off, tables->cdf_size, tables->offset, tables->lut, tables->num_tables};
   cudaStream_t st = as_stream(s);
-  k_rans_encode<<<ns, 32, 0, st>>>(sym, idx, chan_len > 0 ? chan_len : 1, n, seg_size, T, scratch, states,
-                                   nwords);
+  const int64_t cl = chan_len > 0 ? chan_len : 1;
+  k_rans_prepare<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(sym, idx, cl, n, T, packed);
+  PCC_LAUNCHED();
+  k_rans_encode<<<(ns + kEncWarps - 1) / kEncWarps, 32 * kEncWarps, 0, st>>>(sym, idx, packed, cl, n, seg_size, ns, T,
+                                                                          scratch, states, nwords);
   PCC_LAUNCHED();
   k_rans_pack<<<ns, 256, 0, st>>>(scratch, states, nwords, ns, seg_size, (uint32_t)n, out, out_bytes_dev);
   PCC_LAUNCHED();
@@ -313,11 +448,22 @@ int pcc_rans_decode(const uint8_t* container, int64_t container_bytes, int32_t s
   PCC_CHECK_ARG(((uintptr_t)container % 4) == 0);
   const int32_t ns = nseg_of(n, seg_size);
   PCC_CHECK_ARG(container_bytes >= 16 + 4ll * ns);
-  Tables T{tables->cdf, tables->cdf_off, tables->cdf_size, tables->offset, tables->num_tables};
+  Tables T{tables->cdf, tables->cdf_off, tables->cdf_size, tables->offset, tables->lut, tables->num_tables};
   cudaStream_t st = as_stream(s);
   PCC_CUDA(cudaMemsetAsync(status_dev, 0, 4, st));
-  k_rans_decode<<<ns, 32, 0, st>>>(container, container_bytes, seg_size, idx, chan_len > 0 ? chan_len : 1, n,
-                                   T, sym, status_dev);
+  k_rans_decode<<<(ns + kDecWarps - 1) / kDecWarps, 32 * kDecWarps, 0, st>>>(
+      container, container_bytes, seg_size, idx, chan_len > 0 ? chan_len : 1, n, ns, T, sym, status_dev);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+
+int64_t pcc_rans_lut_entries(int32_t num_tables) { return (int64_t)num_tables * (kLutN + 1); }
+
+int pcc_rans_build_lut(const pcc_cdf_tables_t* tables, uint16_t* lut, pcc_stream_t s) {
+  PCC_CHECK_ARG(tables && lut && tables->num_tables > 0);
+  PCC_CHECK_ARG(tables->cdf && tables->cdf_off && tables->cdf_size && tables->offset);
+  Tables T{tables->cdf, tables->cdf_off, tables->cdf_size, tables->offset, nullptr, tables->num_tables};
+  k_rans_build_lut<<<tables->num_tables, 128, 0, as_stream(s)>>>(T, lut);
   PCC_LAUNCHED();
   return PCC_OK;
 }

@@ -222,8 +222,15 @@ typedef struct {
   const int32_t* cdf_off;   /* [T] start of table t in cdf */
   const int32_t* cdf_size;  /* [T] entries in table t (= pmf_length + 2) */
   const int32_t* offset;    /* [T] symbol offset of table t */
+  const uint16_t* lut;      /* [T][129] decode search windows from pcc_rans_build_lut, or NULL */
   int32_t num_tables;
 } pcc_cdf_tables_t;
+
+/* Decoder acceleration table: lut[t][b] = largest s with cdf_t[s] <= b << 9 (b = 0..127),
+ * lut[t][128] = last symbol; narrows the CDF search to a few entries.  pcc_rans_lut_entries()
+ * uint16 elements; build once per table set (model.update()). */
+int64_t pcc_rans_lut_entries(int32_t num_tables);
+int pcc_rans_build_lut(const pcc_cdf_tables_t* tables, uint16_t* lut, pcc_stream_t s);
 
 /* Upper bound on container bytes for n symbols. */
 int64_t pcc_rans_max_bytes(int64_t n, int32_t seg_size);

@@ -119,6 +119,14 @@ def test_rans_gaussian_bytes_match_oracle_and_roundtrip(model, dev, n, seg):
     dec, status = ops.rans_decode(cont, seg, ti, 1, n, gc.tables)
     assert int(status.item()) == 0
     assert np.array_equal(dec.cpu().numpy(), sym)
+    # same stream without the search-window table (plain binary search over the whole CDF row)
+    import copy
+    from b200pcc._lib import CdfTables
+    plain = copy.copy(gc.tables)
+    plain.struct = CdfTables(gc.tables.cdf.data_ptr(), gc.tables.cdf_off.data_ptr(), gc.tables.cdf_size.data_ptr(),
+                             gc.tables.offset.data_ptr(), None, gc.tables.num_tables)
+    dec2, status2 = ops.rans_decode(cont, seg, ti, 1, n, plain)
+    assert int(status2.item()) == 0 and torch.equal(dec2, dec)
     if n >= 200_000:
         # bit-rate: within 2 % of the CompressAI-style single 64-bit stream
         single = R.ref64_encode(sym, idx, _tables_ref(gc))
