@@ -31,7 +31,7 @@ F32 = C.c_float
 
 
 class CdfTables(C.Structure):
-    _fields_ = [("cdf", P), ("cdf_off", P), ("cdf_size", P), ("offset", P), ("lut", P), ("num_tables", I32)]
+    _fields_ = [("cdf", P), ("cdf_off", P), ("cdf_size", P), ("offset", P), ("lut", P), ("num_tables", I32), ("cdf_total", I32)]
 
 
 # name -> (restype, argtypes); must list every symbol include/pcc_b200.h declares

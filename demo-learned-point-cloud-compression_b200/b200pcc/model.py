@@ -310,7 +310,7 @@ class _CodedModel:
     """Shared by both entropy models: device CDF tables + PCL1 string coding."""
 
     tables: ops.DeviceCdfTables = None
-    seg_size = ops.DEFAULT_SEG
+    seg_size = None          # None: ops.auto_seg_size(n) per stream
 
     def _encode(self, sym_flat: torch.Tensor, idx_flat: Optional[torch.Tensor], chan_len: int) -> bytes:
         buf, nbytes = ops.rans_encode(sym_flat, idx_flat, chan_len, self.tables, self.seg_size)

@@ -436,23 +436,35 @@ class DeviceCdfTables:
         self.cdf_size = torch.from_numpy(sizes).to(device)
         self.offset = torch.from_numpy(np.asarray(offsets, dtype=np.int32)).to(device)
         self.struct = CdfTables(self.cdf.data_ptr(), self.cdf_off.data_ptr(), self.cdf_size.data_ptr(),
-                                self.offset.data_ptr(), None, self.num_tables)
+                                self.offset.data_ptr(), None, self.num_tables, int(flat.shape[0]))
         # decode search windows (built on the device once per table set)
         self.lut = torch.empty(lib.pcc_rans_lut_entries(self.num_tables), dtype=torch.int16, device=device)
         with torch.cuda.device(device):
             check(lib.pcc_rans_build_lut(C.byref(self.struct), self.lut.data_ptr(), _stream()))
         self.struct = CdfTables(self.cdf.data_ptr(), self.cdf_off.data_ptr(), self.cdf_size.data_ptr(),
-                                self.offset.data_ptr(), self.lut.data_ptr(), self.num_tables)
+                                self.offset.data_ptr(), self.lut.data_ptr(), self.num_tables, int(flat.shape[0]))
 
 
 DEFAULT_SEG = 1 << 15
 
 
+def auto_seg_size(n: int) -> int:
+    """Symbols per segment (= per warp).  The coder's run time is its critical path, seg_size / 32
+    dependent rounds, so streams are cut into >= ~64 segments; a segment costs 136 bytes of header
+    (32 lane states + counts), which bounds it below.  The value travels in the container header."""
+    seg = 4096
+    while seg < DEFAULT_SEG and seg * 64 < n:
+        seg *= 2
+    return seg
+
+
 def rans_encode(sym: torch.Tensor, idx: Optional[torch.Tensor], chan_len: int, tables: DeviceCdfTables,
-                seg_size: int = DEFAULT_SEG):
+                seg_size: Optional[int] = None):
     """sym: flat int32 device tensor.  Returns (device uint8 buffer, device int32 byte count)."""
     _need_cuda(sym, torch.int32)
     n = sym.numel()
+    if seg_size is None:
+        seg_size = auto_seg_size(n)
     dev = sym.device
     out = torch.empty(lib.pcc_rans_max_bytes(n, seg_size), dtype=torch.uint8, device=dev)
     nbytes = torch.empty(1, dtype=torch.int32, device=dev)

@@ -26,6 +26,7 @@ struct Tables {
   const int32_t* offset;
   const uint16_t* lut;   // [T][kLutN + 1] or null
   int32_t T;
+  int32_t total;         // cdf entries over all tables (0 = unknown)
 };
 
 constexpr int kLutBits = 7, kLutN = 1 << kLutBits, kLutShift = 16 - kLutBits;
@@ -33,10 +34,17 @@ constexpr int kLutBits = 7, kLutN = 1 << kLutBits, kLutShift = 16 - kLutBits;
 // q = x / fr, rem = x % fr for x < fr * 2^16 (so q < 2^16): one float multiply gives q within +-1
 // (relative error 2^-22 on a quotient below 2^16), one correction step makes it exact.
 __device__ __forceinline__ void divmod_small_q(uint32_t x, uint32_t fr, uint32_t& q, uint32_t& rem) {
-  q = __float2uint_rz(__uint2float_rn(x) * __frcp_rn(__uint2float_rn(fr)));
+  float rc;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(__uint2float_rn(fr)));
+  q = __float2uint_rz(__uint2float_rn(x) * rc);
   int32_t r = (int32_t)(x - q * fr);
-  if (r < 0) { --q; r += (int32_t)fr; }
-  else if ((uint32_t)r >= fr) { ++q; r -= (int32_t)fr; }
+  // branch-free correction by at most one in either direction
+  const int32_t neg = r >> 31;                 // -1 when the estimate was one too high
+  q += (uint32_t)neg;
+  r += neg & (int32_t)fr;
+  const uint32_t over = (uint32_t)r >= fr ? 1u : 0u;
+  q += over;
+  r -= (int32_t)(over * fr);
   rem = (uint32_t)r;
 }
 
@@ -73,36 +81,50 @@ __device__ __forceinline__ SymOps make_ops(int32_t symbol, int32_t t, const Tabl
   return o;
 }
 
-// Pass A (fully parallel): per symbol the packed (start | freq << 16) of its table entry, 0 for a
-// symbol outside the table support (escape; the coder then takes the multi-operation path).
+// Pass A (fully parallel): per symbol the packed (start | freq << 16) of the table entry it codes
+// with -- its own entry, or the table's last entry for a value outside the support (escape) -- the
+// escape payload raw[i] (0 when not an escape) and, per 32 symbols (= one coder round), the ballot of
+// escaping lanes.  The coder (pass B) then never touches the tables or the symbols.
 __global__ void __launch_bounds__(256)
 k_rans_prepare(const int32_t* __restrict__ sym, const uint16_t* __restrict__ idx, int64_t chan_len, int64_t n,
-               Tables T, uint32_t* __restrict__ packed) {
+               Tables T, uint32_t* __restrict__ packed, uint32_t* __restrict__ raw, uint32_t* __restrict__ escmask) {
   const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  int32_t t = idx ? (int32_t)idx[i] : (int32_t)(i / chan_len);
-  t = t < T.T ? t : T.T - 1;
-  const int32_t coff = T.off[t], maxv = T.size[t] - 2;
-  const int64_t v = (int64_t)sym[i] - (int64_t)T.offset[t];
-  uint32_t pk = 0;
-  if (v >= 0 && v < maxv) {
+  uint32_t pk = 0, rw = 0;
+  bool esc = false;
+  if (i < n) {
+    int32_t t = idx ? (int32_t)idx[i] : (int32_t)(i / chan_len);
+    t = t < T.T ? t : T.T - 1;
+    const int32_t coff = T.off[t], maxv = T.size[t] - 2;
+    int64_t v = (int64_t)sym[i] - (int64_t)T.offset[t];
+    if (v < 0) {
+      rw = (uint32_t)(-2 * v - 1);
+      v = maxv;
+      esc = true;
+    } else if (v >= maxv) {
+      rw = (uint32_t)(2 * (v - maxv));
+      v = maxv;
+      esc = true;
+    }
     const uint32_t st = T.cdf[coff + v];
     const uint32_t fr = T.cdf[coff + v + 1] - st;
     pk = st | (fr << 16);
+    packed[i] = pk;
+    raw[i] = rw;
   }
-  packed[i] = pk;
+  const unsigned m = __ballot_sync(0xffffffffu, esc);
+  if ((threadIdx.x & 31) == 0 && i < n) escmask[i >> 5] = m;
 }
 
 constexpr int kEncWarps = 4;      // segments per CTA
 constexpr int kChunk = 8;         // rounds whose inputs are prefetched together
 constexpr uint32_t kInactive = 0xffffffffu;
 
-// Pass B: one warp per segment, rounds in reverse.  State update only; the table look-ups were done
-// in pass A and arrive through a double-buffered register prefetch.
+// Pass B: one warp per segment, rounds in reverse.  State update only; pass A's per-symbol words
+// arrive through a double-buffered register prefetch (escape payloads only for escaping lanes).
 __global__ void __launch_bounds__(32 * kEncWarps)
-k_rans_encode(const int32_t* __restrict__ sym, const uint16_t* __restrict__ idx, const uint32_t* __restrict__ packed,
-              int64_t chan_len, int64_t n, int32_t seg_size, int32_t nseg, Tables T, uint16_t* __restrict__ scratch,
-              uint32_t* __restrict__ states, int32_t* __restrict__ nwords) {
+k_rans_encode(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ raw,
+              const uint32_t* __restrict__ escmask, int64_t n, int32_t seg_size, int32_t nseg,
+              uint16_t* __restrict__ scratch, uint32_t* __restrict__ states, int32_t* __restrict__ nwords) {
   const int seg = blockIdx.x * kEncWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (seg >= nseg) return;
   const unsigned lt = (1u << lane) - 1u;
@@ -111,29 +133,53 @@ k_rans_encode(const int32_t* __restrict__ sym, const uint16_t* __restrict__ idx,
   const int32_t rounds = (cnt + 31) / 32;
   uint16_t* out = scratch + (int64_t)seg * seg_cap_words(seg_size);
   const uint32_t* pk_seg = packed + start;
+  const uint32_t* raw_seg = raw + start;
+  const uint32_t* em_seg = escmask + (start >> 5);
   uint32_t x = kRansL;
   int32_t wpos = 0;
-  uint32_t cur[kChunk], nxt[kChunk];
-  auto load_chunk = [&](int32_t rb, uint32_t (&buf)[kChunk]) {   // rounds rb-1 ... rb-kChunk
+  uint32_t cur[kChunk], nxt[kChunk], cur_raw[kChunk], nxt_raw[kChunk], cur_em[kChunk], nxt_em[kChunk];
+  auto load_chunk = [&](int32_t rb, uint32_t (&buf)[kChunk], uint32_t (&braw)[kChunk], uint32_t (&bem)[kChunk]) {
 #pragma unroll
-    for (int k = 0; k < kChunk; ++k) {
+    for (int k = 0; k < kChunk; ++k) {   // rounds rb-1 ... rb-kChunk
       const int32_t r = rb - 1 - k;
       const int32_t li = r * 32 + lane;
+      bem[k] = r >= 0 ? __ldg(em_seg + r) : 0u;
       buf[k] = (r >= 0 && li < cnt) ? __ldg(pk_seg + li) : kInactive;
+      braw[k] = ((bem[k] >> lane) & 1u) ? __ldg(raw_seg + li) : 0u;
     }
   };
-  load_chunk(rounds, cur);
+  load_chunk(rounds, cur, cur_raw, cur_em);
   for (int32_t rb = rounds; rb > 0; rb -= kChunk) {
-    load_chunk(rb - kChunk, nxt);
+    load_chunk(rb - kChunk, nxt, nxt_raw, nxt_em);
 #pragma unroll
     for (int k = 0; k < kChunk; ++k) {
       const int32_t r = rb - 1 - k;
       if (r < 0) break;
       const uint32_t pk = cur[k];
       const bool active = pk != kInactive;
-      const bool esc = active && pk == 0u;
-      if (!__any_sync(0xffffffffu, esc)) {
-        // ---- fast path: every lane has exactly one table operation
+      if (cur_em[k] != 0u) {
+        // ---- a lane escapes: its payload goes first (reverse order): nibbles, then their count;
+        // flat 2^12 / 2^16 model, so the division is a shift
+        const bool esc = (cur_em[k] >> lane) & 1u;
+        const uint32_t rw = cur_raw[k];
+        const int nnib = (esc && rw) ? (35 - __clz(rw)) / 4 : 0;   // ceil(bits / 4)
+        const int nops = esc ? 1 + nnib : 0;                       // count nibble + payload nibbles
+        const int maxops = __reduce_max_sync(0xffffffffu, nops);
+        for (int ts = maxops; ts >= 1; --ts) {
+          const bool has = ts <= nops;
+          const uint32_t val = ts == 1 ? (uint32_t)nnib : ((rw >> (4 * (ts - 2))) & 15u);
+          const bool emit = has && x >= (1u << 28);
+          const unsigned m = __ballot_sync(0xffffffffu, emit);
+          if (emit) {
+            out[wpos + __popc(m & lt)] = (uint16_t)(x & 0xffffu);
+            x >>= 16;
+          }
+          wpos += __popc(m);
+          if (has) x = ((x >> 12) << 16) + (x & 4095u) + (val << 12);
+        }
+      }
+      {
+        // ---- table operation (own entry, or the escape entry) of every active lane
         const uint32_t fr = active ? (pk >> 16) : 1u, st = pk & 0xffffu;
         const bool emit = active && x >= (fr << 16);
         const unsigned m = __ballot_sync(0xffffffffu, emit);
@@ -147,43 +193,14 @@ k_rans_encode(const int32_t* __restrict__ sym, const uint16_t* __restrict__ idx,
           divmod_small_q(x, fr, q, rem);
           x = (q << 16) + rem + st;
         }
-      } else {
-        // ---- general path: lanes with an escape code a count nibble + payload nibbles first
-        SymOps o;
-        o.nops = 0; o.coff = 0; o.v = 0; o.raw = 0; o.nnib = 0;
-        if (active) {
-          const int64_t i = start + r * 32 + lane;
-          int32_t t = idx ? (int32_t)idx[i] : (int32_t)(i / chan_len);
-          t = t < T.T ? t : T.T - 1;
-          o = make_ops(sym[i], t, T);
-        }
-        const int maxops = __reduce_max_sync(0xffffffffu, o.nops);
-        for (int ts = maxops - 1; ts >= 0; --ts) {
-          const bool has = ts < o.nops;
-          uint32_t st = 0, fr = 1;
-          if (has) {
-            if (ts == 0) {
-              st = T.cdf[o.coff + o.v];
-              fr = T.cdf[o.coff + o.v + 1] - st;
-            } else {
-              uint32_t val = ts == 1 ? (uint32_t)o.nnib : ((o.raw >> (4 * (ts - 2))) & 15u);
-              st = val << 12;
-              fr = 1u << 12;
-            }
-          }
-          const bool emit = has && ((uint64_t)x >= ((uint64_t)fr << 16));
-          const unsigned m = __ballot_sync(0xffffffffu, emit);
-          if (emit) {
-            out[wpos + __popc(m & lt)] = (uint16_t)(x & 0xffffu);
-            x >>= 16;
-          }
-          wpos += __popc(m);
-          if (has) x = ((x / fr) << 16) + (x % fr) + st;
-        }
       }
     }
 #pragma unroll
-    for (int k = 0; k < kChunk; ++k) cur[k] = nxt[k];
+    for (int k = 0; k < kChunk; ++k) {
+      cur[k] = nxt[k];
+      cur_raw[k] = nxt_raw[k];
+      cur_em[k] = nxt_em[k];
+    }
   }
   states[seg * 32 + lane] = x;
   if (lane == 0) nwords[seg] = wpos;
@@ -252,11 +269,33 @@ __global__ void k_rans_build_lut(Tables T, uint16_t* __restrict__ lut) {
 }
 
 constexpr int kDecWarps = 4;      // segments per CTA
+constexpr int kWordCap = 8192;    // renormalisation words of a segment staged in shared memory (16 KB per warp)
 
+// SMEM: the CTA first copies the tables into shared memory (CDF entries as uint16 -- only the
+// terminating 65536 of a row does not fit and is implied --, per-table {offset, last symbol, symbol
+// offset} and the search windows), so the dependent look-ups of a round cost shared-memory latency.
+template <bool SMEM>
 __global__ void __launch_bounds__(32 * kDecWarps)
 k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, int32_t seg_size_arg,
               const uint16_t* __restrict__ idx, int64_t chan_len, int64_t n, int32_t nseg_arg, Tables T,
               int32_t* __restrict__ sym, int32_t* __restrict__ status) {
+  extern __shared__ __align__(16) uint8_t dec_smem[];
+  int4* s_meta = reinterpret_cast<int4*>(dec_smem);                                  // [T]
+  uint16_t* s_lut = reinterpret_cast<uint16_t*>(dec_smem + (size_t)T.T * 16);        // [T][kLutN+1]
+  uint16_t* s_cdf = s_lut + (((size_t)T.T * (kLutN + 1) + 7) & ~(size_t)7);          // [total]
+  // per-warp staging of the segment's word stream (after the tables, 16-byte aligned)
+  uint16_t* s_words = SMEM ? s_cdf + (((size_t)T.total + 7) & ~(size_t)7) : reinterpret_cast<uint16_t*>(dec_smem);
+  s_words += (size_t)(threadIdx.x >> 5) * kWordCap;
+  if (SMEM) {
+    for (int t = threadIdx.x; t < T.T; t += blockDim.x)
+      s_meta[t] = make_int4(T.off[t], T.size[t] - 2, T.offset[t], 0);
+    for (int i = threadIdx.x; i < T.T * (kLutN + 1); i += blockDim.x) s_lut[i] = T.lut[i];
+    for (int i = threadIdx.x; i < T.total; i += blockDim.x) s_cdf[i] = (uint16_t)T.cdf[i];
+    __syncthreads();
+  }
+  auto cdf_at = [&](int32_t coff, int32_t k) -> uint32_t {
+    return SMEM ? (uint32_t)s_cdf[coff + k] : __ldg(T.cdf + coff + k);
+  };
   const int seg = blockIdx.x * kDecWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (seg >= nseg_arg) return;
   const unsigned lt = (1u << lane) - 1u;
@@ -282,6 +321,14 @@ k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, in
   }
   uint32_t x = s32[1 + lane];
   const uint16_t* words = reinterpret_cast<const uint16_t*>(container + seg_off + 132);
+  if (wpos <= kWordCap) {
+    // stage the word stream in shared memory: the per-round word fetch is on the critical path
+    const uint32_t* w32 = reinterpret_cast<const uint32_t*>(words);   // seg_off + 132 is 4-byte aligned
+    uint32_t* sw32 = reinterpret_cast<uint32_t*>(s_words);
+    for (int i = lane; i < (wpos + 1) / 2; i += 32) sw32[i] = __ldg(w32 + i);
+    __syncwarp();
+    words = s_words;
+  }
   const int64_t start = (int64_t)seg * seg_size;
   const int32_t cnt = (int32_t)((n - start) < (int64_t)seg_size ? (n - start) : (int64_t)seg_size);
   const int32_t rounds = (cnt + 31) / 32;
@@ -313,9 +360,14 @@ k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, in
       const int64_t i = start + r * 32 + lane;
       int32_t coff = 0, maxv = 0, offs = 0;
       if (active) {
-        coff = __ldg(T.off + t);
-        maxv = __ldg(T.size + t) - 2;
-        offs = __ldg(T.offset + t);
+        if (SMEM) {
+          const int4 mt = s_meta[t];
+          coff = mt.x; maxv = mt.y; offs = mt.z;
+        } else {
+          coff = __ldg(T.off + t);
+          maxv = __ldg(T.size + t) - 2;
+          offs = __ldg(T.offset + t);
+        }
       }
       // step 0: table symbol
       int32_t v = 0;
@@ -323,18 +375,23 @@ k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, in
         const uint32_t cf = x & 0xffffu;
         if (active) {
           int32_t lo = 0, hi = maxv + 1;  // cdf[coff + maxv + 1] == 65536 > cf
-          if (T.lut) {
+          if (SMEM) {
+            const uint16_t* lp = s_lut + t * (kLutN + 1) + (cf >> kLutShift);
+            lo = (int32_t)lp[0];
+            hi = (int32_t)lp[1] + 1;
+          } else if (T.lut) {
             const uint16_t* lp = T.lut + (int64_t)t * (kLutN + 1) + (cf >> kLutShift);
             lo = (int32_t)__ldg(lp);
             hi = (int32_t)__ldg(lp + 1) + 1;
           }
           while (hi - lo > 1) {
             const int32_t mid = (lo + hi) >> 1;
-            if (__ldg(T.cdf + coff + mid) <= cf) lo = mid; else hi = mid;
+            if (cdf_at(coff, mid) <= cf) lo = mid; else hi = mid;
           }
           v = lo;
-          const uint32_t st = __ldg(T.cdf + coff + v);
-          const uint32_t fr = __ldg(T.cdf + coff + v + 1) - st;
+          const uint32_t st = cdf_at(coff, v);
+          const uint32_t nx = v == maxv ? 65536u : cdf_at(coff, v + 1);   // row terminator is implied
+          const uint32_t fr = nx - st;
           x = fr * (x >> 16) + cf - st;
         }
         const bool need = active && x < kRansL;
@@ -402,7 +459,7 @@ int64_t pcc_rans_workspace_bytes(int64_t n, int32_t seg_size) {
   if (n <= 0 || seg_size <= 0) return 256;
   int64_t ns = nseg_of(n, seg_size);
   return align_up(ns * seg_cap_words(seg_size) * 2, 256) + align_up(ns * 128, 256) + align_up(ns * 4, 256) +
-         align_up(n * 4, 256) + 256;
+         2 * align_up(n * 4, 256) + align_up((n + 31) / 32 * 4, 256) + 256;
 }
 
 int pcc_rans_encode(const int32_t* sym, const uint16_t* idx, int64_t chan_len, int64_t n,
@@ -425,12 +482,16 @@ int pcc_rans_encode(const int32_t* sym, const uint16_t* idx, int64_t chan_len, i
   int32_t* nwords = (int32_t*)p;
   p += align_up((int64_t)ns * 4, 256);
   uint32_t* packed = (uint32_t*)p;
-  Tables T{tables->cdf, tables->cdf_off, tables->cdf_size, tables->offset, tables->lut, tables->num_tables};
+  p += align_up(n * 4, 256);
+  uint32_t* raw = (uint32_t*)p;
+  p += align_up(n * 4, 256);
+  uint32_t* escmask = (uint32_t*)p;
+  Tables T{tables->cdf, tables->cdf_off, tables->cdf_size, tables->offset, tables->lut, tables->num_tables, tables->cdf_total};
   cudaStream_t st = as_stream(s);
   const int64_t cl = chan_len > 0 ? chan_len : 1;
-  k_rans_prepare<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(sym, idx, cl, n, T, packed);
+  k_rans_prepare<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(sym, idx, cl, n, T, packed, raw, escmask);
   PCC_LAUNCHED();
-  k_rans_encode<<<(ns + kEncWarps - 1) / kEncWarps, 32 * kEncWarps, 0, st>>>(sym, idx, packed, cl, n, seg_size, ns, T,
+  k_rans_encode<<<(ns + kEncWarps - 1) / kEncWarps, 32 * kEncWarps, 0, st>>>(packed, raw, escmask, n, seg_size, ns,
                                                                           scratch, states, nwords);
   PCC_LAUNCHED();
   k_rans_pack<<<ns, 256, 0, st>>>(scratch, states, nwords, ns, seg_size, (uint32_t)n, out, out_bytes_dev);
@@ -448,11 +509,26 @@ int pcc_rans_decode(const uint8_t* container, int64_t container_bytes, int32_t s
   PCC_CHECK_ARG(((uintptr_t)container % 4) == 0);
   const int32_t ns = nseg_of(n, seg_size);
   PCC_CHECK_ARG(container_bytes >= 16 + 4ll * ns);
-  Tables T{tables->cdf, tables->cdf_off, tables->cdf_size, tables->offset, tables->lut, tables->num_tables};
+  Tables T{tables->cdf, tables->cdf_off, tables->cdf_size, tables->offset, tables->lut, tables->num_tables, tables->cdf_total};
   cudaStream_t st = as_stream(s);
   PCC_CUDA(cudaMemsetAsync(status_dev, 0, 4, st));
-  k_rans_decode<<<(ns + kDecWarps - 1) / kDecWarps, 32 * kDecWarps, 0, st>>>(
-      container, container_bytes, seg_size, idx, chan_len > 0 ? chan_len : 1, n, ns, T, sym, status_dev);
+  const size_t wsm = (size_t)kDecWarps * kWordCap * 2;
+  const size_t smem = (size_t)T.T * 16 +
+                      ((((size_t)T.T * (kLutN + 1) + 7) & ~(size_t)7) + (((size_t)T.total + 7) & ~(size_t)7)) * 2 + wsm;
+  const unsigned grid = (unsigned)((ns + kDecWarps - 1) / kDecWarps);
+  static bool configured = false;
+  if (!configured) {
+    PCC_CUDA(cudaFuncSetAttribute(k_rans_decode<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+    PCC_CUDA(cudaFuncSetAttribute(k_rans_decode<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsm));
+    configured = true;
+  }
+  if (T.lut && T.total > 0 && smem <= 224 * 1024) {
+    k_rans_decode<true><<<grid, 32 * kDecWarps, smem, st>>>(container, container_bytes, seg_size, idx,
+                                                          chan_len > 0 ? chan_len : 1, n, ns, T, sym, status_dev);
+  } else {
+    k_rans_decode<false><<<grid, 32 * kDecWarps, wsm, st>>>(container, container_bytes, seg_size, idx,
+                                                        chan_len > 0 ? chan_len : 1, n, ns, T, sym, status_dev);
+  }
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -462,7 +538,7 @@ int64_t pcc_rans_lut_entries(int32_t num_tables) { return (int64_t)num_tables * 
 int pcc_rans_build_lut(const pcc_cdf_tables_t* tables, uint16_t* lut, pcc_stream_t s) {
   PCC_CHECK_ARG(tables && lut && tables->num_tables > 0);
   PCC_CHECK_ARG(tables->cdf && tables->cdf_off && tables->cdf_size && tables->offset);
-  Tables T{tables->cdf, tables->cdf_off, tables->cdf_size, tables->offset, nullptr, tables->num_tables};
+  Tables T{tables->cdf, tables->cdf_off, tables->cdf_size, tables->offset, nullptr, tables->num_tables, 0};
   k_rans_build_lut<<<tables->num_tables, 128, 0, as_stream(s)>>>(T, lut);
   PCC_LAUNCHED();
   return PCC_OK;

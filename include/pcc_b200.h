@@ -224,6 +224,8 @@ typedef struct {
   const int32_t* offset;    /* [T] symbol offset of table t */
   const uint16_t* lut;      /* [T][129] decode search windows from pcc_rans_build_lut, or NULL */
   int32_t num_tables;
+  int32_t cdf_total;        /* entries in cdf over all tables; 0 = unknown (decoder then reads the
+                               tables from global memory instead of staging them in shared memory) */
 } pcc_cdf_tables_t;
 
 /* Decoder acceleration table: lut[t][b] = largest s with cdf_t[s] <= b << 9 (b = 0..127),

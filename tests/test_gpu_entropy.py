@@ -124,7 +124,7 @@ def test_rans_gaussian_bytes_match_oracle_and_roundtrip(model, dev, n, seg):
     from b200pcc._lib import CdfTables
     plain = copy.copy(gc.tables)
     plain.struct = CdfTables(gc.tables.cdf.data_ptr(), gc.tables.cdf_off.data_ptr(), gc.tables.cdf_size.data_ptr(),
-                             gc.tables.offset.data_ptr(), None, gc.tables.num_tables)
+                             gc.tables.offset.data_ptr(), None, gc.tables.num_tables, 0)
     dec2, status2 = ops.rans_decode(cont, seg, ti, 1, n, plain)
     assert int(status2.item()) == 0 and torch.equal(dec2, dec)
     if n >= 200_000:
