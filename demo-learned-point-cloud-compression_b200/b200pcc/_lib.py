@@ -42,11 +42,14 @@ SIGNATURES = {
     "pcc_keys_from_coords_i32": (INT, [P, I64, P, P]),
     "pcc_keys_from_coords_f32": (INT, [P, I64, P, P]),
     "pcc_ingest_frame": (INT, [P, P, I64, I32, P, P, P]),
+    "pcc_unpack_output": (INT, [P, P, I64, P, P, P]),
     "pcc_coords_from_keys": (INT, [P, I64, P, P]),
     "pcc_sort_unique_workspace_bytes": (I64, [I64]),
     "pcc_sort_unique": (INT, [P, I64, P, P, P, P, I64, P]),
     "pcc_coords_downsample_workspace_bytes": (I64, [I64]),
     "pcc_coords_downsample": (INT, [P, I64, INT, P, P, P, P, I64, P]),
+    "pcc_coords_pyramid_workspace_bytes": (I64, [I64]),
+    "pcc_coords_pyramid": (INT, [P, I64, INT, INT, P, P, P, I32, P, P, I64, P]),
     "pcc_coords_children": (INT, [P, I64, INT, P, P]),
     "pcc_hash_build": (INT, [P, I64, P, P, I64, P]),
     "pcc_hash_query": (INT, [P, I64, P, P, I64, P, P]),

@@ -180,10 +180,12 @@ class AnalysisTransform(_Module):
         f = x.feats_bf16(self.stem.cin_pad)
         if num_frames is None:
             num_frames = int((cm.keys[-1:] >> 48).item()) + 1 if cm.n else 0
+        # all coarser coordinate maps (three for g_a, two more for h_a) and the per-frame counts of every
+        # level in one go: coordinates do not depend on features, so this costs one host sync in total
+        nlev = len(self.down)
+        offs_h = cm.build_pyramid(nlev + 2, num_frames)
         f = self.stem(f, cm.nbr3(), cm.n, relu=True)
-        offs = []
-        for i in range(len(self.down)):
-            offs.append(ops.frame_offsets(cm.keys, num_frames))
+        for i in range(nlev):
             coarse = cm.downsample()
             f = self.down[i](f, cm.nbr_down(), coarse.n, relu=True)
             cm.release_maps()
@@ -192,8 +194,10 @@ class AnalysisTransform(_Module):
             for b in range(0, len(blk), 2):
                 f = _resblock(blk[b], blk[b + 1], cm, f)
         yf = self.head(f, None, cm.n, out_f32=True)
-        offs_h = torch.stack(offs).cpu().numpy()  # one D2H for all three levels
-        counts = [list(map(int, np.diff(o))) for o in offs_h]
+        if offs_h is None:
+            counts = [[] for _ in range(nlev)]
+        else:
+            counts = [list(map(int, np.diff(offs_h[i]))) for i in range(nlev)]   # rows per frame at strides 1, 2, 4
         k = counts[::-1]
         y = SparseTensor(_cmap=cm, _feats=yf, _channels=self.cfg["c_y"])
         y.num_frames = num_frames
@@ -231,13 +235,17 @@ class SynthesisTransform(_Module):
 
     def __call__(self, y_hat: SparseTensor, k=None, return_intermediates=False):
         """g_s(y_hat, k=ks): three generative up-samplings, each followed by occupancy logits and the
-        per-frame top-k prune; colour head (codec_parallel.py:469)."""
+        per-frame top-k prune; colour head (codec_parallel.py:469).
+        When y_hat carries `frame_counts` (rows per frame, host list -- the decoder knows them from the
+        coordinate streams) every kept-row count follows from k on the host and no level syncs."""
         cm = y_hat.cmap
         num_frames = len(k[0])
         dev = cm.device
         f = y_hat.feats_bf16(self.pre.cin_pad)
         f = self.pre(f, None, cm.n, relu=True)
         inter = []
+        prev = getattr(y_hat, "frame_counts", None)
+        kd_all = torch.tensor([list(map(int, k[i])) for i in range(3)], dtype=torch.int32).to(dev, non_blocking=True)
         for i in range(3):
             f = self.up[i](f, relu=True)
             cm = cm.children()
@@ -246,8 +254,11 @@ class SynthesisTransform(_Module):
                 f = _resblock(blk[b], blk[b + 1], cm, f)
             logits = self.occ[i](f, cm.nbr3(), cm.n)
             off = ops.frame_offsets(cm.keys, num_frames)
-            kd = torch.tensor(list(k[i]), dtype=torch.int32, device=dev)
-            keep = ops.topk_select(logits.view(-1), cm.keys, off, kd, num_frames)
+            expect = None
+            if prev is not None:
+                kept = [max(0, min(int(k[i][b]), 8 * int(prev[b]))) for b in range(num_frames)]
+                expect, prev = sum(kept), kept
+            keep = ops.topk_select(logits.view(-1), cm.keys, off, kd_all[i], num_frames, expect=expect)
             if return_intermediates:
                 inter.append({"keys": cm.keys, "F": f, "logits": logits, "keep": keep})
             pruned = cm.subset(keep)
@@ -257,6 +268,7 @@ class SynthesisTransform(_Module):
         colors = self.color(f, cm.nbr3(), cm.n)
         out = SparseTensor(_cmap=cm, _feats=colors, _channels=3)
         out.num_frames = num_frames
+        out.frame_counts = prev
         if return_intermediates:
             return out, inter
         return out
@@ -312,10 +324,22 @@ class _CodedModel:
     tables: ops.DeviceCdfTables = None
     seg_size = None          # None: ops.auto_seg_size(n) per stream
 
+    def _encode_device(self, sym_flat: torch.Tensor, idx_flat: Optional[torch.Tensor], chan_len: int):
+        """-> (device byte buffer, device int32 size): no host sync; see fetch_strings()."""
+        return ops.rans_encode(sym_flat, idx_flat, chan_len, self.tables, self.seg_size)
+
     def _encode(self, sym_flat: torch.Tensor, idx_flat: Optional[torch.Tensor], chan_len: int) -> bytes:
-        buf, nbytes = ops.rans_encode(sym_flat, idx_flat, chan_len, self.tables, self.seg_size)
-        nb = int(nbytes.item())
-        return bytes(buf[:nb].cpu().numpy().tobytes())
+        return fetch_strings([self._encode_device(sym_flat, idx_flat, chan_len)])[0]
+
+    def _decode_device(self, cont: torch.Tensor, hdr, idx_flat: Optional[torch.Tensor], chan_len: int, n: int):
+        """cont: the container already on the device (uint8, 4-byte aligned, padded to 4); hdr: its
+        first 16 bytes on the host.  -> (symbols, status) without a host sync."""
+        if hdr is None or len(hdr) < 16:
+            raise ops._lib.PccError("rANS container too short")
+        h = np.frombuffer(bytes(hdr[:16]), dtype=np.uint32)
+        if h[0] != 0x314C4350 or int(h[1]) != n:
+            raise ops._lib.PccError("rANS container header mismatch")
+        return ops.rans_decode(cont, int(h[2]), idx_flat, chan_len, n, self.tables)
 
     def _decode(self, string: bytes, idx_flat: Optional[torch.Tensor], chan_len: int, n: int, device):
         if len(string) < 16:
@@ -331,6 +355,20 @@ class _CodedModel:
         cont = torch.from_numpy(arr.copy()).to(device)
         sym, status = ops.rans_decode(cont, seg_size, idx_flat, chan_len, n, self.tables)
         return sym, status
+
+
+def fetch_strings(pending) -> List[bytes]:
+    """[(device buffer, device size)] -> [bytes] with two host syncs for the whole list: one for the
+    sizes, one for the payloads (copied through a single packed device buffer)."""
+    if not pending:
+        return []
+    sizes = torch.cat([nb for _, nb in pending]).cpu().numpy()
+    packed = torch.cat([buf[: int(nb)] for (buf, _), nb in zip(pending, sizes)]).cpu().numpy()
+    out, pos = [], 0
+    for nb in sizes:
+        out.append(packed[pos:pos + int(nb)].tobytes())
+        pos += int(nb)
+    return out
 
 
 class EntropyBottleneck(_CodedModel):
@@ -400,6 +438,11 @@ class EntropyBottleneck(_CodedModel):
         sym, zb, _ = self.quantize_rows(z_rows, perm)
         n = z_rows.shape[0]
         return [self._encode(sym.view(-1), None, n)], zb
+
+    def compress_rows_device(self, z_rows: torch.Tensor, perm: torch.Tensor):
+        """Like compress_rows but the string stays on the device: -> ((buffer, size), z_hat bf16)."""
+        sym, zb, _ = self.quantize_rows(z_rows, perm)
+        return self._encode_device(sym.view(-1), None, z_rows.shape[0]), zb
 
     def decompress_rows(self, strings, n: int, perm: torch.Tensor):
         sym, status = self._decode(strings[0], None, n, n * self.channels, self.device)

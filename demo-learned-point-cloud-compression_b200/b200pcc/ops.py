@@ -54,8 +54,30 @@ class _prof:
         return False
 
 
+_STREAM_CACHE = None
+
+
 def _stream() -> int:
+    if _STREAM_CACHE is not None:
+        return _STREAM_CACHE
     return torch.cuda.current_stream().cuda_stream
+
+
+class stream_scope:
+    """Resolve the current CUDA stream once for a whole compress()/decompress() call (the per-launch
+    torch.cuda.current_stream() lookup is a measurable share of the host time at ~170 launches/frame).
+    The pipelines hold their lock while inside, so the cache is not shared between callers."""
+
+    def __enter__(self):
+        global _STREAM_CACHE
+        self.prev = _STREAM_CACHE
+        _STREAM_CACHE = torch.cuda.current_stream().cuda_stream
+        return self
+
+    def __exit__(self, *exc):
+        global _STREAM_CACHE
+        _STREAM_CACHE = self.prev
+        return False
 
 
 def _ptr(t: Optional[torch.Tensor]):
@@ -109,6 +131,19 @@ def ingest_frame(points_i16: torch.Tensor, colors_f64: torch.Tensor, batch: int,
                                _stream()))
 
 
+def unpack_output(keys: torch.Tensor, feats3: torch.Tensor):
+    """-> (points int32 [n,3], colours float32 [n,3] clipped like the reference's pack_batches)."""
+    _need_cuda(keys, torch.int64)
+    _need_cuda(feats3, torch.float32)
+    n = keys.shape[0]
+    if feats3.shape != (n, 3):
+        raise _lib.PccError(f"unpack_output: expected [{n}, 3] colours, got {tuple(feats3.shape)}")
+    pts = torch.empty((n, 3), dtype=torch.int32, device=keys.device)
+    col = torch.empty((n, 3), dtype=torch.float32, device=keys.device)
+    check(lib.pcc_unpack_output(_ptr(keys), _ptr(feats3), n, _ptr(pts), _ptr(col), _stream()))
+    return pts, col
+
+
 def coords_from_keys(keys: torch.Tensor) -> torch.Tensor:
     _need_cuda(keys, torch.int64)
     n = keys.shape[0]
@@ -117,8 +152,40 @@ def coords_from_keys(keys: torch.Tensor) -> torch.Tensor:
     return out
 
 
-def sort_unique(keys: torch.Tensor, want_src: bool = True):
-    """-> (unique sorted keys, src_row or None).  One host sync for the count."""
+# Deferred size checks.  A caller that already knows a data-dependent count (the decoder reads them
+# from the bitstream) passes it as `expect`: the op then returns without a host sync and files
+# (device count, expected value, message) here; the pipeline verifies all of them with one copy at the
+# end of the call (verify_deferred) and raises if any differs.
+_DEFERRED = []
+
+
+def _defer(cnt: torch.Tensor, expect: int, what: str):
+    _DEFERRED.append((cnt, int(expect), what))
+
+
+def verify_deferred(extra_status=()):
+    """One device->host copy for every deferred count and status word; raises PccError on mismatch."""
+    global _DEFERRED
+    items, _DEFERRED = _DEFERRED, []
+    tensors = [c.reshape(1).to(torch.int32) for c, _, _ in items] + [t.reshape(1).to(torch.int32) for t, _ in extra_status]
+    if not tensors:
+        return
+    host = torch.cat(tensors).cpu().numpy()
+    for (c, e, what), v in zip(items, host[:len(items)]):
+        if int(v) != e:
+            raise _lib.PccError(f"{what}: device count {int(v)} != expected {e}")
+    for (t, what), v in zip(extra_status, host[len(items):]):
+        if int(v) != 0:
+            raise _lib.PccError(f"{what} (status {int(v)})")
+
+
+def clear_deferred():
+    global _DEFERRED
+    _DEFERRED = []
+
+
+def sort_unique(keys: torch.Tensor, want_src: bool = True, expect: Optional[int] = None):
+    """-> (unique sorted keys, src_row or None).  One host sync for the count, none with `expect`."""
     _need_cuda(keys, torch.int64)
     n = keys.shape[0]
     dev = keys.device
@@ -129,7 +196,11 @@ def sort_unique(keys: torch.Tensor, want_src: bool = True):
     ws = workspace(wsb, dev)
     with _prof("sort_unique", n * (16 + 12 + (8 if want_src else 0))):
         check(lib.pcc_sort_unique(_ptr(keys), n, _ptr(out), _ptr(src), _ptr(cnt), _ptr(ws), ws.numel(), _stream()))
-    m = int(cnt.item())
+    if expect is not None:
+        m = int(expect)
+        _defer(cnt, m, "sort_unique")
+    else:
+        m = int(cnt.item())
     return out[:m], (src[:m] if want_src else None)
 
 
@@ -147,6 +218,47 @@ def coords_downsample(keys: torch.Tensor, log2_stride: int):
                                     ws.numel(), _stream()))
     m = int(cnt.item())
     return out[:m], parent
+
+
+def coords_pyramid_expect(keys: torch.Tensor, log2_stride: int, levels: int, expect_last: int):
+    """Decoder variant: only the last level is used and its size is known from the bitstream, so the
+    pyramid runs without any host sync; the device count is filed for verify_deferred()."""
+    _need_cuda(keys, torch.int64)
+    n = keys.shape[0]
+    dev = keys.device
+    kout = torch.empty((levels, max(n, 1)), dtype=torch.int64, device=dev)
+    par = torch.empty((levels, max(n, 1)), dtype=torch.int32, device=dev)
+    meta = torch.empty(levels, dtype=torch.int32, device=dev)
+    ws = workspace(lib.pcc_coords_pyramid_workspace_bytes(n), dev)
+    check(lib.pcc_coords_pyramid(_ptr(keys), n, log2_stride, levels, _ptr(kout), _ptr(par), _ptr(meta), 0, None,
+                                 _ptr(ws), ws.numel(), _stream()))
+    _defer(meta[levels - 1], expect_last, "coords_pyramid (last level size vs bitstream)")
+    return kout[levels - 1, :int(expect_last)]
+
+
+def coords_pyramid(keys: torch.Tensor, log2_stride: int, levels: int, num_frames: int):
+    """All `levels` stride-2 coarsenings of a sorted key set with ONE host sync.
+    -> (list of level keys, list of parent_row [rows of the finer level], host counts [levels],
+        host frame offsets [(levels+1), num_frames+1] (row 0 = the input set))."""
+    _need_cuda(keys, torch.int64)
+    n = keys.shape[0]
+    dev = keys.device
+    kout = torch.empty((levels, max(n, 1)), dtype=torch.int64, device=dev)
+    par = torch.empty((levels, max(n, 1)), dtype=torch.int32, device=dev)
+    nf1 = num_frames + 1
+    meta = torch.empty(levels + (levels + 1) * nf1, dtype=torch.int32, device=dev)
+    ws = workspace(lib.pcc_coords_pyramid_workspace_bytes(n), dev)
+    with _prof("coords_pyramid", levels * n * (8 + 4 + 8)):
+        check(lib.pcc_coords_pyramid(_ptr(keys), n, log2_stride, levels, _ptr(kout), _ptr(par), _ptr(meta),
+                                     num_frames, meta.data_ptr() + 4 * levels if num_frames else None, _ptr(ws),
+                                     ws.numel(), _stream()))
+    host = meta.cpu().numpy()                  # the one sync
+    counts = [int(c) for c in host[:levels]]
+    offs = host[levels:].reshape(levels + 1, nf1) if num_frames else None
+    keys_l = [kout[l, :counts[l]] for l in range(levels)]
+    n_fine = [n] + counts[:-1]
+    par_l = [par[l, :n_fine[l]] for l in range(levels)]
+    return keys_l, par_l, counts, offs
 
 
 def coords_children(keys: torch.Tensor, log2_stride_out: int) -> torch.Tensor:
@@ -285,8 +397,8 @@ def gather_keys(src: torch.Tensor, src_row: torch.Tensor) -> torch.Tensor:
 
 
 def topk_select(logits: torch.Tensor, keys: torch.Tensor, frame_off: torch.Tensor, k: torch.Tensor,
-                num_frames: int) -> torch.Tensor:
-    """-> kept rows (ascending).  One host sync for the count."""
+                num_frames: int, expect: Optional[int] = None) -> torch.Tensor:
+    """-> kept rows (ascending).  One host sync for the count, none with `expect`."""
     _need_cuda(logits, torch.float32)
     n = keys.shape[0]
     dev = keys.device
@@ -297,7 +409,11 @@ def topk_select(logits: torch.Tensor, keys: torch.Tensor, frame_off: torch.Tenso
     with _prof("topk_select", n * (4 + 8 + 4)):
         check(lib.pcc_topk_select(_ptr(logits), _ptr(keys), n, _ptr(frame_off), _ptr(k), num_frames, _ptr(keep),
                                   _ptr(cnt), _ptr(ws), ws.numel(), _stream()))
-    m = int(cnt.item())
+    if expect is not None:
+        m = int(expect)
+        _defer(cnt, m, "topk_select")
+    else:
+        m = int(cnt.item())
     return keep[:m]
 
 

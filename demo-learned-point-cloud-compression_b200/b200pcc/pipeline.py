@@ -103,6 +103,7 @@ class CompressionPipeline:
         self.compression_model = model if model is not None else _shared_model(self.device, config)
         self._lock = threading.Lock()
         self._stager = _Stager()
+        self._copy_stream = None
         self.h2d_bytes = 0
         self.d2h_bytes = 0
         self.keep_debug = False     # tests: keep stage tensors of the last call in self.debug
@@ -151,30 +152,49 @@ class CompressionPipeline:
         return self.compression_model.entropy_model.h_a(y)
 
     def factorized_model_step_batched(self, z):
+        """codec_pipeline.py:294-317.  The z string stays on the device until compress() collects all
+        strings at once; z_hat = round(z - median) + median is what re-decoding the string would give."""
         em = self.compression_model.entropy_model
         perm = z.cmap.lex_perm()
-        z_strings, zhat = em.entropy_bottleneck.compress_rows(z._feats, perm)
+        z_pending, zhat = em.entropy_bottleneck.compress_rows_device(z._feats, perm)
         z_hat = SparseTensor(_cmap=z.cmap, _feats=zhat, _channels=z._channels)
         if self.keep_debug:
             self.debug.update(z=z, z_hat=z_hat)
-        return z_hat, z_strings, [z.cmap.n]
+        return z_hat, [z_pending], [z.cmap.n]
 
     def hyper_synthesis_step(self, z_hat):
         return self.compression_model.entropy_model.h_s(z_hat)
 
-    def geometry_compression_step(self, y, num_frames):
+    def start_coordinate_copy(self, ycm):
+        """Device->host copy of the stride-8 latent coordinates on a side stream, issued as soon as the
+        coordinate pyramid exists, so the host-side coordinate coder overlaps the transforms."""
+        C = ycm.coords()
+        ev = torch.cuda.Event()
+        ev.record()
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        host = torch.empty(C.shape, dtype=C.dtype, pin_memory=True)
+        with torch.cuda.stream(self._copy_stream):
+            self._copy_stream.wait_event(ev)
+            host.copy_(C, non_blocking=True)
+            done = torch.cuda.Event()
+            done.record()
+        self.d2h_bytes += C.numel() * 4
+        return host, done, C
+
+    def geometry_compression_step(self, coords_copy, num_frames):
         """Per-frame coordinate streams for the stride-8 latent coordinates (replaces gpcc_encode,
         codec_pipeline.py:441-462)."""
-        C = y.C.cpu().numpy()
-        self.d2h_bytes += C.nbytes
-        streams = []
-        for b in range(num_frames):
-            streams.append(geometry.encode_points(C[C[:, 0] == b][:, 1:], 8))
-        return streams
+        host, done, _keepalive = coords_copy
+        done.synchronize()
+        C = host.numpy()
+        off = np.searchsorted(C[:, 0], np.arange(num_frames + 1))
+        return [geometry.encode_points(C[off[b]:off[b + 1], 1:], 8) for b in range(num_frames)]
 
     def gaussian_model_step_batched(self, y, settings, gaussian_params):
         """All qualities in one pass (codec_pipeline.py:397-437): gather h_s rows at the y
-        coordinates, gain, build_indexes, quantise, then one rANS container per quality."""
+        coordinates, gain, build_indexes, quantise, then one rANS container per quality (left on the
+        device; compress() fetches every string of the GOP with one size sync)."""
         em = self.compression_model.entropy_model
         gc = em.gaussian_conditional
         prow = ops.hash_query(y.cmap.keys, gaussian_params.cmap.table())
@@ -183,20 +203,14 @@ class CompressionPipeline:
         sym, idx = ops.gauss_encode(y._feats, gaussian_params._feats, prow, perm, scale, gc.table_d, gc.scale_bound)
         if self.keep_debug:
             self.debug.update(y=y, gaussian_params=gaussian_params, y_sym=sym, y_idx=idx, scale=scale)
-        strings = []
-        pending = []
-        for qi in range(len(settings)):
-            pending.append(ops.rans_encode(sym[qi].reshape(-1), idx[qi].reshape(-1), 1, gc.tables, gc.seg_size))
-        sizes = torch.cat([nb for _, nb in pending]).cpu().numpy()   # one sync for all qualities
-        for (buf, _), nb in zip(pending, sizes):
-            strings.append(buf[: int(nb)].cpu().numpy().tobytes())
-            self.d2h_bytes += int(nb)
-        return strings, [y.cmap.n]
+        pending = [gc._encode_device(sym[qi].reshape(-1), idx[qi].reshape(-1), 1) for qi in range(len(settings))]
+        return pending, [y.cmap.n]
 
     # ---- entry point -----------------------------------------------------------------------------------------
     def compress(self, data, staged=None):
         """gop dict -> (compressed_data {0: raw frames, i+1: bytes for settings[i]}, sideinfo)."""
-        with self._lock, torch.cuda.device(self.device):
+        from .model import fetch_strings
+        with self._lock, torch.cuda.device(self.device), ops.stream_scope():
             t_start = time.time()
             compressed_data = {0: data["frames"]}
             tm = _StageTimer()
@@ -204,33 +218,42 @@ class CompressionPipeline:
             x, sideinfo = self.unpack_batch(data, staged)
             num_points = x.cmap.n
             nf = x.num_frames
+            # every coarser coordinate map (g_a: 3, h_a: 2) with one host sync, then the latent
+            # coordinates start their trip to the host while the transforms run
+            x.cmap.build_pyramid(5, nf)
+            ycm = x.cmap.coarse.coarse.coarse
+            coords_copy = self.start_coordinate_copy(ycm)
             tm.mark("unpack")
             y, k = self.analysis_step(x)
             tm.mark("analysis")
             z = self.hyper_analysis_step(y)
             tm.mark("hyper_analysis")
-            z_hat, z_strings, z_shapes = self.factorized_model_step_batched(z)
+            z_hat, z_pending, z_shapes = self.factorized_model_step_batched(z)
             tm.mark("factorized_model")
             gaussian_params = self.hyper_synthesis_step(z_hat)
             tm.mark("hyper_synthesis")
-            points_streams = self.geometry_compression_step(y, nf)
-            tm.mark("geometry_compression")
-            y_strings, y_shapes = self.gaussian_model_step_batched(y, self.settings, gaussian_params)
+            y_pending, y_shapes = self.gaussian_model_step_batched(y, self.settings, gaussian_params)
             tm.mark("gaussian_model")
+            # host work that overlaps the GPU: coordinate streams
+            t_g0 = time.time()
+            points_streams = self.geometry_compression_step(coords_copy, nf)
+            t_geo = time.time() - t_g0
+            strings = fetch_strings(z_pending + y_pending)       # the GOP's two remaining syncs
+            z_strings, y_strings = strings[:1], strings[1:]
+            self.d2h_bytes += sum(len(b) for b in strings)
             t7 = []
             for i, q in enumerate(self.settings):
                 t0 = time.time()
                 compressed_data[i + 1] = container.make_bitstream_batched(
                     y_strings[i], z_strings[0], y_shapes[0], z_shapes[0], points_streams, k, q)
                 t7.append(time.time() - t0)
-            torch.cuda.synchronize()
             st = tm.resolve()
             sideinfo["enc_time_measurements"] = {
                 "analysis": st.get("analysis", 0.0) + st.get("unpack", 0.0),
                 "hyper_analysis": st.get("hyper_analysis", 0.0),
                 "factorized_model": st.get("factorized_model", 0.0),
                 "hyper_synthesis": st.get("hyper_synthesis", 0.0),
-                "geometry_compression": st.get("geometry_compression", 0.0),
+                "geometry_compression": t_geo,
                 "gaussian_model": st.get("gaussian_model", 0.0),
                 "bitstream_writing": t7,
             }
@@ -266,23 +289,37 @@ class DecompressionPipeline:
             out.append(np.concatenate([np.full((p.shape[0], 1), b, dtype=np.int32), p], axis=1))
         return np.concatenate(out, axis=0) if out else np.zeros((0, 4), np.int32)
 
-    def factorized_model_step_batched(self, z_strings, z_shape, y_points_dev, num_frames):
+    def stage_bitstream(self, y_points, y_strings, z_strings):
+        """One pinned staging copy for everything the decoder needs on the device: the decoded latent
+        coordinates and the two entropy-coded strings (padded to 4 bytes for the lane decoder)."""
+        def pad4(b):
+            a = np.frombuffer(b, dtype=np.uint8)
+            p = (-len(a)) % 4
+            return np.concatenate([a, np.zeros(p, np.uint8)]) if p else a
+        arrays = [y_points, pad4(y_strings[0]), pad4(z_strings[0])]
+        dev = self._stager.to_device(arrays, self.device)
+        self.h2d_bytes += sum(a.nbytes for a in arrays)
+        return dev
+
+    def factorized_model_step_batched(self, z_string_dev, z_hdr, z_shape, y_points_dev, num_frames):
         """Rebuild the stride-32 coordinates from the y coordinates and decode z_hat
-        (codec_parallel.py:291-318; g_s.down_conv is used for coordinates only)."""
+        (codec_parallel.py:291-318; g_s.down_conv is used for coordinates only).  No host sync: the
+        sizes come from the bitstream and are verified at the end of decompress()."""
         m = self.decompression_model
-        ykeys, _ = ops.sort_unique(ops.keys_from_coords(y_points_dev), want_src=False)
+        n_y = int(y_points_dev.shape[0])
+        ykeys, _ = ops.sort_unique(ops.keys_from_coords(y_points_dev), want_src=False, expect=n_y)
         ycm = CoordMap(ykeys, 3)
-        zcm = ycm.downsample().downsample()
-        if zcm.n != z_shape:
-            raise ValueError(f"bitstream z shape {z_shape} != coordinates {zcm.n}")
+        zkeys = ops.coords_pyramid_expect(ykeys, 3, 2, z_shape)
+        zcm = CoordMap(zkeys, 5)
         eb = m.entropy_model.entropy_bottleneck
-        zhat, status = eb.decompress_rows(z_strings, zcm.n, zcm.lex_perm())
+        sym, status = eb._decode_device(z_string_dev, z_hdr, None, zcm.n, zcm.n * eb.channels)
+        zhat, _ = ops.factorized_dequant(sym.view(eb.channels, zcm.n), zcm.lex_perm(), eb.medians_d)
         return ycm, SparseTensor(_cmap=zcm, _feats=zhat, _channels=eb.channels), status
 
     def hyper_synthesis_step(self, z_hat):
         return self.decompression_model.entropy_model.h_s(z_hat)
 
-    def gaussian_model_step_batched(self, y_strings, ycm, q, gaussian_params):
+    def gaussian_model_step_batched(self, y_string_dev, y_hdr, ycm, q, gaussian_params):
         """codec_parallel.py:382-419."""
         em = self.decompression_model.entropy_model
         gc = em.gaussian_conditional
@@ -291,7 +328,7 @@ class DecompressionPipeline:
         perm = ycm.lex_perm()
         scale = em.scale_for([list(q)], self.device)
         idx = ops.gauss_indexes(gaussian_params._feats, prow, perm, scale, gc.table_d, gc.scale_bound, ycm.n, cy)
-        sym, status = gc._decode(y_strings[0], idx.view(-1), 1, ycm.n * cy, self.device)
+        sym, status = gc._decode_device(y_string_dev, y_hdr, idx.view(-1), 1, ycm.n * cy)
         yb, _ = ops.gauss_dequant(sym.view(cy, ycm.n), gaussian_params._feats, prow, perm, scale[0].contiguous(),
                                   em.offset_gain_d, gc.scale_bound)
         y_hat = SparseTensor(_cmap=ycm, _feats=yb, _channels=cy)
@@ -304,24 +341,35 @@ class DecompressionPipeline:
         return self.decompression_model.g_s(y_hat, k=ks)
 
     def pack_batches(self, pointcloud, num_frames):
-        """codec_parallel.py:474-502: split per frame, NaN -> 0, clip colours to [0,1]."""
-        C = pointcloud.C.cpu().numpy()
-        F = pointcloud.F.cpu().numpy()
-        self.d2h_bytes += C.nbytes + F.nbytes
-        off = np.searchsorted(C[:, 0], np.arange(num_frames + 1))
-        batch = []
-        for i in range(num_frames):
-            pts = C[off[i]:off[i + 1], 1:]
-            col = np.nan_to_num(F[off[i]:off[i + 1]], nan=0.0)
-            col = np.clip(col * 255.0, 0, 255) / 255
-            batch.append({"points": pts, "colors": col})
-        return batch
+        """codec_parallel.py:474-502: split per frame, NaN -> 0, clip colours to [0,1].  The clip runs
+        on the device; points (int32 [N,3]) and colours (float32 [N,3]) land in pinned host memory that
+        the returned arrays own."""
+        n = pointcloud.cmap.n
+        pts_d, col_d = ops.unpack_output(pointcloud.cmap.keys, pointcloud._feats)
+        pts_h = torch.empty((n, 3), dtype=torch.int32, pin_memory=True)
+        col_h = torch.empty((n, 3), dtype=torch.float32, pin_memory=True)
+        pts_h.copy_(pts_d, non_blocking=True)
+        col_h.copy_(col_d, non_blocking=True)
+        counts = getattr(pointcloud, "frame_counts", None)
+        if counts is None:
+            off_d = ops.frame_offsets(pointcloud.cmap.keys, num_frames)
+            off = off_d.cpu().numpy()
+        else:
+            off = np.concatenate([[0], np.cumsum(counts)])
+        self.d2h_bytes += 24 * n
+        return pts_h, col_h, off
+
+    @staticmethod
+    def _finish_batches(pts_h, col_h, off, num_frames):
+        P, Cc = pts_h.numpy(), col_h.numpy()
+        return [{"points": P[off[i]:off[i + 1]], "colors": Cc[off[i]:off[i + 1]]} for i in range(num_frames)]
 
     def decompress(self, compressed_data, to_host=True):
         """bytes -> (frames, sideinfo).  to_host=False leaves the reconstruction on the device (returns
         the SparseTensor instead of the per-frame numpy dicts)."""
-        with self._lock, torch.cuda.device(self.device):
+        with self._lock, torch.cuda.device(self.device), ops.stream_scope():
             t_start = time.time()
+            ops.clear_deferred()
             tm = _StageTimer()
             tm.mark("start")
             y_strings, z_strings, y_shape, z_shape, points_streams, ks, q = self.read_bitstream_batched(compressed_data)
@@ -330,21 +378,22 @@ class DecompressionPipeline:
             y_points = self.geometry_decompression_step(points_streams)
             if y_points.shape[0] != y_shape:
                 raise ValueError(f"bitstream y shape {y_shape} != decoded coordinates {y_points.shape[0]}")
-            (y_points_dev,) = self._stager.to_device([y_points], self.device)
-            self.h2d_bytes += y_points.nbytes + len(compressed_data)
+            frame_counts = np.bincount(y_points[:, 0], minlength=nf).tolist() if len(y_points) else [0] * nf
+            y_points_dev, y_dev, z_dev = self.stage_bitstream(y_points, y_strings, z_strings)
             tm.mark("geometry_decompression")
-            ycm, z_hat, st_z = self.factorized_model_step_batched(z_strings, z_shape, y_points_dev, nf)
+            ycm, z_hat, st_z = self.factorized_model_step_batched(z_dev, z_strings[0][:16], z_shape, y_points_dev, nf)
             tm.mark("factorized_model")
             gaussian_params = self.hyper_synthesis_step(z_hat)
             tm.mark("hyper_synthesis")
-            y_hat, st_y = self.gaussian_model_step_batched(y_strings, ycm, q, gaussian_params)
+            y_hat, st_y = self.gaussian_model_step_batched(y_dev, y_strings[0][:16], ycm, q, gaussian_params)
+            y_hat.frame_counts = frame_counts
             tm.mark("guassian_model")
             x_hat = self.hyper_synthesis(y_hat, ks)
             tm.mark("synthesis_transform")
-            final_data = self.pack_batches(x_hat, nf) if to_host else x_hat
-            status = int(st_z.item()) | int(st_y.item())
-            if status != 0:
-                raise ops._lib.PccError(f"entropy decode failed (status {status})")
+            packed = self.pack_batches(x_hat, nf) if to_host else None
+            # the call's single blocking point: every deferred size check and both decoder status words
+            ops.verify_deferred([(st_z, "entropy decode of z failed"), (st_y, "entropy decode of y failed")])
+            final_data = self._finish_batches(*packed, nf) if to_host else x_hat
             st = tm.resolve()
             sideinfo = {"time_measurements": {}, "timestamps": {}}
             for key in ("bitstream_reading", "geometry_decompression", "factorized_model", "hyper_synthesis",

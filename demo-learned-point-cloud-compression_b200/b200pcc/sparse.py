@@ -29,6 +29,7 @@ class CoordMap:
         self.coarse = None          # CoordMap at 2x stride
         self.parent_row = None      # int32 [n]: row in `coarse`
         self._nbr_down = None
+        self.frame_off_host = None  # set by build_pyramid
 
     @property
     def stride(self) -> int:
@@ -68,6 +69,24 @@ class CoordMap:
             self.coarse = CoordMap(keys, self.log2_stride + 1)
             self.parent_row = parent
         return self.coarse
+
+    def build_pyramid(self, levels: int, num_frames: int = 0):
+        """Precompute the next `levels` coarser maps (and per-frame row counts of every level) with a
+        single host sync, instead of one sync per downsample().  Returns the host frame offsets
+        [(levels+1), num_frames+1] (row 0 = this map) or None."""
+        have, cm = 0, self
+        while cm.coarse is not None and have < levels:
+            cm, have = cm.coarse, have + 1
+        if have >= levels and (num_frames == 0 or self.frame_off_host is not None):
+            return self.frame_off_host
+        keys_l, par_l, counts, offs = ops.coords_pyramid(self.keys, self.log2_stride, levels, num_frames)
+        cm = self
+        for l in range(levels):
+            cm.coarse = CoordMap(keys_l[l], cm.log2_stride + 1)
+            cm.parent_row = par_l[l]
+            cm = cm.coarse
+        self.frame_off_host = offs
+        return offs
 
     def nbr_down(self) -> torch.Tensor:
         """[8, n_coarse] kernel map of the k=2 stride-2 convolution onto ``downsample()``."""

@@ -48,6 +48,27 @@ __global__ void k_coords_from_keys(const uint64_t* __restrict__ keys, int64_t n,
   c[i] = make_int4(b, x, y, z);
 }
 
+// decoder output: keys -> int32 xyz, colours nan -> 0 and clip(c * 255, 0, 255) / 255 in fp32
+// (pack_batches, receiver/decoder/codec_parallel.py:474-502)
+__global__ void k_unpack_output(const uint64_t* __restrict__ keys, const float* __restrict__ feats, int64_t n,
+                                int32_t* __restrict__ pts, float* __restrict__ col) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int b, x, y, z;
+  unpack_key(keys[i], b, x, y, z);
+  pts[3 * i] = x;
+  pts[3 * i + 1] = y;
+  pts[3 * i + 2] = z;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    float v = feats[3 * i + c];
+    if (v != v) v = 0.0f;
+    float t = __fmul_rn(v, 255.0f);
+    t = fminf(fmaxf(t, 0.0f), 255.0f);
+    col[3 * i + c] = __fdiv_rn(t, 255.0f);
+  }
+}
+
 __global__ void k_iota(int32_t* v, int64_t n) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i < n) v[i] = (int32_t)i;
@@ -77,6 +98,48 @@ __global__ void k_scatter_runs(const uint64_t* __restrict__ keys, const int32_t*
   }
   if (run_of) run_of[i] = r;
   if (i == n - 1) *n_out = incl[i];
+}
+
+// ---- device-count variants (no host round trip between pyramid levels) --------------------------
+// n_dev (may be null: then n = nmax) is the true element count; the launch covers nmax >= n.
+__global__ void k_run_flags_dc(const uint64_t* __restrict__ keys, const int32_t* __restrict__ n_dev, int64_t nmax,
+                               uint64_t mask, int32_t* __restrict__ flags) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= nmax) return;
+  const int64_t n = n_dev ? (int64_t)*n_dev : nmax;
+  int32_t f = 0;
+  if (i < n) {
+    uint64_t k = keys[i] & mask;
+    f = (i == 0 || (keys[i - 1] & mask) != k) ? 1 : 0;
+  }
+  flags[i] = f;
+}
+__global__ void k_scatter_runs_dc(const uint64_t* __restrict__ keys, const int32_t* __restrict__ incl,
+                                  const int32_t* __restrict__ n_dev, int64_t nmax, uint64_t mask,
+                                  uint64_t* __restrict__ keys_out, int32_t* __restrict__ run_of,
+                                  int32_t* __restrict__ n_out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int64_t n = n_dev ? (int64_t)*n_dev : nmax;
+  if (i == 0 && n == 0) *n_out = 0;
+  if (i >= n) return;
+  int32_t r = incl[i] - 1;
+  bool first = (i == 0) || (incl[i - 1] != incl[i]);
+  if (first) keys_out[r] = keys[i] & mask;
+  run_of[i] = r;
+  if (i == n - 1) *n_out = incl[i];
+}
+__global__ void k_frame_offsets_dc(const uint64_t* __restrict__ keys, const int32_t* __restrict__ n_dev,
+                                   int64_t nmax, int nf, int32_t* __restrict__ off) {
+  int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b > nf) return;
+  const int64_t n = n_dev ? (int64_t)*n_dev : nmax;
+  uint64_t target = (uint64_t)b << 48;
+  int64_t lo = 0, hi = n;
+  while (lo < hi) {
+    int64_t mid = (lo + hi) >> 1;
+    if (keys[mid] < target) lo = mid + 1; else hi = mid;
+  }
+  off[b] = (int32_t)lo;
 }
 
 __global__ void k_children(const uint64_t* __restrict__ keys, int64_t n, int shift,
@@ -207,6 +270,15 @@ int pcc_ingest_frame(const int16_t* points, const double* colors, int64_t n, int
   PCC_LAUNCHED();
   return PCC_OK;
 }
+int pcc_unpack_output(const uint64_t* keys, const float* feats3, int64_t n, int32_t* points, float* colors,
+                      pcc_stream_t s) {
+  PCC_CHECK_ARG(n >= 0);
+  if (n == 0) return PCC_OK;
+  PCC_CHECK_ARG(keys && feats3 && points && colors);
+  k_unpack_output<<<blocks_for(n), kThreads, 0, as_stream(s)>>>(keys, feats3, n, points, colors);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
 int pcc_coords_from_keys(const uint64_t* keys, int64_t n, int32_t* coords, pcc_stream_t s) {
   PCC_CHECK_ARG(n >= 0);
   if (n == 0) return PCC_OK;
@@ -310,6 +382,59 @@ int pcc_coords_downsample(const uint64_t* keys_in, int64_t n, int log2_stride, u
   k_scatter_runs<<<blocks_for(n), kThreads, 0, st>>>(keys_in, nullptr, flags, n, mask, keys_out,
                                                      nullptr, parent_row, n_out_dev);
   PCC_LAUNCHED();
+  return PCC_OK;
+}
+
+// Whole stride pyramid in one call: level l+1 = stride-2 coarsening of level l, counts stay on the
+// device (the launches of a level cover the input's size n, an upper bound of every level).
+int64_t pcc_coords_pyramid_workspace_bytes(int64_t n) { return pcc_coords_downsample_workspace_bytes(n); }
+
+int pcc_coords_pyramid(const uint64_t* keys_in, int64_t n, int log2_stride, int levels, uint64_t* keys_out,
+                       int32_t* parent_row, int32_t* counts_dev, int32_t num_frames,
+                       int32_t* frame_offsets_dev, void* ws, int64_t ws_bytes, pcc_stream_t s) {
+  PCC_CHECK_ARG(n >= 0 && n < (1ll << 31) && levels >= 1 && levels <= 14 && log2_stride >= 0 &&
+                log2_stride + levels <= 15 && counts_dev);
+  PCC_CHECK_ARG(num_frames >= 0 && num_frames < 65535 && (num_frames == 0 || frame_offsets_dev));
+  cudaStream_t st = as_stream(s);
+  if (n == 0) {
+    PCC_CUDA(cudaMemsetAsync(counts_dev, 0, 4 * (size_t)levels, st));
+    if (num_frames) PCC_CUDA(cudaMemsetAsync(frame_offsets_dev, 0, 4 * (size_t)(levels + 1) * (num_frames + 1), st));
+    return PCC_OK;
+  }
+  PCC_CHECK_ARG(keys_in && keys_out && parent_row && ws);
+  WsCarver w(ws, ws_bytes);
+  int32_t* flags = (int32_t*)w.take(n * 4);
+  size_t scan_b = cub_scan_bytes(n);
+  void* scan_ws = w.take((int64_t)scan_b);
+  if (!flags || !scan_ws) {
+    set_error("pcc_coords_pyramid: workspace too small");
+    return PCC_E_WORKSPACE;
+  }
+  const unsigned fo_blocks = blocks_for(num_frames + 1, 64);
+  if (num_frames) {
+    k_frame_offsets_dc<<<fo_blocks, 64, 0, st>>>(keys_in, nullptr, n, num_frames, frame_offsets_dev);
+    PCC_LAUNCHED();
+  }
+  const uint64_t* cur = keys_in;
+  const int32_t* cur_n = nullptr;
+  for (int l = 0; l < levels; ++l) {
+    const uint64_t mask = ~((1ull << (3 * (log2_stride + l + 1))) - 1ull);
+    uint64_t* out = keys_out + (int64_t)l * n;
+    int32_t* par = parent_row + (int64_t)l * n;
+    k_run_flags_dc<<<blocks_for(n), kThreads, 0, st>>>(cur, cur_n, n, mask, flags);
+    PCC_LAUNCHED();
+    PCC_CUDA(cub::DeviceScan::InclusiveSum(scan_ws, scan_b, flags, flags, (int)n, st));
+    g_launches.fetch_add(1);
+    k_scatter_runs_dc<<<blocks_for(n), kThreads, 0, st>>>(cur, flags, cur_n, n, mask, out, par, counts_dev + l);
+    PCC_LAUNCHED();
+    if (num_frames) {
+      k_frame_offsets_dc<<<fo_blocks, 64, 0, st>>>(out, counts_dev + l, n, num_frames,
+                                                   frame_offsets_dev + (int64_t)(l + 1) * (num_frames + 1));
+      PCC_LAUNCHED();
+    }
+    cur = out;
+    cur_n = counts_dev + l;
+  }
   return PCC_OK;
 }
 

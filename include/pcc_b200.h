@@ -55,6 +55,10 @@ int pcc_keys_from_coords_f32(const float* coords, int64_t n, uint64_t* keys, pcc
  * codec_pipeline.py:257-260 (shared/utils.py:10-42). */
 int pcc_ingest_frame(const int16_t* points, const double* colors, int64_t n, int32_t batch,
                      uint64_t* keys, float* feats4, pcc_stream_t s);
+/* Decoder output packing (pack_batches, codec_parallel.py:474-502): keys -> int32 [n,3] (x,y,z) and
+ * colours [n,3] with NaN -> 0 and clip(c * 255, 0, 255) / 255 evaluated in fp32. */
+int pcc_unpack_output(const uint64_t* keys, const float* feats3, int64_t n, int32_t* points, float* colors,
+                      pcc_stream_t s);
 /* keys -> int32 [n,4] (b,x,y,z): the `.C` attribute. */
 int pcc_coords_from_keys(const uint64_t* keys, int64_t n, int32_t* coords, pcc_stream_t s);
 
@@ -71,6 +75,17 @@ int64_t pcc_coords_downsample_workspace_bytes(int64_t n);
 int pcc_coords_downsample(const uint64_t* keys_in, int64_t n, int log2_stride, uint64_t* keys_out,
                           int32_t* parent_row, int32_t* n_out_dev, void* ws, int64_t ws_bytes,
                           pcc_stream_t s);
+/* The whole stride pyramid of a coordinate set in one call (the output coordinates of the chained
+ * stride-2 convolutions of g_a and h_a, codec_pipeline.py:273,287, and of g_s.down_conv x2,
+ * codec_parallel.py:302-303): level l (0-based) holds the keys at stride 2^(log2_stride+l+1) in
+ * keys_out[l*n ...], parent_row[l*n + i] = row of level l-1's (or the input's) row i in level l, and
+ * counts_dev[l] its size.  Counts stay on the device between levels, so the caller syncs once for all
+ * of them.  frame_offsets_dev: [(levels+1)][num_frames+1] per-frame row ranges of the input and of
+ * every level (num_frames = 0: skipped). */
+int64_t pcc_coords_pyramid_workspace_bytes(int64_t n);
+int pcc_coords_pyramid(const uint64_t* keys_in, int64_t n, int log2_stride, int levels, uint64_t* keys_out,
+                       int32_t* parent_row, int32_t* counts_dev, int32_t num_frames,
+                       int32_t* frame_offsets_dev, void* ws, int64_t ws_bytes, pcc_stream_t s);
 /* Generative transposed convolution coordinates (k=2, s=2): 8 children per input voxel; child row
  * 8*p + j, j = dx + 2dy + 4dz  (MinkowskiGenerativeConvolutionTranspose inside g_s / h_s:
  * codec_parallel.py:376,469).  log2_stride = log2 of the OUTPUT tensor stride. */
