@@ -254,14 +254,38 @@ def main():
         summ = prof.summary()
         fams = sorted(summ.items(), key=lambda kv: -kv[1]["ms"])
         kernel_ms = sum(v["ms"] for v in summ.values())
-        top_name, top = fams[0]
+        top_name, _ = fams[0]
+        # the dominant kernel = the largest launch shape of the family with the largest time share
+        shapes = {}
+        for fam, nbytes, flops, e0, e1 in prof.records:
+            if fam == top_name:
+                d = shapes.setdefault(nbytes, {"launches": 0, "ms": 0.0, "bytes": 0, "flops": 0})
+                d["launches"] += 1
+                d["ms"] += e0.elapsed_time(e1)
+                d["bytes"] += nbytes
+                d["flops"] += flops
+        top_bytes = max(shapes)
+        top = shapes[top_bytes]
         gbs = top["bytes"] / (top["ms"] * 1e-3) / 1e9
         tfs = top["flops"] / (top["ms"] * 1e-3) / 1e12
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+        if os.path.exists(tpath):
+            best = None
+            for ent in json.load(open(tpath)).get("kernels", []):
+                err = abs(ent["algorithmic_bytes"] - top_bytes) / top_bytes
+                if ent["family"] == top_name and err <= 0.05 and (best is None or err < best[0]):
+                    best = (err, ent["dram_bytes_per_launch"])
+            traffic = best[1] if best else None
         roof = {"bound": "hbm", "kernel": top_name, "achieved": gbs, "peak": hbm_peak, "unit": "GB/s",
-                "frac": gbs / hbm_peak, "traffic": None, "peak_source": which,
+                "frac": gbs / hbm_peak, "traffic": traffic, "peak_source": which,
+                "algorithmic_bytes_per_launch": int(top_bytes),
                 "launches_per_step": top["launches"] / steps, "avg_launch_ms": top["ms"] / top["launches"],
-                "share_of_kernel_time": top["ms"] / kernel_ms, "tensor_tflops": tfs,
-                "tensor_frac": tfs / tf_peak}
+                "share_of_kernel_time": top["ms"] / kernel_ms,
+                "family_share_of_kernel_time": fams[0][1]["ms"] / kernel_ms, "tensor_tflops": tfs,
+                "tensor_frac": tfs / tf_peak,
+                "note": "largest launch shape of the top family; traffic = dram read+write bytes of the same "
+                        "shape from the ncu --set full capture summarised under profiles/"}
         if args.breakdown:
             print(f"{'family':34s} {'n/step':>7s} {'ms/step':>9s} {'GB/s':>9s} {'TF/s':>8s}", file=sys.stderr)
             for name, v in fams:
