@@ -60,6 +60,11 @@ SIGNATURES = {
     "pcc_frame_offsets": (INT, [P, I64, I32, P, P]),
     "pcc_lex_order_workspace_bytes": (I64, [I64]),
     "pcc_lex_order": (INT, [P, I64, P, P, I64, P]),
+    "pcc_octree_max_bytes": (I64, [I64]),
+    "pcc_octree_encode_workspace_bytes": (I64, [I64, I32]),
+    "pcc_octree_encode": (INT, [P, I64, P, I32, INT, P, P, P, P, I64, P]),
+    "pcc_octree_decode_workspace_bytes": (I64, [I64]),
+    "pcc_octree_decode": (INT, [P, P, P, P, I32, I64, INT, P, P, P, I64, P]),
     "pcc_spconv_packed_weight_bytes": (I64, [INT, INT, INT]),
     "pcc_spconv_pack_weights": (INT, [P, INT, INT, INT, INT, P]),
     "pcc_spconv_umma": (INT, [P, I64, INT, P, I64, I64, INT, P, P, INT, P, I64, INT, P, P, I64, INT, P]),

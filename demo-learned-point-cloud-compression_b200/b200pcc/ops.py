@@ -258,7 +258,8 @@ def coords_pyramid(keys: torch.Tensor, log2_stride: int, levels: int, num_frames
     keys_l = [kout[l, :counts[l]] for l in range(levels)]
     n_fine = [n] + counts[:-1]
     par_l = [par[l, :n_fine[l]] for l in range(levels)]
-    return keys_l, par_l, counts, offs
+    offs_dev = meta[levels:].view(levels + 1, nf1) if num_frames else None
+    return keys_l, par_l, counts, offs, offs_dev
 
 
 def coords_children(keys: torch.Tensor, log2_stride_out: int) -> torch.Tensor:
@@ -355,6 +356,49 @@ def lex_order(keys: torch.Tensor) -> torch.Tensor:
     ws = workspace(wsb, keys.device)
     check(lib.pcc_lex_order(_ptr(keys), n, _ptr(perm), _ptr(ws), ws.numel(), _stream()))
     return perm
+
+
+# ------------------------------------------------------------------------------------------------
+# coordinate coder (OCT2 streams)
+# ------------------------------------------------------------------------------------------------
+def octree_encode(keys: torch.Tensor, frame_off_dev: torch.Tensor, frame_counts, log2_stride: int):
+    """Per-frame OCT2 streams of a sorted key set, left on the device.
+    frame_off_dev: int32 [num_frames+1] device row offsets; frame_counts: the same row counts on the
+    host (they size the output).  -> [(device uint8 buffer, device int32 size)] per frame."""
+    _need_cuda(keys, torch.int64)
+    _need_cuda(frame_off_dev, torch.int32)
+    nf = len(frame_counts)
+    dev = keys.device
+    bounds = [int(lib.pcc_octree_max_bytes(int(c))) for c in frame_counts]
+    offs = np.zeros(nf + 1, dtype=np.int64)
+    offs[1:] = np.cumsum(bounds)
+    out = torch.empty(max(int(offs[-1]), 4), dtype=torch.uint8, device=dev)
+    out_off = torch.from_numpy(offs[:nf].copy()).to(dev, non_blocking=True)
+    sizes = torch.empty(max(nf, 1), dtype=torch.int32, device=dev)
+    n = keys.shape[0]
+    ws = workspace(lib.pcc_octree_encode_workspace_bytes(n, nf), dev, "octree")
+    with _prof("octree_encode", n * 8 * 2 + n * 2):    # keys read by the level and the pack pass; ~1.3 n bytes out
+        check(lib.pcc_octree_encode(_ptr(keys), n, _ptr(frame_off_dev), nf, log2_stride, _ptr(out), _ptr(out_off),
+                                    _ptr(sizes), _ptr(ws), ws.numel(), _stream()))
+    return [(out[int(offs[b]):int(offs[b + 1])], sizes[b:b + 1]) for b in range(nf)]
+
+
+def octree_decode(streams: torch.Tensor, stream_off: torch.Tensor, stream_len: torch.Tensor,
+                  row_off: torch.Tensor, num_frames: int, n_total: int, log2_stride: int):
+    """streams: device uint8 blob holding every frame's stream at a 4-byte aligned offset.
+    -> (keys int64 [n_total] ascending, status int32 [1]); no host sync."""
+    _need_cuda(streams, torch.uint8)
+    _need_cuda(stream_off, torch.int64)
+    _need_cuda(stream_len, torch.int32)
+    _need_cuda(row_off, torch.int32)
+    dev = streams.device
+    keys = torch.empty(n_total, dtype=torch.int64, device=dev)
+    status = torch.empty(1, dtype=torch.int32, device=dev)
+    ws = workspace(lib.pcc_octree_decode_workspace_bytes(n_total), dev, "octree")
+    with _prof("octree_decode", n_total * 8 * 3):
+        check(lib.pcc_octree_decode(_ptr(streams), _ptr(stream_off), _ptr(stream_len), _ptr(row_off), num_frames,
+                                    n_total, log2_stride, _ptr(keys), _ptr(status), _ptr(ws), ws.numel(), _stream()))
+    return keys, status
 
 
 # ------------------------------------------------------------------------------------------------

@@ -165,31 +165,11 @@ class CompressionPipeline:
     def hyper_synthesis_step(self, z_hat):
         return self.compression_model.entropy_model.h_s(z_hat)
 
-    def start_coordinate_copy(self, ycm):
-        """Device->host copy of the stride-8 latent coordinates on a side stream, issued as soon as the
-        coordinate pyramid exists, so the host-side coordinate coder overlaps the transforms."""
-        C = ycm.coords()
-        ev = torch.cuda.Event()
-        ev.record()
-        if self._copy_stream is None:
-            self._copy_stream = torch.cuda.Stream(device=self.device)
-        host = torch.empty(C.shape, dtype=C.dtype, pin_memory=True)
-        with torch.cuda.stream(self._copy_stream):
-            self._copy_stream.wait_event(ev)
-            host.copy_(C, non_blocking=True)
-            done = torch.cuda.Event()
-            done.record()
-        self.d2h_bytes += C.numel() * 4
-        return host, done, C
-
-    def geometry_compression_step(self, coords_copy, num_frames):
+    def geometry_compression_step(self, ycm):
         """Per-frame coordinate streams for the stride-8 latent coordinates (replaces gpcc_encode,
-        codec_pipeline.py:441-462)."""
-        host, done, _keepalive = coords_copy
-        done.synchronize()
-        C = host.numpy()
-        off = np.searchsorted(C[:, 0], np.arange(num_frames + 1))
-        return [geometry.encode_points(C[off[b]:off[b + 1], 1:], 8) for b in range(num_frames)]
+        codec_pipeline.py:441-462): built on the device right after the coordinate pyramid; the
+        streams stay there until compress() fetches every string of the GOP at once."""
+        return geometry.encode_device(ycm)
 
     def gaussian_model_step_batched(self, y, settings, gaussian_params):
         """All qualities in one pass (codec_pipeline.py:397-437): gather h_s rows at the y
@@ -218,12 +198,12 @@ class CompressionPipeline:
             x, sideinfo = self.unpack_batch(data, staged)
             num_points = x.cmap.n
             nf = x.num_frames
-            # every coarser coordinate map (g_a: 3, h_a: 2) with one host sync, then the latent
-            # coordinates start their trip to the host while the transforms run
+            # every coarser coordinate map (g_a: 3, h_a: 2) with one host sync
             x.cmap.build_pyramid(5, nf)
             ycm = x.cmap.coarse.coarse.coarse
-            coords_copy = self.start_coordinate_copy(ycm)
             tm.mark("unpack")
+            geo_pending = self.geometry_compression_step(ycm)
+            tm.mark("geometry_compression")
             y, k = self.analysis_step(x)
             tm.mark("analysis")
             z = self.hyper_analysis_step(y)
@@ -234,12 +214,9 @@ class CompressionPipeline:
             tm.mark("hyper_synthesis")
             y_pending, y_shapes = self.gaussian_model_step_batched(y, self.settings, gaussian_params)
             tm.mark("gaussian_model")
-            # host work that overlaps the GPU: coordinate streams
-            t_g0 = time.time()
-            points_streams = self.geometry_compression_step(coords_copy, nf)
-            t_geo = time.time() - t_g0
-            strings = fetch_strings(z_pending + y_pending)       # the GOP's two remaining syncs
-            z_strings, y_strings = strings[:1], strings[1:]
+            strings = fetch_strings(z_pending + y_pending + geo_pending)   # the GOP's two remaining syncs
+            z_strings, y_strings = strings[:1], strings[1:1 + len(y_pending)]
+            points_streams = strings[1 + len(y_pending):]
             self.d2h_bytes += sum(len(b) for b in strings)
             t7 = []
             for i, q in enumerate(self.settings):
@@ -253,7 +230,7 @@ class CompressionPipeline:
                 "hyper_analysis": st.get("hyper_analysis", 0.0),
                 "factorized_model": st.get("factorized_model", 0.0),
                 "hyper_synthesis": st.get("hyper_synthesis", 0.0),
-                "geometry_compression": t_geo,
+                "geometry_compression": st.get("geometry_compression", 0.0),
                 "gaussian_model": st.get("gaussian_model", 0.0),
                 "bitstream_writing": t7,
             }
@@ -280,41 +257,38 @@ class DecompressionPipeline:
     def read_bitstream_batched(self, compressed_data):
         return container.read_bitstream_batched(compressed_data)
 
-    def geometry_decompression_step(self, points_streams):
-        """Per-frame coordinate streams -> stacked (b,x,y,z) int32 (replaces gpcc_decode + stack_tensors,
-        codec_parallel.py:266-289)."""
-        out = []
-        for b, s in enumerate(points_streams):
-            p = geometry.decode_points(s, 8)
-            out.append(np.concatenate([np.full((p.shape[0], 1), b, dtype=np.int32), p], axis=1))
-        return np.concatenate(out, axis=0) if out else np.zeros((0, 4), np.int32)
-
-    def stage_bitstream(self, y_points, y_strings, z_strings):
-        """One pinned staging copy for everything the decoder needs on the device: the decoded latent
-        coordinates and the two entropy-coded strings (padded to 4 bytes for the lane decoder)."""
+    def stage_bitstream(self, points_streams, y_strings, z_strings):
+        """One pinned staging copy for everything the decoder needs on the device: the coordinate
+        streams (+ their offsets / lengths / row offsets) and the two entropy-coded strings (padded to
+        4 bytes for the lane decoder).  -> (device tensors, per-frame latent point counts)."""
         def pad4(b):
             a = np.frombuffer(b, dtype=np.uint8)
             p = (-len(a)) % 4
             return np.concatenate([a, np.zeros(p, np.uint8)]) if p else a
-        arrays = [y_points, pad4(y_strings[0]), pad4(z_strings[0])]
+        blob, offs, meta32, counts = geometry.pack_streams(points_streams)
+        arrays = [blob, offs, meta32, pad4(y_strings[0]), pad4(z_strings[0])]
         dev = self._stager.to_device(arrays, self.device)
         self.h2d_bytes += sum(a.nbytes for a in arrays)
-        return dev
+        return dev, counts
 
-    def factorized_model_step_batched(self, z_string_dev, z_hdr, z_shape, y_points_dev, num_frames):
+    def geometry_decompression_step(self, blob_d, offs_d, meta32_d, counts):
+        """Per-frame coordinate streams -> the sorted stride-8 coordinate map of the latents, on the
+        device (replaces gpcc_decode + stack_tensors, codec_parallel.py:266-289).  The octree expands
+        in ascending key order, so no sort / de-duplication pass follows."""
+        ykeys, status = geometry.decode_device(blob_d, offs_d, meta32_d, counts)
+        return CoordMap(ykeys, geometry.LOG2_STRIDE), status
+
+    def factorized_model_step_batched(self, z_string_dev, z_hdr, z_shape, ycm):
         """Rebuild the stride-32 coordinates from the y coordinates and decode z_hat
         (codec_parallel.py:291-318; g_s.down_conv is used for coordinates only).  No host sync: the
         sizes come from the bitstream and are verified at the end of decompress()."""
         m = self.decompression_model
-        n_y = int(y_points_dev.shape[0])
-        ykeys, _ = ops.sort_unique(ops.keys_from_coords(y_points_dev), want_src=False, expect=n_y)
-        ycm = CoordMap(ykeys, 3)
-        zkeys = ops.coords_pyramid_expect(ykeys, 3, 2, z_shape)
+        zkeys = ops.coords_pyramid_expect(ycm.keys, 3, 2, z_shape)
         zcm = CoordMap(zkeys, 5)
         eb = m.entropy_model.entropy_bottleneck
         sym, status = eb._decode_device(z_string_dev, z_hdr, None, zcm.n, zcm.n * eb.channels)
         zhat, _ = ops.factorized_dequant(sym.view(eb.channels, zcm.n), zcm.lex_perm(), eb.medians_d)
-        return ycm, SparseTensor(_cmap=zcm, _feats=zhat, _channels=eb.channels), status
+        return SparseTensor(_cmap=zcm, _feats=zhat, _channels=eb.channels), status
 
     def hyper_synthesis_step(self, z_hat):
         return self.decompression_model.entropy_model.h_s(z_hat)
@@ -375,13 +349,13 @@ class DecompressionPipeline:
             y_strings, z_strings, y_shape, z_shape, points_streams, ks, q = self.read_bitstream_batched(compressed_data)
             nf = len(points_streams)
             tm.mark("bitstream_reading")
-            y_points = self.geometry_decompression_step(points_streams)
-            if y_points.shape[0] != y_shape:
-                raise ValueError(f"bitstream y shape {y_shape} != decoded coordinates {y_points.shape[0]}")
-            frame_counts = np.bincount(y_points[:, 0], minlength=nf).tolist() if len(y_points) else [0] * nf
-            y_points_dev, y_dev, z_dev = self.stage_bitstream(y_points, y_strings, z_strings)
+            (blob_d, offs_d, meta32_d, y_dev, z_dev), frame_counts = self.stage_bitstream(points_streams, y_strings,
+                                                                                          z_strings)
+            if sum(frame_counts) != y_shape:
+                raise ValueError(f"bitstream y shape {y_shape} != coordinate streams {sum(frame_counts)}")
+            ycm, st_geo = self.geometry_decompression_step(blob_d, offs_d, meta32_d, frame_counts)
             tm.mark("geometry_decompression")
-            ycm, z_hat, st_z = self.factorized_model_step_batched(z_dev, z_strings[0][:16], z_shape, y_points_dev, nf)
+            z_hat, st_z = self.factorized_model_step_batched(z_dev, z_strings[0][:16], z_shape, ycm)
             tm.mark("factorized_model")
             gaussian_params = self.hyper_synthesis_step(z_hat)
             tm.mark("hyper_synthesis")
@@ -392,7 +366,8 @@ class DecompressionPipeline:
             tm.mark("synthesis_transform")
             packed = self.pack_batches(x_hat, nf) if to_host else None
             # the call's single blocking point: every deferred size check and both decoder status words
-            ops.verify_deferred([(st_z, "entropy decode of z failed"), (st_y, "entropy decode of y failed")])
+            ops.verify_deferred([(st_geo, "coordinate stream decode failed"), (st_z, "entropy decode of z failed"),
+                                 (st_y, "entropy decode of y failed")])
             final_data = self._finish_batches(*packed, nf) if to_host else x_hat
             st = tm.resolve()
             sideinfo = {"time_measurements": {}, "timestamps": {}}

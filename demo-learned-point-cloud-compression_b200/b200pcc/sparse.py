@@ -30,6 +30,8 @@ class CoordMap:
         self.parent_row = None      # int32 [n]: row in `coarse`
         self._nbr_down = None
         self.frame_off_host = None  # set by build_pyramid
+        self.frame_off_dev = None   # int32 [num_frames+1] device row offsets (levels made by build_pyramid)
+        self.frame_counts = None    # the same as host row counts
 
     @property
     def stride(self) -> int:
@@ -79,12 +81,15 @@ class CoordMap:
             cm, have = cm.coarse, have + 1
         if have >= levels and (num_frames == 0 or self.frame_off_host is not None):
             return self.frame_off_host
-        keys_l, par_l, counts, offs = ops.coords_pyramid(self.keys, self.log2_stride, levels, num_frames)
+        keys_l, par_l, counts, offs, offs_dev = ops.coords_pyramid(self.keys, self.log2_stride, levels, num_frames)
         cm = self
         for l in range(levels):
             cm.coarse = CoordMap(keys_l[l], cm.log2_stride + 1)
             cm.parent_row = par_l[l]
             cm = cm.coarse
+            if offs_dev is not None:      # per-frame row ranges of this level, on both sides
+                cm.frame_off_dev = offs_dev[l + 1]
+                cm.frame_counts = [int(c) for c in (offs[l + 1][1:] - offs[l + 1][:-1])]
         self.frame_off_host = offs
         return offs
 

@@ -156,7 +156,12 @@ struct UmmaParams {
   uint32_t tmem_cols, acc_cols;
 };
 
-constexpr int kMmaWarp = 4, kLoaderWarp = 5, kProdWarp0 = 6;
+// warps 4..7 issue MMAs: one elected thread each, every warp owning the tiles t = w (mod 4) of a
+// stage.  A single issuing thread was the bottleneck of the kernel (ncu r1g: the gather warps spent
+// 90 % of their time waiting for their slot to be released while the lone MMA warp never waited):
+// building two descriptors and issuing one tcgen05.mma costs ~100 issue cycles in the uniform
+// datapath, i.e. ~1500 cycles for the 8 MMAs + commits of a T = 4 stage that the gather fills in ~500.
+constexpr int kMmaWarp = 4, kMmaWarps = 4, kLoaderWarp = 8, kProdWarp0 = 9;
 constexpr int kNbrBufs = 3;   // kernel-map ring depth (units)
 
 template <bool CG>
@@ -179,10 +184,11 @@ __device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr) {
 // N = cout as small as 32 a chain of accumulating tcgen05.mma into ONE accumulator runs at the MMA
 // pipeline latency, not at its throughput; the per-stage hand-off cost is amortised over T tiles.
 //   warps 0-3   epilogue (TMEM lane quarter = warp): TMEM -> bias/residual/ReLU -> global, per round
-//   warp  4     MMA issuer + TMEM owner (2 x T accumulators: round r+1 accumulates while r drains)
-//   warp  5     kernel-map loader: units of jc offsets x T tiles, one 512-byte cp.async.bulk per
+//   warps 4-7   MMA issuers (one thread each; warp 4 owns TMEM: 2 x T accumulators, round r+1
+//               accumulates while r drains); issuer w handles the tiles t = w (mod 4) of every stage
+//   warp  8     kernel-map loader: units of jc offsets x T tiles, one 512-byte cp.async.bulk per
 //               (offset, tile) into a 3-deep ring; resident weight panels
-//   warps 6..   G gather groups of 4 warps.  Group i owns ring slot i and the stages g = i (mod G):
+//   warps 9..   G gather groups of 4 warps.  Group i owns ring slot i and the stages g = i (mod G):
 //               wait slot free -> cp.async all T x 128 rows (zero fill for absent neighbours) into
 //               the no-swizzle K-major core-matrix layout -> wait landed -> proxy fence -> signal.
 //               While one group waits for its rows the other groups issue theirs.
@@ -223,12 +229,13 @@ k_spconv_umma(const UmmaParams p) {
   const uint32_t nunits = (uint32_t)(kvol / p.jc);   // kernel-map units per round
 
   if (tid == 0) {
+    const uint32_t nmma = (uint32_t)(T < kMmaWarps ? T : kMmaWarps);   // MMA warps with work
     for (int s = 0; s < G; ++s) {
       mbar_init(full0 + 8u * s, 4);
-      mbar_init(empty0 + 8u * s, 1);
+      mbar_init(empty0 + 8u * s, nmma);
     }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(tfull0 + 8u * i, 1);
+      mbar_init(tfull0 + 8u * i, nmma);
       mbar_init(tempty0 + 8u * i, 4);
     }
     for (int i = 0; i < kNbrBufs; ++i) {
@@ -377,40 +384,44 @@ k_spconv_umma(const UmmaParams p) {
         }
       }
     }
-  } else if (warp == kMmaWarp) {
-    // ---------------- MMA issuer ----------------
-    // instruction descriptor: c=f32 (bit 4), a=b=bf16 (bits 7,10), K-major both, N>>3 @17, M>>4 @24
-    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(cout >> 3) << 17) |
-                           ((uint32_t)(kTileM >> 4) << 24);
-    const uint32_t lbo_b = (uint32_t)cout * 16u;
-    constexpr int ksteps = CIN >> 4;
-    if (p.wres) mbar_wait(wfull, 0);
-    uint32_t s = 0, ph = 0;
-    int r = 0;
-    for (int64_t rg = blockIdx.x; rg < p.nrounds_total; rg += gridDim.x, ++r) {
-      const uint32_t par = (uint32_t)(r & 1);
-      if (r >= 2) mbar_wait(tempty0 + 8u * par, (uint32_t)(((r >> 1) - 1) & 1));
-      tc_fence_after();
-      const uint32_t tmem_d0 = tmem_base + (par << lt) * p.acc_cols;
-      for (int j = 0; j < kvol; ++j) {
-        mbar_wait(full0 + 8u * s, ph & 1u);
+  } else if (warp >= kMmaWarp && warp < kMmaWarp + kMmaWarps) {
+    // ---------------- MMA issuers (one thread per warp; warp mw owns tiles t = mw, mw + 4, ...) ----------------
+    const int mw = warp - kMmaWarp;
+    if (lane == 0 && mw < T) {
+      // instruction descriptor: c=f32 (bit 4), a=b=bf16 (bits 7,10), K-major both, N>>3 @17, M>>4 @24
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(cout >> 3) << 17) |
+                             ((uint32_t)(kTileM >> 4) << 24);
+      const uint32_t lbo_b = (uint32_t)cout * 16u;
+      constexpr int ksteps = CIN >> 4;
+      // descriptors differ only in their 14-bit start-address field: keep the bases in registers and
+      // add (bytes >> 4) per slot / offset / K step (every address is below 256 KB: no carry out)
+      const uint64_t adesc0 = make_desc(a0 + (uint32_t)mw * a_tile, lbo_a, sbo_a);
+      const uint64_t bdesc0 = make_desc(w0, lbo_b, 128u);
+      const uint32_t a_slot = a_bytes >> 4, a_ks = (2u * lbo_a) >> 4, a_t = (kMmaWarps * a_tile) >> 4;
+      const uint32_t b_step = b_bytes >> 4, b_ks = (2u * lbo_b) >> 4;
+      if (p.wres) mbar_wait(wfull, 0);
+      uint32_t s = 0, ph = 0;
+      int r = 0;
+      for (int64_t rg = blockIdx.x; rg < p.nrounds_total; rg += gridDim.x, ++r) {
+        const uint32_t par = (uint32_t)(r & 1);
+        if (r >= 2) mbar_wait(tempty0 + 8u * par, (uint32_t)(((r >> 1) - 1) & 1));
         tc_fence_after();
-        if (lane == 0) {
-          const uint32_t a_s = a0 + s * a_bytes;
-          const uint32_t b_s = p.wres ? w0 + (uint32_t)j * b_bytes : w0 + s * b_bytes;
+        const uint32_t tmem_d0 = tmem_base + ((par << lt) + (uint32_t)mw) * p.acc_cols;
+        for (int j = 0; j < kvol; ++j) {
+          mbar_wait(full0 + 8u * s, ph & 1u);
+          tc_fence_after();
+          const uint64_t ad = adesc0 + (uint64_t)(s * a_slot);
+          const uint64_t bd = bdesc0 + (uint64_t)((p.wres ? (uint32_t)j : s) * b_step);
+          for (int t = mw, ti = 0; t < T; t += kMmaWarps, ++ti) {
 #pragma unroll
-          for (int ks = 0; ks < ksteps; ++ks) {
-            const uint64_t bdesc = make_desc(b_s + (uint32_t)ks * 2u * lbo_b, lbo_b, 128u);
-            for (int t = 0; t < T; ++t) {
-              const uint64_t adesc = make_desc(a_s + (uint32_t)t * a_tile + (uint32_t)ks * 2u * lbo_a, lbo_a, sbo_a);
-              umma_bf16(tmem_d0 + (uint32_t)t * p.acc_cols, adesc, bdesc, idesc, (j == 0 && ks == 0) ? 0u : 1u);
-            }
+            for (int ks = 0; ks < ksteps; ++ks)
+              umma_bf16(tmem_d0 + (uint32_t)(ti * kMmaWarps) * p.acc_cols, ad + (uint64_t)(ti * a_t + ks * a_ks),
+                        bd + (uint64_t)(ks * b_ks), idesc, (j == 0 && ks == 0) ? 0u : 1u);
           }
           umma_commit(empty0 + 8u * s);
           if (j == kvol - 1) umma_commit(tfull0 + 8u * par);
+          if (++s == (uint32_t)G) { s = 0; ++ph; }
         }
-        __syncwarp();
-        if (++s == (uint32_t)G) { s = 0; ++ph; }
       }
     }
   } else {
@@ -435,8 +446,15 @@ k_spconv_umma(const UmmaParams p) {
 #pragma unroll
             for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
             if (p.bias) {
+              const float4* bp = reinterpret_cast<const float4*>(p.bias + c0);   // 16-byte aligned (checked)
 #pragma unroll
-              for (int i = 0; i < 16; ++i) f[i] += __ldg(p.bias + c0 + i);
+              for (int i = 0; i < 4; ++i) {
+                const float4 b4 = __ldg(bp + i);
+                f[4 * i] += b4.x;
+                f[4 * i + 1] += b4.y;
+                f[4 * i + 2] += b4.z;
+                f[4 * i + 3] += b4.w;
+              }
             }
             if (p.residual) {
               const uint4* rp = reinterpret_cast<const uint4*>(p.residual + o * p.ldr + c0);
@@ -585,6 +603,7 @@ int pcc_spconv_umma(const void* in_bf16, int64_t n_in, int cin, const int32_t* n
   PCC_CHECK_ARG(cs < cout || !out_bf16 || ((uintptr_t)out_bf16 % 16) == 0);
   PCC_CHECK_ARG(cs < cout || !out_f32 || ((uintptr_t)out_f32 % 16) == 0);
   PCC_CHECK_ARG(!residual_bf16 || ((uintptr_t)residual_bf16 % 16) == 0);
+  PCC_CHECK_ARG(!bias || ((uintptr_t)bias % 16) == 0);
 
   UmmaParams p;
   p.in = (const __nv_bfloat16*)in_bf16;

@@ -129,6 +129,31 @@ int64_t pcc_lex_order_workspace_bytes(int64_t n);
 int pcc_lex_order(const uint64_t* keys, int64_t n, int32_t* perm, void* ws, int64_t ws_bytes,
                   pcc_stream_t s);
 
+/* Lossless coordinate coder ("OCT2" streams): fills the slot the reference fills
+ * with gpcc_encode / gpcc_decode -- a G-PCC tmc3 subprocess over temporary PLY files
+ * (shared/utils.py:169-240, called at codec_pipeline.py:441-462 and codec_parallel.py:266-289) -- for
+ * the stride-8 latent coordinates, without leaving the device.  A frame's rows are a sorted run of
+ * Morton keys, so the breadth-first octree occupancy bytes follow from prefix comparisons.
+ * encode: frame b = rows [frame_offsets_dev[b], frame_offsets_dev[b+1]); its stream is written at
+ * out + out_offsets_dev[b] (multiples of 4; reserve pcc_octree_max_bytes(rows of b)) and its size
+ * to sizes_dev[b].  Stream: "OCT2" | u32 n | u32 depth | u64 root | u32 nodes[depth] | level bytes.
+ * decode: frame b's stream is streams + stream_offsets_dev[b] (multiples of 4), stream_bytes_dev[b]
+ * long; its keys (ascending: no sort or de-duplication needed afterwards) go to
+ * keys_out[row_offsets_dev[b] .. row_offsets_dev[b+1]), the row counts being the n fields of the
+ * stream headers, which the host reads from the bitstream.  status_dev: 0 ok, bit 0 malformed or
+ * truncated header, bit 1 inconsistent occupancy bytes (keys of such a frame are set to b << 48). */
+int64_t pcc_octree_max_bytes(int64_t n);
+int64_t pcc_octree_encode_workspace_bytes(int64_t n_total, int32_t num_frames);
+int pcc_octree_encode(const uint64_t* keys, int64_t n_total, const int32_t* frame_offsets_dev,
+                      int32_t num_frames, int log2_stride, uint8_t* out,
+                      const int64_t* out_offsets_dev, int32_t* sizes_dev, void* ws, int64_t ws_bytes,
+                      pcc_stream_t s);
+int64_t pcc_octree_decode_workspace_bytes(int64_t n_total);
+int pcc_octree_decode(const uint8_t* streams, const int64_t* stream_offsets_dev,
+                      const int32_t* stream_bytes_dev, const int32_t* row_offsets_dev,
+                      int32_t num_frames, int64_t n_total, int log2_stride, uint64_t* keys_out,
+                      int32_t* status_dev, void* ws, int64_t ws_bytes, pcc_stream_t s);
+
 /* ------------------------------------------------------------------------------------------
  * (2) sparse convolution
  * ------------------------------------------------------------------------------------------ */

@@ -135,19 +135,33 @@ def test_rans_oracles_roundtrip_any_int32(n, seg):
         R.pcl1_decode(c[: len(c) // 2], idx, 1, n, t)
 
 
-def test_geometry_stream_roundtrip():
+def test_geometry_stream_oracle_roundtrip():
+    """OCT2 coordinate streams: the numpy restatement round-trips (any order in, Morton order out) and
+    the product's host-side header helpers agree with it (the coder itself is CUDA: test_gpu_octree)."""
+    from oracle import octree_ref as O
     from b200pcc import geometry, synth
     p = synth.small_frame(seed=9, n_target=8000)["points"].astype(np.int64)
     p8 = np.unique(np.floor_divide(p, 8) * 8, axis=0)
-    s = geometry.encode_points(p8, 8)
-    q = geometry.decode_points(s, 8)
+    s = O.encode_points(p8[::-1], 3)
+    q = O.decode_points(s, 3)
     assert sorted(map(tuple, q)) == sorted(map(tuple, p8))
+    k = S.morton_key(np.concatenate([np.zeros((len(q), 1), np.int64), q], axis=1))
+    assert np.all(k[1:] > k[:-1])                   # decoded in ascending Morton order
     assert len(s) < 3 * len(p8)                     # ~1-2 bytes per point
-    assert geometry.decode_points(geometry.encode_points(np.zeros((0, 3), int))).shape == (0, 3)
+    assert geometry.stream_points(s) == len(p8)
+    empty = O.encode_points(np.zeros((0, 3), int))
+    assert len(empty) == 20 and O.decode_points(empty).shape == (0, 3)
     one = np.array([[-16, 8, 0]])
-    assert geometry.decode_points(geometry.encode_points(one)).tolist() == one.tolist()
+    assert len(O.encode_points(one)) == 20 and O.decode_points(O.encode_points(one)).tolist() == one.tolist()
+    for bad in (s[: len(s) - 5], b"OCT1" + s[4:], s[:24] + bytes([s[24] ^ 1]) + s[25:]):
+        with pytest.raises(ValueError):
+            O.decode_points(bad, 3)
+    blob, offs, meta32, counts = geometry.pack_streams([s, empty, O.encode_points(one)])
+    assert counts == [len(p8), 0, 1] and offs.tolist() == [0, (len(s) + 3) // 4 * 4, (len(s) + 3) // 4 * 4 + 20]
+    assert meta32.tolist() == [len(s), 20, 20, 0, len(p8), len(p8), len(p8) + 1]
+    assert bytes(blob[offs[2]:offs[2] + 20]) == O.encode_points(one)
     with pytest.raises(ValueError):
-        geometry.decode_points(s[: len(s) - 5], 8)
+        geometry.stream_points(b"nope")
 
 
 def test_container_roundtrip_and_layout():
