@@ -1,23 +1,18 @@
 // (2) Output-stationary gather-GEMM sparse convolution on tcgen05 (sm_100a).
 //
-// One CTA owns a tile of 128 output rows.  For every kernel offset j (fixed order 0..kvol-1) the 128
-// gathered input rows (zero rows where the neighbour is absent) form the A operand [128 x cin] and
-// the weight panel W[j] is the B operand [cout x cin] (K-major).  tcgen05.mma accumulates all offsets
-// into one fp32 TMEM tile [128 lanes x cout columns]; the epilogue adds bias / residual, applies ReLU
-// and writes each output row exactly once.  No atomics and a fixed accumulation order make results
-// run-to-run deterministic and independent of the order rows were inserted in (SURVEY 3.2 inv. 3).
-//
-// Warp roles (160 threads): warps 0-3 gather (cp.async 16-byte chunks with zero fill into the
-// no-swizzle K-major core-matrix layout; the weight panel arrives by one cp.async.bulk), then become
-// the epilogue warps (TMEM lane = output row); warp 4 allocates TMEM and its lane 0 issues the MMAs.
-// Stages are recycled through full/empty mbarriers; tcgen05.commit releases a stage.
+// out[o] = act(bias + sum_j in[nbr[j][o]] . W[j] (+ residual[o])): for every kernel offset j (fixed order
+// 0..kvol-1) the gathered input rows of a 128-row output tile (zero rows where the neighbour is absent)
+// form the A operand [128 x cin] and the weight panel W[j] the B operand [cout x cin] (K-major).
+// tcgen05.mma accumulates all offsets into fp32 TMEM tiles [128 lanes x cout columns]; the epilogue
+// adds bias / residual, applies ReLU and writes each output row exactly once.  No atomics and a fixed
+// accumulation order make results run-to-run deterministic and independent of the order rows were
+// inserted in (SURVEY 3.2 inv. 3).  The kernel is persistent and warp specialised; its structure is
+// described above k_spconv_umma below.
 #include "common.cuh"
 
 namespace pcc {
 
 constexpr int kTileM = 128;
-constexpr int kProducerThreads = 128;
-constexpr int kThreadsUmma = 160;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);
@@ -164,12 +159,9 @@ struct UmmaParams {
 constexpr int kMmaWarp = 4, kMmaWarps = 4, kLoaderWarp = 8, kProdWarp0 = 9;
 constexpr int kNbrBufs = 3;   // kernel-map ring depth (units)
 
-template <bool CG>
-__device__ __forceinline__ void cp_async16_x(uint32_t dst, const void* src, uint32_t src_bytes) {
-  if (CG)
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
-  else
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+__device__ __forceinline__ void cp_async16_ca(uint32_t dst, const void* src, uint32_t src_bytes) {
+  // .ca on purpose: with .cg (L1 bypass) the 1.79 M-row c32 layer takes 571 us instead of 363 us
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
 }
 __device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr) {
   uint32_t v;
@@ -195,12 +187,11 @@ __device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr) {
 // All hand-offs are mbarriers: groups never wait for one another.
 // Shared memory: [weights: all kvol panels (resident) | one panel per slot][A: G slots x T tiles]
 //                [kernel-map ring 3 x jc x T x 128 x 4][barriers].
-template <int CIN, int G, bool CG>
+template <int CIN, int G, int LT>
 __global__ void __launch_bounds__(32 * (kProdWarp0 + 4 * G), 1)
 k_spconv_umma(const UmmaParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   constexpr int CPR = CIN / 8;     // 16-byte chunks per row
-  constexpr int RPI = 32 / CPR;    // rows covered by one warp-wide cp.async
   // A tile layout (no-swizzle K-major core matrices of 8 rows x 16 B): chunk (row, kc) sits at
   // (row >> 3) * sbo_a + kc * lbo_a + (row & 7) * 16.  lbo_a = 144 (not 128) rotates the banks by one
   // 16-byte slot per K chunk, so the chunks of one gathered row -- which return from L1/L2 together,
@@ -212,7 +203,7 @@ k_spconv_umma(const UmmaParams p) {
   const int warp = tid >> 5;
   const int lane = tid & 31;
   const int cout = p.cout, kvol = p.kvol;
-  const int lt = p.lt, T = 1 << lt;
+  constexpr int lt = LT, T = 1 << LT;   // compile time: the tile loops unroll, dirty bits become immediates
   const uint32_t b_bytes = (uint32_t)CIN * cout * 2u;
   const uint32_t a_bytes = a_tile << lt;    // one stage: T tiles
   uint32_t base = smem_u32(smem_raw);
@@ -268,10 +259,13 @@ k_spconv_umma(const UmmaParams p) {
     }
     const int rowb = 32 * pw + rl0 * CPR;   // first of this thread's rows
     const uint32_t a_s = a0 + (uint32_t)gi * a_bytes;
+    uint32_t a_dst[CPR];
+#pragma unroll
+    for (int it = 0; it < CPR; ++it) a_dst[it] = a_s + dst_c[it];
     const uint32_t fullb = full0 + 8u * gi, emptyb = empty0 + 8u * gi;
     // chunks this thread wrote non-zero data to at the previous use of its slot (bit t*CPR + it).
     // A chunk that was zero and stays zero needs no copy at all; all ones forces the first fill.
-    uint64_t dirty = ~0ull;
+    uint32_t dirty = ~0u;         // T * CPR <= 32 bits (checked by the launcher)
     uint32_t use = 0;               // times this slot has been filled
     uint32_t j = (uint32_t)gi;      // kernel offset of the next stage
     uint32_t r = 0;                 // local round
@@ -292,41 +286,37 @@ k_spconv_umma(const UmmaParams p) {
         mbar_expect_tx(fullb, b_bytes);
         bulk_g2s(w0 + (uint32_t)gi * b_bytes, p.w + (size_t)j * b_bytes, b_bytes, fullb);
       }
-      uint64_t now = 0;
+      uint32_t now = 0;
+      const bool has_nbr = p.nbr != nullptr;
+#pragma unroll
       for (int t = 0; t < T; ++t) {
-        const int64_t tile = (rg << lt) + t;
-        const int64_t row0 = tile * kTileM;
-        const bool tile_ok = tile < p.ntiles;
         uint32_t rr[CPR];
+        if (has_nbr) {
+          // (tiles past the end of the map hold -1: the loader fills them)
+          const uint32_t ia = nb_addr + (uint32_t)(t * kTileM + rowb) * 4u;
+          if (CPR >= 4) {
 #pragma unroll
-        for (int it = 0; it < CPR; ++it) rr[it] = 0xffffffffu;
-        if (tile_ok) {
-          if (p.nbr) {
-            const uint32_t ia = nb_addr + (uint32_t)(t * kTileM + rowb) * 4u;
-            if (CPR >= 4) {
-#pragma unroll
-              for (int v4 = 0; v4 < CPR / 4; ++v4)
-                asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
-                             : "=r"(rr[4 * v4]), "=r"(rr[4 * v4 + 1]), "=r"(rr[4 * v4 + 2]), "=r"(rr[4 * v4 + 3])
-                             : "r"(ia + 16u * v4)
-                             : "memory");
-            } else {
-              asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(rr[0]), "=r"(rr[1]) : "r"(ia) : "memory");
-            }
+            for (int v4 = 0; v4 < CPR / 4; ++v4)
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                           : "=r"(rr[4 * v4]), "=r"(rr[4 * v4 + 1]), "=r"(rr[4 * v4 + 2]), "=r"(rr[4 * v4 + 3])
+                           : "r"(ia + 16u * v4)
+                           : "memory");
           } else {
-#pragma unroll
-            for (int it = 0; it < CPR; ++it)
-              if (row0 + rowb + it < p.n_out) rr[it] = (uint32_t)(row0 + rowb + it);
+            asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(rr[0]), "=r"(rr[1]) : "r"(ia) : "memory");
           }
+        } else {
+          const int64_t o0 = (((rg << lt) + t) * kTileM) + rowb;
+#pragma unroll
+          for (int it = 0; it < CPR; ++it) rr[it] = (o0 + it < p.n_out) ? (uint32_t)(o0 + it) : 0xffffffffu;
         }
 #pragma unroll
         for (int it = 0; it < CPR; ++it) {
           const bool ok = rr[it] < n_in32;
-          const uint64_t bit = 1ull << (t * CPR + it);
+          const uint32_t bit = 1u << (t * CPR + it);
           if (ok) now |= bit;
           if (ok || (dirty & bit)) {
-            const char* src = in_b + (ok ? (size_t)rr[it] * (CIN * 2) : (size_t)0);
-            cp_async16_x<CG>(a_s + (uint32_t)t * a_tile + dst_c[it], src, ok ? 16u : 0u);
+            const uint32_t rc = ok ? rr[it] : 0u;
+            cp_async16_ca(a_dst[it] + (uint32_t)t * a_tile, in_b + (size_t)rc * (CIN * 2), ok ? 16u : 0u);
           }
         }
       }
@@ -361,6 +351,12 @@ k_spconv_umma(const UmmaParams p) {
           if (unit >= kNbrBufs) mbar_wait_relaxed(nempty0 + 8u * nb, ((unit / kNbrBufs) - 1u) & 1u);
           const uint32_t dst = nbr0 + nb * unit_bytes;
           if (p.nbr_bulk) {
+            if (tv < T) {      // last round: tiles past the end of the map gather nothing
+              for (int e = lane; e < jc * T * kTileM; e += 32)
+                if (((e >> 7) & (T - 1)) >= (int)tv)
+                  asm volatile("st.shared.b32 [%0], %1;" ::"r"(dst + (uint32_t)e * 4u), "r"(-1) : "memory");
+              __syncwarp();
+            }
             if (lane == 0) {
               mbar_arrive_expect_tx(nfull0 + 8u * nb, (uint32_t)(jc * tv * kTileM * 4));
               for (int jj = 0; jj < jc; ++jj)
@@ -547,22 +543,26 @@ int pcc_spconv_pack_weights(const float* w, int kvol, int cin, int cout, int cin
 }
 
 extern "C++" {
-static int g_groups = 0, g_max_t = 4, g_cg = 0;  // g_groups 0 = by channel count
+static int g_groups = 0, g_max_t = 4;  // g_groups 0 = by channel count
 
-template <int CIN, int G, bool CG>
-static int launch_umma_gc(const UmmaParams& p, size_t smem, unsigned grid, cudaStream_t st) {
+template <int CIN, int G, int LT>
+static int launch_umma_glt(const UmmaParams& p, size_t smem, unsigned grid, cudaStream_t st) {
   static bool configured = false;
   if (!configured) {
-    PCC_CUDA(cudaFuncSetAttribute(k_spconv_umma<CIN, G, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
+    PCC_CUDA(cudaFuncSetAttribute(k_spconv_umma<CIN, G, LT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
     configured = true;
   }
-  k_spconv_umma<CIN, G, CG><<<grid, 32 * (kProdWarp0 + 4 * G), smem, st>>>(p);
+  k_spconv_umma<CIN, G, LT><<<grid, 32 * (kProdWarp0 + 4 * G), smem, st>>>(p);
   PCC_LAUNCHED();
   return PCC_OK;
 }
 template <int CIN, int G>
 static int launch_umma_g(const UmmaParams& p, size_t smem, unsigned grid, cudaStream_t st) {
-  return g_cg ? launch_umma_gc<CIN, G, true>(p, smem, grid, st) : launch_umma_gc<CIN, G, false>(p, smem, grid, st);
+  switch (p.lt) {
+    case 2: return launch_umma_glt<CIN, G, 2>(p, smem, grid, st);
+    case 1: return launch_umma_glt<CIN, G, 1>(p, smem, grid, st);
+    default: return launch_umma_glt<CIN, G, 0>(p, smem, grid, st);
+  }
 }
 template <int CIN>
 static int launch_umma(const UmmaParams& p, int groups, size_t smem, unsigned grid, cudaStream_t st) {
@@ -575,10 +575,10 @@ static int launch_umma(const UmmaParams& p, int groups, size_t smem, unsigned gr
 }  // extern "C++"
 
 int pcc_spconv_set_tuning(int groups, int max_tiles, int use_cg) {
-  PCC_CHECK_ARG(max_tiles == 1 || max_tiles == 2 || max_tiles == 4 || max_tiles == 8);
-  g_max_t = max_tiles;
-  g_cg = use_cg ? 1 : 0;
+  PCC_CHECK_ARG(max_tiles == 1 || max_tiles == 2 || max_tiles == 4);
   PCC_CHECK_ARG(groups == 0 || groups == 1 || groups == 2 || groups == 4);
+  PCC_CHECK_ARG(use_cg == 0);   // the cp.async.cg gather variant was measured slower (571 vs 363 us) and removed
+  g_max_t = max_tiles;
   g_groups = groups;
   return PCC_OK;
 }
@@ -654,7 +654,7 @@ int pcc_spconv_umma(const void* in_bf16, int64_t n_in, int cin, const int32_t* n
   }
   int T = 1, lt = 0;
   while (2 * T <= g_max_t && (uint32_t)(2 * (2 * T)) * p.acc_cols <= 512u && ntiles / (2 * T) >= 2 * sms &&
-         2 * T * (cin / 8) <= 64 &&
+         2 * T * (cin / 8) <= 32 &&
          smem_need(groups, 2 * T) <= budget) {
     T *= 2;
     ++lt;
