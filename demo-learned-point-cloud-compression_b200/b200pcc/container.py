@@ -23,8 +23,9 @@ def make_bitstream_batched(y_string: bytes, z_string: bytes, y_shape: int, z_sha
     return b"".join(parts)
 
 
-def read_bitstream_batched(data: bytes):
-    """-> y_strings, z_strings, y_shape, z_shape, points_streams, ks, q (codec_parallel.py:173-216)."""
+def read_bitstream_batched(data: bytes, copy: bool = True):
+    """-> y_strings, z_strings, y_shape, z_shape, points_streams, ks, q (codec_parallel.py:173-216).
+    copy=False returns memoryviews into `data` instead of bytes objects."""
     mv = memoryview(data)
     pos = 0
 
@@ -41,9 +42,9 @@ def read_bitstream_batched(data: bytes):
         nonlocal pos
         if n < 0 or pos + n > len(mv):
             raise ValueError("truncated bitstream")
-        b = bytes(mv[pos:pos + n])
+        b = mv[pos:pos + n]
         pos += n
-        return b
+        return bytes(b) if copy else b
 
     num_frames, q_g, q_a = take(">idd")
     y_shape, z_shape, y_len, z_len = take(">iiii")

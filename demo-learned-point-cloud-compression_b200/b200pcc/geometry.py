@@ -28,7 +28,7 @@ def encode_device(cmap):
 
 def stream_points(stream: bytes) -> int:
     """Point count stated by a stream's header."""
-    if len(stream) < 20 or stream[:4] != _MAGIC:
+    if len(stream) < 20 or bytes(stream[:4]) != _MAGIC:
         raise ValueError("bad geometry stream")
     return struct.unpack_from("<I", stream, 4)[0]
 

@@ -357,16 +357,18 @@ class _CodedModel:
         return sym, status
 
 
-def fetch_strings(pending) -> List[bytes]:
+def fetch_strings(pending, as_bytes: bool = True):
     """[(device buffer, device size)] -> [bytes] with two host syncs for the whole list: one for the
-    sizes, one for the payloads (copied through a single packed device buffer)."""
+    sizes, one for the payloads (copied through a single packed device buffer).  as_bytes=False returns
+    memoryviews over the one host copy (the container writer joins them without another copy)."""
     if not pending:
         return []
     sizes = torch.cat([nb for _, nb in pending]).cpu().numpy()
-    packed = torch.cat([buf[: int(nb)] for (buf, _), nb in zip(pending, sizes)]).cpu().numpy()
+    packed = memoryview(torch.cat([buf[: int(nb)] for (buf, _), nb in zip(pending, sizes)]).cpu().numpy())
     out, pos = [], 0
     for nb in sizes:
-        out.append(packed[pos:pos + int(nb)].tobytes())
+        v = packed[pos:pos + int(nb)]
+        out.append(v.tobytes() if as_bytes else v)
         pos += int(nb)
     return out
 
@@ -576,6 +578,7 @@ class EntropyModel:
         self.eps = float(cfg["eps"])
         self.offset_gain = np.ones(cfg["c_y"], np.float32)
         self.offset_gain_d = None
+        self._scale_cache = {}
 
     def get_offsets(self, stdev: torch.Tensor, scale: torch.Tensor) -> torch.Tensor:
         """Centroid shift (toward zero) of a unit bin for a Laplacian of std `stdev`, times the
@@ -590,8 +593,15 @@ class EntropyModel:
 
     def scale_for(self, settings, device) -> torch.Tensor:
         """[Q, Cy] gains = scale_nn(q) + eps for a list of [q_geo, q_att]."""
-        s = self.scale_nn.numpy(np.asarray(settings, dtype=np.float32)) + np.float32(self.eps)
-        return torch.from_numpy(s.astype(np.float32)).to(device)
+        key = (tuple(tuple(float(v) for v in q) for q in settings), str(device))
+        hit = self._scale_cache.get(key)
+        if hit is None:            # the gains depend on the weights and q only: evaluate once per setting list
+            s = self.scale_nn.numpy(np.asarray(settings, dtype=np.float32)) + np.float32(self.eps)
+            hit = torch.from_numpy(s.astype(np.float32)).to(device)
+            if len(self._scale_cache) > 256:
+                self._scale_cache.clear()
+            self._scale_cache[key] = hit
+        return hit
 
 
 class ColorModel:
@@ -623,6 +633,7 @@ class ColorModel:
         em.entropy_bottleneck.load(sd)
         em.scale_nn.load(sd)
         em.offset_gain = np.asarray(sd["entropy_model.offset_gain"], np.float32).copy()
+        em._scale_cache = {}
         self._sd = sd
         if self.device is not None:
             self.to(self.device)

@@ -72,7 +72,8 @@ class _Stager:
     def __init__(self):
         self.buf = None
 
-    def to_device(self, arrays: List[np.ndarray], device) -> List[torch.Tensor]:
+    def to_device(self, arrays: List[np.ndarray], device, pad4: bool = False) -> List[torch.Tensor]:
+        """pad4: uint8 arrays come back with their length rounded up to 4 (zero filled)."""
         total = sum((a.nbytes + 255) // 256 * 256 for a in arrays)
         if self.buf is None or self.buf.numel() < total:
             self.buf = torch.empty(max(total, 1 << 20), dtype=torch.uint8, pin_memory=True)
@@ -82,13 +83,16 @@ class _Stager:
         for a in arrays:
             b = np.ascontiguousarray(a).view(np.uint8).reshape(-1)
             hv[pos:pos + b.size] = b
+            hv[pos + b.size:pos + (b.size + 15) // 16 * 16] = 0      # readers may round a length up
             offs.append(pos)
             pos += (b.size + 255) // 256 * 256
         dev[:pos].copy_(self.buf[:pos], non_blocking=True)
         outs = []
         for a, o in zip(arrays, offs):
-            t = dev[o:o + a.nbytes].view(_TORCH_DT[a.dtype.name]).view(a.shape)
-            outs.append(t)
+            if pad4 and a.dtype == np.uint8 and a.ndim == 1:
+                outs.append(dev[o:o + (a.nbytes + 3) // 4 * 4])
+            else:
+                outs.append(dev[o:o + a.nbytes].view(_TORCH_DT[a.dtype.name]).view(a.shape))
         return outs
 
 
@@ -202,10 +206,11 @@ class CompressionPipeline:
             x.cmap.build_pyramid(5, nf)
             ycm = x.cmap.coarse.coarse.coarse
             tm.mark("unpack")
-            geo_pending = self.geometry_compression_step(ycm)
-            tm.mark("geometry_compression")
             y, k = self.analysis_step(x)
             tm.mark("analysis")
+            # (after the analysis transform is enqueued: its host-side preparation then overlaps GPU work)
+            geo_pending = self.geometry_compression_step(ycm)
+            tm.mark("geometry_compression")
             z = self.hyper_analysis_step(y)
             tm.mark("hyper_analysis")
             z_hat, z_pending, z_shapes = self.factorized_model_step_batched(z)
@@ -214,7 +219,7 @@ class CompressionPipeline:
             tm.mark("hyper_synthesis")
             y_pending, y_shapes = self.gaussian_model_step_batched(y, self.settings, gaussian_params)
             tm.mark("gaussian_model")
-            strings = fetch_strings(z_pending + y_pending + geo_pending)   # the GOP's two remaining syncs
+            strings = fetch_strings(z_pending + y_pending + geo_pending, as_bytes=False)   # the GOP's two remaining syncs
             z_strings, y_strings = strings[:1], strings[1:1 + len(y_pending)]
             points_streams = strings[1 + len(y_pending):]
             self.d2h_bytes += sum(len(b) for b in strings)
@@ -255,19 +260,16 @@ class DecompressionPipeline:
         self.debug = {}
 
     def read_bitstream_batched(self, compressed_data):
-        return container.read_bitstream_batched(compressed_data)
+        return container.read_bitstream_batched(compressed_data, copy=False)
 
     def stage_bitstream(self, points_streams, y_strings, z_strings):
         """One pinned staging copy for everything the decoder needs on the device: the coordinate
         streams (+ their offsets / lengths / row offsets) and the two entropy-coded strings (padded to
         4 bytes for the lane decoder).  -> (device tensors, per-frame latent point counts)."""
-        def pad4(b):
-            a = np.frombuffer(b, dtype=np.uint8)
-            p = (-len(a)) % 4
-            return np.concatenate([a, np.zeros(p, np.uint8)]) if p else a
         blob, offs, meta32, counts = geometry.pack_streams(points_streams)
-        arrays = [blob, offs, meta32, pad4(y_strings[0]), pad4(z_strings[0])]
-        dev = self._stager.to_device(arrays, self.device)
+        arrays = [blob, offs, meta32, np.frombuffer(y_strings[0], dtype=np.uint8),
+                  np.frombuffer(z_strings[0], dtype=np.uint8)]
+        dev = self._stager.to_device(arrays, self.device, pad4=True)
         self.h2d_bytes += sum(a.nbytes for a in arrays)
         return dev, counts
 

@@ -290,7 +290,21 @@ k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, in
     for (int t = threadIdx.x; t < T.T; t += blockDim.x)
       s_meta[t] = make_int4(T.off[t], T.size[t] - 2, T.offset[t], 0);
     for (int i = threadIdx.x; i < T.T * (kLutN + 1); i += blockDim.x) s_lut[i] = T.lut[i];
-    for (int i = threadIdx.x; i < T.total; i += blockDim.x) s_cdf[i] = (uint16_t)T.cdf[i];
+    // four entries per 16-byte load, batches of four independent loads in flight per thread
+    const uint4* c4 = reinterpret_cast<const uint4*>(T.cdf);
+    uint2* s4 = reinterpret_cast<uint2*>(s_cdf);
+    const int nq = (reinterpret_cast<uintptr_t>(T.cdf) & 15) == 0 ? T.total >> 2 : 0;   // unaligned table: scalar copy
+    for (int i0 = threadIdx.x; i0 < nq; i0 += 4 * blockDim.x) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (i0 + u * (int)blockDim.x < nq) v[u] = __ldg(c4 + i0 + u * blockDim.x);
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (i0 + u * (int)blockDim.x < nq)
+          s4[i0 + u * blockDim.x] = make_uint2((v[u].x & 0xffffu) | (v[u].y << 16), (v[u].z & 0xffffu) | (v[u].w << 16));
+    }
+    for (int i = (nq << 2) + threadIdx.x; i < T.total; i += blockDim.x) s_cdf[i] = (uint16_t)T.cdf[i];
     __syncthreads();
   }
   auto cdf_at = [&](int32_t coff, int32_t k) -> uint32_t {
@@ -339,11 +353,11 @@ k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, in
 #pragma unroll
     for (int k = 0; k < kChunk; ++k) {
       const int32_t li = (r0 + k) * 32 + lane;
+      // the raw value only: clamping here would make every chunk wait for its own loads
       int32_t t = -1;
       if (r0 + k < rounds && li < cnt) {
         const int64_t i = start + li;
         t = idx ? (int32_t)__ldg(idx + i) : (int32_t)(i / chan_len);
-        t = t < T.T ? t : T.T - 1;
       }
       buf[k] = t;
     }
@@ -355,8 +369,8 @@ k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, in
     for (int k = 0; k < kChunk; ++k) {
       const int32_t r = r0 + k;
       if (r >= rounds) break;
-      const int32_t t = cur[k];
-      const bool active = t >= 0;
+      const bool active = cur[k] >= 0;
+      const int32_t t = cur[k] < T.T ? cur[k] : T.T - 1;
       const int64_t i = start + r * 32 + lane;
       int32_t coff = 0, maxv = 0, offs = 0;
       if (active) {
