@@ -236,10 +236,23 @@ def coords_pyramid_expect(keys: torch.Tensor, log2_stride: int, levels: int, exp
     return kout[levels - 1, :int(expect_last)]
 
 
-def coords_pyramid(keys: torch.Tensor, log2_stride: int, levels: int, num_frames: int):
+_SIDE = {}
+
+
+def _side_stream(device) -> torch.cuda.Stream:
+    st = _SIDE.get(str(device))
+    if st is None:
+        st = _SIDE[str(device)] = torch.cuda.Stream(device=device)
+    return st
+
+
+def coords_pyramid(keys: torch.Tensor, log2_stride: int, levels: int, num_frames: int, overlap=None):
     """All `levels` stride-2 coarsenings of a sorted key set with ONE host sync.
     -> (list of level keys, list of parent_row [rows of the finer level], host counts [levels],
-        host frame offsets [(levels+1), num_frames+1] (row 0 = the input set))."""
+        host frame offsets [(levels+1), num_frames+1] (row 0 = the input set), the same on the device).
+    overlap: optional callable that enqueues independent work on the current stream; it runs after the
+    pyramid kernels are launched, and the counts are read back on a side stream, so the host wait (and
+    the host-side bookkeeping that follows) is covered by that work instead of leaving the GPU idle."""
     _need_cuda(keys, torch.int64)
     n = keys.shape[0]
     dev = keys.device
@@ -247,12 +260,26 @@ def coords_pyramid(keys: torch.Tensor, log2_stride: int, levels: int, num_frames
     par = torch.empty((levels, max(n, 1)), dtype=torch.int32, device=dev)
     nf1 = num_frames + 1
     meta = torch.empty(levels + (levels + 1) * nf1, dtype=torch.int32, device=dev)
-    ws = workspace(lib.pcc_coords_pyramid_workspace_bytes(n), dev)
+    ws = workspace(lib.pcc_coords_pyramid_workspace_bytes(n), dev, "pyramid")
     with _prof("coords_pyramid", levels * n * (8 + 4 + 8)):
         check(lib.pcc_coords_pyramid(_ptr(keys), n, log2_stride, levels, _ptr(kout), _ptr(par), _ptr(meta),
                                      num_frames, meta.data_ptr() + 4 * levels if num_frames else None, _ptr(ws),
                                      ws.numel(), _stream()))
-    host = meta.cpu().numpy()                  # the one sync
+    if overlap is None:
+        host = meta.cpu().numpy()              # the one sync
+    else:
+        ready = torch.cuda.Event()
+        ready.record()
+        overlap()
+        side = _side_stream(dev)
+        host_t = torch.empty(meta.shape, dtype=meta.dtype, pin_memory=True)
+        with torch.cuda.stream(side):
+            side.wait_event(ready)
+            host_t.copy_(meta, non_blocking=True)
+            done = torch.cuda.Event()
+            done.record()
+        done.synchronize()                     # the one sync (pyramid kernels + 100-byte copy only)
+        host = host_t.numpy()
     counts = [int(c) for c in host[:levels]]
     offs = host[levels:].reshape(levels + 1, nf1) if num_frames else None
     keys_l = [kout[l, :counts[l]] for l in range(levels)]
@@ -306,11 +333,14 @@ def kmap_k3(keys: torch.Tensor, log2_stride: int, table) -> torch.Tensor:
     return nbr
 
 
-def blockmap_build(keys: torch.Tensor, log2_stride: int):
-    """4x4x4-block table of a sorted key set -> (table keys, table values [cap, 2] int64)."""
+def blockmap_build(keys: torch.Tensor, log2_stride: int, block_bound: Optional[int] = None):
+    """4x4x4-block table of a sorted key set -> (table keys, table values [cap, 2] int64).
+    block_bound: host-known upper bound on the number of occupied blocks (= coordinates two levels
+    coarser); it sizes the table, which otherwise has to assume one block per voxel.  A compact table
+    (a few MB instead of ~100 MB at 1.8 M rows) keeps the probes of the map kernel in L2."""
     _need_cuda(keys, torch.int64)
     n = keys.shape[0]
-    cap = hash_capacity(n)
+    cap = hash_capacity(n if block_bound is None else max(min(int(block_bound), n), 1))
     tk = torch.empty(cap, dtype=torch.int64, device=keys.device)
     tv = torch.empty((cap, 2), dtype=torch.int64, device=keys.device)
     with _prof("blockmap_build", n * 8 + cap * 8 + (n // 8) * 24):   # keys read, table cleared, ~n/8 entries

@@ -203,7 +203,9 @@ class CompressionPipeline:
             num_points = x.cmap.n
             nf = x.num_frames
             # every coarser coordinate map (g_a: 3, h_a: 2) with one host sync
-            x.cmap.build_pyramid(5, nf)
+            # (the stride-1 kernel map of the stem does not depend on the pyramid: it is built while the host
+            # waits for the level sizes)
+            x.cmap.build_pyramid(5, nf, overlap=x.cmap.nbr3)
             ycm = x.cmap.coarse.coarse.coarse
             tm.mark("unpack")
             y, k = self.analysis_step(x)

@@ -32,6 +32,8 @@ class CoordMap:
         self.frame_off_host = None  # set by build_pyramid
         self.frame_off_dev = None   # int32 [num_frames+1] device row offsets (levels made by build_pyramid)
         self.frame_counts = None    # the same as host row counts
+        self.up1 = None             # host-known upper bounds on the number of coordinates one / two levels
+        self.up2 = None             # coarser (exact where the coarser maps exist); None = unknown
 
     @property
     def stride(self) -> int:
@@ -49,7 +51,10 @@ class CoordMap:
     def nbr3(self) -> torch.Tensor:
         """[27, n] kernel map of a k=3 stride-1 convolution on this map (block-table probing)."""
         if self._nbr3 is None:
-            bt = ops.blockmap_build(self.keys, self.log2_stride)
+            bound = self.up2 if self.up2 is not None else (self.up1 if self.up1 is not None else None)
+            if self.coarse is not None and self.coarse.coarse is not None:
+                bound = self.coarse.coarse.n          # occupied 4x4x4 blocks = coordinates two levels up
+            bt = ops.blockmap_build(self.keys, self.log2_stride, bound)
             self._nbr3 = ops.kmap_k3_blocks(self.keys, self.log2_stride, bt)
         return self._nbr3
 
@@ -72,7 +77,7 @@ class CoordMap:
             self.parent_row = parent
         return self.coarse
 
-    def build_pyramid(self, levels: int, num_frames: int = 0):
+    def build_pyramid(self, levels: int, num_frames: int = 0, overlap=None):
         """Precompute the next `levels` coarser maps (and per-frame row counts of every level) with a
         single host sync, instead of one sync per downsample().  Returns the host frame offsets
         [(levels+1), num_frames+1] (row 0 = this map) or None."""
@@ -81,7 +86,7 @@ class CoordMap:
             cm, have = cm.coarse, have + 1
         if have >= levels and (num_frames == 0 or self.frame_off_host is not None):
             return self.frame_off_host
-        keys_l, par_l, counts, offs, offs_dev = ops.coords_pyramid(self.keys, self.log2_stride, levels, num_frames)
+        keys_l, par_l, counts, offs, offs_dev = ops.coords_pyramid(self.keys, self.log2_stride, levels, num_frames, overlap)
         cm = self
         for l in range(levels):
             cm.coarse = CoordMap(keys_l[l], cm.log2_stride + 1)
@@ -104,11 +109,15 @@ class CoordMap:
         """Generative k=2 s=2 transposed-convolution coordinates: child row 8p + octant."""
         assert self.log2_stride >= 1
         keys = ops.coords_children(self.keys, self.log2_stride - 1)
-        return CoordMap(keys, self.log2_stride - 1)
+        cm = CoordMap(keys, self.log2_stride - 1)
+        cm.up1, cm.up2 = self.n, self.up1
+        return cm
 
     def subset(self, rows: torch.Tensor) -> "CoordMap":
         """Pruned map (rows ascending => still sorted)."""
-        return CoordMap(ops.gather_keys(self.keys, rows), self.log2_stride)
+        cm = CoordMap(ops.gather_keys(self.keys, rows), self.log2_stride)
+        cm.up1, cm.up2 = self.up1, self.up2     # still upper bounds after pruning
+        return cm
 
     def release_maps(self):
         self._table = None

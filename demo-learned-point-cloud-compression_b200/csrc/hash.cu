@@ -161,6 +161,7 @@ k_blockmap_insert(const uint64_t* __restrict__ keys, int64_t n, int shift, uint6
     }
     base = (base + kWin) & cap_mask;
   }
+  __trap();   // table full: the caller's capacity was below the number of occupied blocks
 }
 
 struct BlockEntry {
@@ -326,7 +327,7 @@ int pcc_kmap_down2(const uint64_t* child_keys, const int32_t* parent_row, int64_
 int pcc_blockmap_build(const uint64_t* keys, int64_t n, int log2_stride, uint64_t* table_keys,
                        void* table_vals16, int64_t capacity, pcc_stream_t s) {
   PCC_CHECK_ARG(n >= 0 && log2_stride >= 0 && log2_stride <= 13);
-  PCC_CHECK_ARG(capacity >= 8 && (capacity & (capacity - 1)) == 0 && capacity >= 2 * n);
+  PCC_CHECK_ARG(capacity >= 8 && (capacity & (capacity - 1)) == 0);
   PCC_CHECK_ARG(table_keys && table_vals16 && ((uintptr_t)table_vals16 % 16) == 0 &&
                 ((uintptr_t)table_keys % 32) == 0);
   cudaStream_t st = as_stream(s);

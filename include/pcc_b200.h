@@ -107,7 +107,9 @@ int pcc_kmap_k3(const uint64_t* keys, int64_t n, int log2_stride, const uint64_t
 /* Block table: the same open-addressing hash keyed on 4x4x4-voxel Morton blocks
  * (key >> (3*log2_stride + 6)); value = {64-bit occupancy mask, first row}.  Rows of a block are
  * contiguous in the sorted key set, so row(voxel idx) = base + popc(mask & ((1 << idx) - 1)).
- * table_vals16: capacity x 16 bytes.  capacity: power of two >= 2n.
+ * table_vals16: capacity x 16 bytes.  capacity: power of two >= 2 x the number of occupied blocks
+ * (<= n; the coordinates two strides coarser bound it, which keeps the table small enough to stay
+ * in L2); a table that turns out too small traps (CUDA error) instead of dropping blocks.
  * pcc_kmap_k3_blocks builds the same [27, n] kernel map as pcc_kmap_k3 with <= 8 block probes per
  * row (a 3x3x3 neighbourhood spans at most 2x2x2 blocks). */
 int pcc_blockmap_build(const uint64_t* keys, int64_t n, int log2_stride, uint64_t* table_keys,
