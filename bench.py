@@ -27,6 +27,12 @@ for _p in (ROOT, PKG_DIR):
     if _p not in sys.path:
         sys.path.insert(0, _p)
 
+if "reference" in sys.argv:
+    # the CPU arm uses every host core: torchrun exports OMP_NUM_THREADS=1, which would pin the BLAS
+    # pools of the port to one thread (must be undone before numpy is imported)
+    for _v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[_v] = str(os.cpu_count())
+
 import numpy as np  # noqa: E402
 
 METRIC = "codec Mpoints/s (enc+dec)"
@@ -88,6 +94,16 @@ def _crop_sample(frame, n_target):
     return {"points": p[sel], "colors": frame["colors"][sel]}
 
 
+def _blas_threads():
+    """Threads the numpy BLAS pool of this process actually uses (what the CPU port runs on)."""
+    try:
+        from threadpoolctl import threadpool_info
+        n = [int(p.get("num_threads", 1)) for p in threadpool_info() if p.get("user_api") == "blas"]
+        return max(n) if n else 1
+    except Exception:
+        return 1
+
+
 def cpu_port_run(frame, sample_points, reps=1):
     """Oracle port (numpy + C rANS) timed on the host cores: encode + decode of the sample."""
     from b200pcc import config as cfgmod
@@ -118,7 +134,7 @@ def run_reference(args):
     t = times[warmup:]
     total = sum(t)
     value = n * len(t) / total / 1e6
-    cores = os.cpu_count()
+    cores = _blas_threads()
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
         "warmup": warmup, "ms_per_step": 1e3 * total / len(t), "higher_is_better": True, "scaling": "weak",
@@ -146,6 +162,11 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
+    # stdout carries exactly one JSON line: libraries that print there (NCCL's version banner under
+    # torchrun) are sent to stderr for the duration of the run
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
 
     import torch
     import torch.distributed as dist
@@ -316,12 +337,12 @@ def main():
         }
         if not args.no_cpu_baseline and world == 1:
             n, times = cpu_port_run(frames[0], args.cpu_sample, reps=1)
-            line["cpu_baseline"] = {"value": n / times[0] / 1e6, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
+            line["cpu_baseline"] = {"value": n / times[0] / 1e6, "unit": UNIT, "cores": _blas_threads(), "kind": "port",
                                     "sample": f"{n}-point slab of the cfg-2 frame, encode+decode once "
                                               f"({times[0]:.1f} s; numpy BLAS threads + scalar C rANS)"}
         else:
             line["cpu_baseline"] = None
-        print(json.dumps(line))
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.destroy_process_group()
 

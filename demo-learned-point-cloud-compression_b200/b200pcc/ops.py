@@ -509,28 +509,37 @@ def spconv_umma(x: torch.Tensor, nbr: Optional[torch.Tensor], n_out: int, kvol: 
                 relu: bool = False, out_bf16: Optional[torch.Tensor] = None,
                 out_f32: Optional[torch.Tensor] = None, col0: int = 0, cstore: int = 0) -> None:
     """Writes columns [col0, col0+cout) of the given output tensors (cstore in 1..15: narrow head, only
-    the first cstore columns exist in the output)."""
-    _need_cuda(x, torch.bfloat16)
-    esz_b = 2
-    ob = None if out_bf16 is None else out_bf16.data_ptr() + col0 * esz_b
+    the first cstore columns exist in the output).  This wrapper runs ~50 times per frame: it is kept
+    free of anything that is not needed to make the call (the profiling leg is a separate branch)."""
+    if not x.is_cuda or x.dtype is not torch.bfloat16 or not x.is_contiguous():
+        raise _lib.PccError("spconv_umma: expected a contiguous CUDA bfloat16 feature matrix (there is no CPU fallback)")
+    n_in, cin = x.shape
+    ob = None if out_bf16 is None else out_bf16.data_ptr() + col0 * 2
     of = None if out_f32 is None else out_f32.data_ptr() + col0 * 4
     ldo = (out_bf16 if out_bf16 is not None else out_f32).shape[1]
     rp, ldr = None, 0
     if residual is not None:
-        rp = residual.data_ptr() + col0 * esz_b
+        rp = residual.data_ptr() + col0 * 2
         ldr = residual.shape[1]
-    cin = x.shape[1]
+    nbr_p, nbr_ld = None, 0
+    if nbr is not None:
+        nbr_ld, cs = nbr.stride()
+        if cs != 1 or nbr.dtype is not torch.int32:
+            raise _lib.PccError("kernel map must be int32 [kvol, n] with unit column stride")
+        nbr_p = nbr.data_ptr()
+    bias_p = None if bias is None else bias.data_ptr()
+    if PROFILER is None:
+        rc = lib.pcc_spconv_umma(x.data_ptr(), n_in, cin, nbr_p, nbr_ld, n_out, kvol, w_packed.data_ptr(), bias_p, cout,
+                                 rp, ldr, int(relu), ob, of, ldo, cstore, _stream())
+        if rc:
+            check(rc)
+        return
     cw = cstore if 0 < cstore < cout else cout
-    nbytes = 2 * x.shape[0] * cin + n_out * (cw * ((2 if ob else 0) + (4 if of else 0)) + cout * (2 if rp else 0)) + \
+    nbytes = 2 * n_in * cin + n_out * (cw * ((2 if ob else 0) + (4 if of else 0)) + cout * (2 if rp else 0)) + \
         (4 * kvol * n_out if nbr is not None else 0) + 2 * kvol * cin * cout
     with _prof(f"spconv_umma_k{kvol}_c{cin}x{cout}", nbytes, 2 * kvol * n_out * cin * cout):
-        nbr_ld = 0
-        if nbr is not None:
-            if nbr.stride(1) != 1 or nbr.dtype != torch.int32:
-                raise _lib.PccError("kernel map must be int32 [kvol, n] with unit column stride")
-            nbr_ld = nbr.stride(0)
-        check(lib.pcc_spconv_umma(_ptr(x), x.shape[0], x.shape[1], _ptr(nbr), nbr_ld, n_out, kvol, _ptr(w_packed),
-                                  _ptr(bias), cout, rp, ldr, int(relu), ob, of, ldo, int(cstore), _stream()))
+        check(lib.pcc_spconv_umma(x.data_ptr(), n_in, cin, nbr_p, nbr_ld, n_out, kvol, w_packed.data_ptr(), bias_p, cout,
+                                  rp, ldr, int(relu), ob, of, ldo, cstore, _stream()))
 
 
 def spconv_simt(x: torch.Tensor, nbr: Optional[torch.Tensor], n_out: int, kvol: int, w_bf16: torch.Tensor,
