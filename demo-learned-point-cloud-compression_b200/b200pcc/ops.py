@@ -4,6 +4,7 @@ torch is used for device memory and streams only: every function hands raw ``dat
 current CUDA stream to libpcc_b200.so.  Nothing here computes on the host.
 """
 import ctypes as C
+import threading
 from typing import Optional
 
 import numpy as np
@@ -12,7 +13,11 @@ import torch
 from . import _lib
 from ._lib import lib, check, CdfTables
 
-_WS = {}
+# Per-thread state.  The C calls release the GIL and most of them launch several kernels that share a
+# scratch buffer, so two callers (the containers use 3-worker pools: encoder.py:50,75, decoder.py:47)
+# must never share a workspace: another thread's kernels could be enqueued between two kernels of one
+# call.  Workspaces, the cached stream handle and the deferred-check list are therefore thread local.
+_TLS = threading.local()
 
 
 class KernelProfiler:
@@ -54,29 +59,25 @@ class _prof:
         return False
 
 
-_STREAM_CACHE = None
-
-
 def _stream() -> int:
-    if _STREAM_CACHE is not None:
-        return _STREAM_CACHE
+    st = getattr(_TLS, "stream", None)
+    if st is not None:
+        return st
     return torch.cuda.current_stream().cuda_stream
 
 
 class stream_scope:
     """Resolve the current CUDA stream once for a whole compress()/decompress() call (the per-launch
     torch.cuda.current_stream() lookup is a measurable share of the host time at ~170 launches/frame).
-    The pipelines hold their lock while inside, so the cache is not shared between callers."""
+    The cached handle is thread local."""
 
     def __enter__(self):
-        global _STREAM_CACHE
-        self.prev = _STREAM_CACHE
-        _STREAM_CACHE = torch.cuda.current_stream().cuda_stream
+        self.prev = getattr(_TLS, "stream", None)
+        _TLS.stream = torch.cuda.current_stream().cuda_stream
         return self
 
     def __exit__(self, *exc):
-        global _STREAM_CACHE
-        _STREAM_CACHE = self.prev
+        _TLS.stream = self.prev
         return False
 
 
@@ -87,12 +88,15 @@ def _ptr(t: Optional[torch.Tensor]):
 
 
 def workspace(nbytes: int, device, slot: str = "ws") -> torch.Tensor:
-    """Growing per-device scratch buffer (stream ordered reuse on the current stream)."""
+    """Growing per-thread, per-device scratch buffer (stream ordered reuse on the current stream)."""
+    ws = getattr(_TLS, "ws", None)
+    if ws is None:
+        ws = _TLS.ws = {}
     key = (str(device), slot)
-    buf = _WS.get(key)
+    buf = ws.get(key)
     if buf is None or buf.numel() < nbytes:
         buf = torch.empty(max(int(nbytes * 1.25), 1 << 20), dtype=torch.uint8, device=device)
-        _WS[key] = buf
+        ws[key] = buf
     return buf
 
 
@@ -156,17 +160,21 @@ def coords_from_keys(keys: torch.Tensor) -> torch.Tensor:
 # from the bitstream) passes it as `expect`: the op then returns without a host sync and files
 # (device count, expected value, message) here; the pipeline verifies all of them with one copy at the
 # end of the call (verify_deferred) and raises if any differs.
-_DEFERRED = []
+def _deferred_list():
+    d = getattr(_TLS, "deferred", None)
+    if d is None:
+        d = _TLS.deferred = []
+    return d
 
 
 def _defer(cnt: torch.Tensor, expect: int, what: str):
-    _DEFERRED.append((cnt, int(expect), what))
+    _deferred_list().append((cnt, int(expect), what))
 
 
 def verify_deferred(extra_status=()):
     """One device->host copy for every deferred count and status word; raises PccError on mismatch."""
-    global _DEFERRED
-    items, _DEFERRED = _DEFERRED, []
+    items = list(_deferred_list())
+    _TLS.deferred = []
     tensors = [c.reshape(1).to(torch.int32) for c, _, _ in items] + [t.reshape(1).to(torch.int32) for t, _ in extra_status]
     if not tensors:
         return
@@ -180,8 +188,7 @@ def verify_deferred(extra_status=()):
 
 
 def clear_deferred():
-    global _DEFERRED
-    _DEFERRED = []
+    _TLS.deferred = []
 
 
 def sort_unique(keys: torch.Tensor, want_src: bool = True, expect: Optional[int] = None):
