@@ -1,50 +1,144 @@
 // Per-frame top-k occupancy selection (torch.topk + MinkowskiPruning of g_s).
-// Deterministic rule: higher logit first; equal logits -> lower row (= lower key).  Implemented as one
-// stable radix sort of (frame, ~orderable(logit)) with the row as payload, a rank test against
-// k[frame], and an order-preserving compaction of the kept rows.
+// Deterministic rule: higher logit first; equal logits -> lower row (= lower key).
+// Radix select instead of a sort: four 8-bit passes over the order-preserving integer image of the
+// logits find, per frame, the value T of the k-th largest logit and the number r of rows equal to T
+// that still belong to the top k; a row is kept iff logit > T, or logit == T and fewer than r equal
+// rows precede it in its frame (exclusive scan of the tie indicator).  The kept rows leave through an
+// order-preserving compaction.  Every pass reads 4 bytes per candidate; nothing is sorted.
 #include "common.cuh"
 #include <cub/cub.cuh>
 
 namespace pcc {
 
 __device__ __forceinline__ uint32_t orderable(float f) {
+  if (f != f) f = -INFINITY;  // NaN ranks last
+  f = f + 0.0f;               // -0 == +0 (as in torch.topk)
   uint32_t u = __float_as_uint(f);
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);  // ascending in float order
 }
 
-__global__ void k_topk_keys(const float* __restrict__ logits, const uint64_t* __restrict__ keys, int64_t n,
-                            uint64_t* __restrict__ skey, int32_t* __restrict__ row) {
-  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  uint64_t b = keys[i] >> 48;
-  float l = logits[i];
-  if (l != l) l = -INFINITY;  // NaN ranks last
-  skey[i] = (b << 32) | (uint64_t)(~orderable(l));
-  row[i] = (int32_t)i;
+constexpr int kSelThreads = 256;
+constexpr int kSelPerThread = 8;
+constexpr int kSelChunk = kSelThreads * kSelPerThread;
+
+// Per-frame selection state: {prefix (threshold bits found so far), rows still to take, blocks done}
+struct SelState {
+  uint32_t prefix;
+  int32_t kleft;
+  uint32_t done;
+  uint32_t pad;
+};
+
+__global__ void k_sel_init(const int32_t* __restrict__ k, int nf, SelState* __restrict__ st, uint32_t* __restrict__ hist) {
+  const int b = blockIdx.x;
+  if (threadIdx.x == 0) {
+    st[b].prefix = 0;
+    st[b].kleft = k[b] > 0 ? k[b] : 0;
+    st[b].done = 0;
+  }
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) hist[b * 256 + i] = 0;
 }
 
-__global__ void k_topk_flags(const uint64_t* __restrict__ skey_sorted, const int32_t* __restrict__ row_sorted,
-                             int64_t n, const int32_t* __restrict__ frame_off, const int32_t* __restrict__ k,
-                             int nf, uint8_t* __restrict__ flags) {
-  int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (p >= n) return;
-  int b = (int)(skey_sorted[p] >> 32);
-  int keep = 0;
-  if (b < nf) {
-    int64_t rank = p - frame_off[b];
-    keep = rank < (int64_t)k[b];
+// grid (chunks, frames): histogram of digit `shift` among the frame's rows whose higher bits equal the
+// prefix; the last block of a frame to finish picks the digit holding the k-th largest row, updates
+// the state and clears the histogram for the next pass.
+__global__ void __launch_bounds__(kSelThreads)
+k_sel_pass(const float* __restrict__ logits, const int32_t* __restrict__ frame_off, int shift,
+           SelState* __restrict__ st, uint32_t* __restrict__ hist) {
+  __shared__ uint32_t sh[256];
+  __shared__ bool last;
+  const int b = blockIdx.y;
+  const int r0 = frame_off[b], r1 = frame_off[b + 1];
+  const int nblk = (r1 - r0 + kSelChunk - 1) / kSelChunk;
+  if ((int)blockIdx.x >= nblk) return;
+  sh[threadIdx.x] = 0;
+  __syncthreads();
+  const uint32_t prefix = st[b].prefix;
+  const int hs = shift + 8;
+  const int base = r0 + blockIdx.x * kSelChunk;
+#pragma unroll
+  for (int e = 0; e < kSelPerThread; ++e) {
+    const int i = base + e * kSelThreads + threadIdx.x;
+    uint32_t digit = 256u;   // not counted
+    if (i < r1) {
+      const uint32_t u = orderable(__ldg(logits + i));
+      if (hs >= 32 || (u >> hs) == (prefix >> hs)) digit = (u >> shift) & 255u;
+    }
+    // logits share their high digits: aggregate equal digits inside the warp before the shared atomic
+    const unsigned peers = __match_any_sync(0xffffffffu, digit);
+    if (digit < 256u && (threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&sh[digit], (uint32_t)__popc(peers));
   }
-  flags[row_sorted[p]] = (uint8_t)keep;
+  __syncthreads();
+  if (sh[threadIdx.x]) atomicAdd(&hist[b * 256 + threadIdx.x], sh[threadIdx.x]);
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) last = atomicAdd(&st[b].done, 1u) == (uint32_t)(nblk - 1);
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  sh[threadIdx.x] = __ldcg(&hist[b * 256 + threadIdx.x]);
+  hist[b * 256 + threadIdx.x] = 0;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int32_t kleft = st[b].kleft;
+    uint32_t cum = 0;
+    int d = 255;
+    for (; d > 0; --d) {
+      if ((int64_t)cum + sh[d] >= (int64_t)kleft) break;
+      cum += sh[d];
+    }
+    // d == 0 also catches k larger than the frame: everything down to the smallest digit is taken
+    st[b].prefix = prefix | ((uint32_t)d << shift);
+    st[b].kleft = kleft - (int32_t)cum;
+    st[b].done = 0;
+  }
+}
+
+// tie[i] = logit image equals the frame's threshold
+__global__ void __launch_bounds__(kSelThreads)
+k_sel_ties(const float* __restrict__ logits, const int32_t* __restrict__ frame_off, const SelState* __restrict__ st,
+           int32_t* __restrict__ tie) {
+  const int b = blockIdx.y;
+  const int r0 = frame_off[b], r1 = frame_off[b + 1];
+  const uint32_t T = st[b].prefix;
+  const int base = r0 + blockIdx.x * kSelChunk;
+  if (base >= r1) return;
+#pragma unroll
+  for (int e = 0; e < kSelPerThread; ++e) {
+    const int i = base + e * kSelThreads + threadIdx.x;
+    if (i < r1) tie[i] = orderable(__ldg(logits + i)) == T;
+  }
+}
+
+__global__ void __launch_bounds__(kSelThreads)
+k_sel_flags(const float* __restrict__ logits, const int32_t* __restrict__ frame_off, const SelState* __restrict__ st,
+            const int32_t* __restrict__ tie_scan, uint8_t* __restrict__ flags) {
+  const int b = blockIdx.y;
+  const int r0 = frame_off[b], r1 = frame_off[b + 1];
+  const int base = r0 + blockIdx.x * kSelChunk;
+  if (base >= r1) return;
+  const uint32_t T = st[b].prefix;
+  const int32_t r = st[b].kleft;
+  const int32_t t0 = tie_scan[r0];
+#pragma unroll
+  for (int e = 0; e < kSelPerThread; ++e) {
+    const int i = base + e * kSelThreads + threadIdx.x;
+    if (i < r1) {
+      const uint32_t u = orderable(__ldg(logits + i));
+      flags[i] = (uint8_t)(u > T || (u == T && tie_scan[i] - t0 < r));
+    }
+  }
 }
 
 }  // namespace pcc
 
 using namespace pcc;
 
-static size_t sort_bytes(int64_t n) {
+constexpr int64_t kMaxFrames = 4096;   // frames per call (a GOP holds a handful)
+
+static size_t scan_bytes(int64_t n) {
   size_t b = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, b, (const uint64_t*)nullptr, (uint64_t*)nullptr,
-                                  (const int32_t*)nullptr, (int32_t*)nullptr, (int)n, 0, 48);
+  cub::DeviceScan::ExclusiveSum(nullptr, b, (const int32_t*)nullptr, (int32_t*)nullptr, (int)n);
   return b;
 }
 static size_t select_bytes(int64_t n) {
@@ -58,17 +152,17 @@ extern "C" {
 
 int64_t pcc_topk_workspace_bytes(int64_t n) {
   if (n <= 0) return 256;
-  return 2 * align_up(n * 8, 256) + 2 * align_up(n * 4, 256) + align_up(n, 256) +
-         align_up((int64_t)sort_bytes(n), 256) + align_up((int64_t)select_bytes(n), 256) + 256;
+  return 2 * align_up(n * 4, 256) + align_up(n, 256) + align_up((int64_t)scan_bytes(n), 256) +
+         align_up((int64_t)select_bytes(n), 256) + align_up(kMaxFrames * (16 + 1024), 256) + 2 * 256;
 }
 
 int pcc_topk_select(const float* logits, const uint64_t* keys, int64_t n,
                     const int32_t* frame_offsets, const int32_t* k, int32_t num_frames,
                     int32_t* keep_row, int32_t* n_keep_dev, void* ws, int64_t ws_bytes,
                     pcc_stream_t s) {
-  PCC_CHECK_ARG(n >= 0 && n < (1ll << 31) && n_keep_dev && num_frames >= 0);
+  PCC_CHECK_ARG(n >= 0 && n < (1ll << 31) && n_keep_dev && num_frames >= 0 && num_frames <= kMaxFrames);
   cudaStream_t st = as_stream(s);
-  if (n == 0) {
+  if (n == 0 || num_frames == 0) {
     PCC_CUDA(cudaMemsetAsync(n_keep_dev, 0, 4, st));
     return PCC_OK;
   }
@@ -83,24 +177,33 @@ int pcc_topk_select(const float* logits, const uint64_t* keys, int64_t n,
     left -= b;
     return r;
   };
-  uint64_t* skey = (uint64_t*)take(n * 8);
-  uint64_t* skey2 = (uint64_t*)take(n * 8);
-  int32_t* row = (int32_t*)take(n * 4);
-  int32_t* row2 = (int32_t*)take(n * 4);
+  int32_t* tie = (int32_t*)take(n * 4);
+  int32_t* tie_scan = (int32_t*)take(n * 4);
   uint8_t* flags = (uint8_t*)take(n);
-  size_t sb = sort_bytes(n), fb = select_bytes(n);
+  size_t sb = scan_bytes(n), fb = select_bytes(n);
   void* sws = take((int64_t)sb);
   void* fws = take((int64_t)fb);
-  if (!skey || !skey2 || !row || !row2 || !flags || !sws || !fws) {
+  SelState* state = (SelState*)take((int64_t)num_frames * sizeof(SelState));
+  uint32_t* hist = (uint32_t*)take((int64_t)num_frames * 1024);
+  if (!tie || !tie_scan || !flags || !sws || !fws || !state || !hist) {
     set_error("pcc_topk_select: workspace too small");
     return PCC_E_WORKSPACE;
   }
-  unsigned grid = (unsigned)((n + 255) / 256);
-  k_topk_keys<<<grid, 256, 0, st>>>(logits, keys, n, skey, row);
+  // rows of frames >= num_frames (none in a well-formed batch) are dropped
+  PCC_CUDA(cudaMemsetAsync(flags, 0, (size_t)n, st));
+  PCC_CUDA(cudaMemsetAsync(tie, 0, (size_t)n * 4, st));
+  const dim3 grid((unsigned)((n + kSelChunk - 1) / kSelChunk), (unsigned)num_frames);
+  k_sel_init<<<(unsigned)num_frames, 256, 0, st>>>(k, num_frames, state, hist);
   PCC_LAUNCHED();
-  PCC_CUDA(cub::DeviceRadixSort::SortPairs(sws, sb, skey, skey2, row, row2, (int)n, 0, 48, st));
+  for (int shift = 24; shift >= 0; shift -= 8) {
+    k_sel_pass<<<grid, kSelThreads, 0, st>>>(logits, frame_offsets, shift, state, hist);
+    PCC_LAUNCHED();
+  }
+  k_sel_ties<<<grid, kSelThreads, 0, st>>>(logits, frame_offsets, state, tie);
+  PCC_LAUNCHED();
+  PCC_CUDA(cub::DeviceScan::ExclusiveSum(sws, sb, tie, tie_scan, (int)n, st));
   g_launches.fetch_add(1);
-  k_topk_flags<<<grid, 256, 0, st>>>(skey2, row2, n, frame_offsets, k, num_frames, flags);
+  k_sel_flags<<<grid, kSelThreads, 0, st>>>(logits, frame_offsets, state, tie_scan, flags);
   PCC_LAUNCHED();
   PCC_CUDA(cub::DeviceSelect::Flagged(fws, fb, cub::CountingInputIterator<int32_t>(0), flags, keep_row,
                                       n_keep_dev, (int)n, st));

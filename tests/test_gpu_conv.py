@@ -222,3 +222,40 @@ def test_topk_select(cloud, dev):
     ref = np.nonzero(S.topk_mask(logits, Ck, ks))[0]
     assert np.array_equal(keep, ref)
     assert len(keep) == sum(ks)
+
+
+@pytest.mark.parametrize("case", ["k0", "kbig", "allequal", "nan_negzero", "emptyframe", "large"])
+def test_topk_select_edge_cases(dev, case):
+    """Radix select vs the oracle's sort on the cases a sort handles implicitly."""
+    from b200pcc import ops
+    rng = np.random.default_rng(len(case))
+    n0, n1 = (400_000, 300_000) if case == "large" else (3000, 2500)
+    pts = np.unique(rng.integers(-60 if case != "large" else -400, 60 if case != "large" else 400, (n0 + n1, 3)), axis=0)
+    nf = 3
+    b = np.where(np.arange(len(pts)) < len(pts) // 2, 0, 2 if case == "emptyframe" else 1)
+    C = np.concatenate([b[:, None], pts], axis=1).astype(np.int32)
+    keys, _ = ops.sort_unique(ops.keys_from_coords(torch.from_numpy(C).to(dev)))
+    Ck = ops.coords_from_keys(keys).cpu().numpy()
+    n = len(Ck)
+    logits = rng.normal(0, 2, n).astype(np.float32)
+    cnt = np.bincount(Ck[:, 0], minlength=nf)
+    ks = [int(cnt[0] // 3), int(cnt[1] // 2), int(cnt[2] // 4)]
+    if case == "k0":
+        ks = [0, int(cnt[1]), 0]
+    elif case == "kbig":
+        ks = [int(cnt[0]) + 5, 10 * n, 1]
+    elif case == "allequal":
+        logits[:] = 1.5
+    elif case == "nan_negzero":
+        logits[::3] = np.nan
+        logits[1::5] = -0.0
+        logits[2::5] = 0.0
+        ks = [int(cnt[0] * 0.8), int(cnt[1] * 0.8), 0]
+    elif case == "large":
+        logits = np.round(logits, 1)          # heavy ties at every threshold
+    off = ops.frame_offsets(keys, nf)
+    keep = ops.topk_select(torch.from_numpy(logits).to(dev), keys, off,
+                           torch.tensor(ks, dtype=torch.int32, device=dev), nf).cpu().numpy()
+    ref = np.nonzero(S.topk_mask(logits, Ck, ks))[0]
+    assert np.array_equal(keep, ref)
+    assert len(keep) == sum(min(k, int(c)) for k, c in zip(ks, cnt))
