@@ -22,11 +22,17 @@ import torch
 
 from . import ops
 from . import config as cfgmod
+from . import program as prg
 from .sparse import CoordMap, SparseTensor
 
 SCALE_MIN, SCALE_MAX, SCALE_LEVELS = 0.11, 256.0, 64
 SCALE_BOUND = 0.11
 TAIL_MASS = 1e-9
+
+# Run whole transforms as launch programs (program.py) instead of one Python call per layer.  The
+# per-layer path stays: it is the readable statement of the graph, serves return_intermediates and
+# degenerate (empty) inputs, and the tests require both paths to agree bit for bit.
+USE_PROGRAMS = True
 
 
 def _pad16(c: int) -> int:
@@ -184,6 +190,12 @@ class AnalysisTransform(_Module):
         # level in one go: coordinates do not depend on features, so this costs one host sync in total
         nlev = len(self.down)
         offs_h = cm.build_pyramid(nlev + 2, num_frames)
+        if USE_PROGRAMS and offs_h is not None and cm.n > 0:
+            yf, cm = self._program(f, cm, nlev)
+            counts = [list(map(int, np.diff(offs_h[i]))) for i in range(nlev)]
+            y = SparseTensor(_cmap=cm, _feats=yf, _channels=self.cfg["c_y"])
+            y.num_frames = num_frames
+            return y, counts[::-1]
         f = self.stem(f, cm.nbr3(), cm.n, relu=True)
         for i in range(nlev):
             coarse = cm.downsample()
@@ -202,6 +214,38 @@ class AnalysisTransform(_Module):
         y = SparseTensor(_cmap=cm, _feats=yf, _channels=self.cfg["c_y"])
         y.num_frames = num_frames
         return y, k
+
+
+def _block_bound(cm):
+    if cm.coarse is not None and cm.coarse.coarse is not None:
+        return cm.coarse.coarse.n
+    return cm.up2 if cm.up2 is not None else cm.up1
+
+
+def _analysis_program(self, f, cm, nlev):
+    """g_a as one launch program: stem, then per level kmap_down2 + down conv + block table + k3 map +
+    the residual blocks, then the 1x1 head.  -> (y features fp32 tensor, stride-8 CoordMap)."""
+    pr = prg.Program(f.device)
+    nbr0 = cm.nbr3()
+    cur = pr.alloc(cm.n * self.stem.cout * 2)
+    pr.conv(self.stem, f.data_ptr(), cm.n, nbr0.data_ptr(), nbr0.stride(0), cm.n, out_bf16=cur, relu=True)
+    for i in range(nlev):
+        coarse = cm.coarse
+        nd, ld = pr.kmap_down2(cm)
+        c = self.down[i].cout
+        o = pr.alloc(coarse.n * c * 2)
+        pr.conv(self.down[i], cur, cm.n, nd, ld, coarse.n, out_bf16=o, relu=True)
+        cm, cur = coarse, o
+        nb, ld3 = pr.kmap_k3(cm.keys.data_ptr(), cm.n, cm.log2_stride, _block_bound(cm))
+        cur = pr.resblocks(self.blocks[i], cur, cm.n, c, nb, ld3)
+    yf = torch.empty((cm.n, self.cfg["c_y"]), dtype=torch.float32, device=f.device)
+    pr.conv(self.head, cur, cm.n, 0, 0, cm.n, out_f32=yf.data_ptr())
+    pr.keep += [f, nbr0, yf]
+    pr.run()
+    return yf, cm
+
+
+AnalysisTransform._program = _analysis_program
 
 
 class SynthesisTransform(_Module):
@@ -242,6 +286,10 @@ class SynthesisTransform(_Module):
         num_frames = len(k[0])
         dev = cm.device
         f = y_hat.feats_bf16(self.pre.cin_pad)
+        if USE_PROGRAMS and not return_intermediates and getattr(y_hat, "frame_counts", None) is not None and cm.n > 0:
+            out = self._program(f, cm, k, num_frames, list(y_hat.frame_counts))
+            if out is not None:
+                return out
         f = self.pre(f, None, cm.n, relu=True)
         inter = []
         prev = getattr(y_hat, "frame_counts", None)
@@ -274,6 +322,76 @@ class SynthesisTransform(_Module):
         return out
 
 
+def _synthesis_program(self, f, cm, k, num_frames, prev):
+    """g_s as one launch program (decoder: every kept-row count follows from k and the per-frame latent
+    counts, so all sizes are known on the host).  Per level: generative up-conv, children coordinates,
+    block table + k3 map, residual blocks, occupancy head, per-frame top-k, prune; then the colour head.
+    Returns None when a level would be empty (the per-layer path handles degenerate inputs)."""
+    dev = f.device
+    kept_l, n_l = [], []
+    n = cm.n
+    for i in range(3):
+        kept = [max(0, min(int(k[i][b]), 8 * int(prev[b]))) for b in range(num_frames)]
+        if sum(kept) == 0:
+            return None
+        kept_l.append(kept)
+        n_l.append(8 * n)
+        n, prev = sum(kept), kept
+    pr = prg.Program(dev)
+    kd_all = torch.tensor([list(map(int, k[i])) for i in range(3)], dtype=torch.int32).to(dev, non_blocking=True)
+    counts = torch.empty(3, dtype=torch.int32, device=dev)
+    n = cm.n
+    cur = pr.alloc(n * self.pre.cout * 2)
+    pr.conv(self.pre, f.data_ptr(), n, 0, 0, n, out_bf16=cur, relu=True)
+    keys_ptr, l2, up1, up2 = cm.keys.data_ptr(), cm.log2_stride, cm.up1, cm.up2
+    out_keys = None
+    for i in range(3):
+        up = self.up[i]
+        c = up.cout
+        cur = pr.gen_up(up, cur, n, relu=True)
+        nc = 8 * n
+        ck = pr.alloc(nc * 8)
+        l2 -= 1
+        pr.add(prg.OP_COORDS_CHILDREN, keys_ptr, n, l2, ck)
+        up1, up2 = n, up1
+        nb, ld = pr.kmap_k3(ck, nc, l2, up2 if up2 is not None else up1)
+        cur = pr.resblocks(self.blocks[i], cur, nc, c, nb, ld)
+        logits = pr.alloc(nc * 4)
+        pr.conv(self.occ[i], cur, nc, nb, ld, nc, out_f32=logits)
+        off = pr.alloc((num_frames + 1) * 4)
+        pr.add(prg.OP_FRAME_OFFSETS, ck, nc, num_frames, off)
+        m = sum(kept_l[i])
+        keep = pr.alloc(nc * 4)
+        wsb = int(prg.lib.pcc_topk_workspace_bytes(nc))
+        ws = pr.alloc(wsb)
+        pr.add(prg.OP_TOPK_SELECT, logits, ck, nc, off, kd_all[i].data_ptr(), num_frames, keep,
+               counts.data_ptr() + 4 * i, ws, wsb)
+        ops._defer(counts[i], m, "topk_select")
+        if i == 2:
+            out_keys = torch.empty(m, dtype=torch.int64, device=dev)
+            pk = out_keys.data_ptr()
+        else:
+            pk = pr.alloc(m * 8)
+        pr.add(prg.OP_GATHER_KEYS, ck, keep, m, pk)
+        pf = pr.alloc(m * c * 2)
+        pr.add(prg.OP_GATHER_ROWS_BF16, cur, c, keep, m, pf)
+        keys_ptr, n, cur = pk, m, pf
+    nb, ld = pr.kmap_k3(keys_ptr, n, l2, up2 if up2 is not None else up1)
+    colors = torch.empty((n, 3), dtype=torch.float32, device=dev)
+    pr.conv(self.color, cur, n, nb, ld, n, out_f32=colors.data_ptr())
+    pr.keep += [f, kd_all, counts, out_keys, colors]
+    pr.run()
+    ocm = CoordMap(out_keys, l2)
+    ocm.up1, ocm.up2 = up1, up2
+    out = SparseTensor(_cmap=ocm, _feats=colors, _channels=3)
+    out.num_frames = num_frames
+    out.frame_counts = kept_l[2]
+    return out
+
+
+SynthesisTransform._program = _synthesis_program
+
+
 class HyperAnalysis(_Module):
     def __init__(self, cfg):
         self.down0 = Conv("entropy_model.h_a.down0", 8, cfg["c_y"], cfg["c_h"])
@@ -282,6 +400,25 @@ class HyperAnalysis(_Module):
 
     def __call__(self, y: SparseTensor) -> SparseTensor:
         cm = y.cmap
+        if (USE_PROGRAMS and y._feats.dtype == torch.float32 and y._feats.is_contiguous() and cm.n > 0
+                and cm.coarse is not None and cm.coarse.coarse is not None and cm.coarse.coarse.n > 0):
+            c1, c2 = cm.coarse, cm.coarse.coarse
+            pr = prg.Program(y._feats.device)
+            cp = self.down0.cin_pad
+            f = pr.alloc(cm.n * cp * 2)
+            pr.add(prg.OP_ROWS_F32_TO_BF16, y._feats.data_ptr(), y._feats.shape[1], 0, cm.n, f, cp)
+            nd, ld = pr.kmap_down2(cm)
+            h = pr.alloc(c1.n * self.down0.cout * 2)
+            pr.conv(self.down0, f, cm.n, nd, ld, c1.n, out_bf16=h, relu=True)
+            nd, ld = pr.kmap_down2(c1)
+            z = torch.empty((c2.n, self.cfg["c_z"]), dtype=torch.float32, device=y._feats.device)
+            pr.conv(self.down1, h, c1.n, nd, ld, c2.n, out_f32=z.data_ptr())
+            pr.keep += [y._feats, z]
+            pr.run()
+            out = SparseTensor(_cmap=c2, _feats=z, _channels=self.cfg["c_z"])
+            if hasattr(y, "num_frames"):
+                out.num_frames = y.num_frames
+            return out
         f = y.feats_bf16(self.down0.cin_pad)
         c1 = cm.downsample()
         f = self.down0(f, cm.nbr_down(), c1.n, relu=True)
@@ -303,6 +440,23 @@ class HyperSynthesis(_Module):
     def __call__(self, z_hat: SparseTensor) -> SparseTensor:
         cm = z_hat.cmap
         f = z_hat.feats_bf16(self.up0.cin_pad)
+        if USE_PROGRAMS and cm.n > 0:
+            dev = f.device
+            pr = prg.Program(dev)
+            n = cm.n
+            h = pr.gen_up(self.up0, f.data_ptr(), n, relu=True)
+            k1 = pr.alloc(8 * n * 8)
+            pr.add(prg.OP_COORDS_CHILDREN, cm.keys.data_ptr(), n, cm.log2_stride - 1, k1)
+            h = pr.gen_up(self.up1, h, 8 * n, relu=True)
+            k2 = torch.empty(64 * n, dtype=torch.int64, device=dev)
+            pr.add(prg.OP_COORDS_CHILDREN, k1, 8 * n, cm.log2_stride - 2, k2.data_ptr())
+            p = torch.empty((64 * n, 2 * self.cfg["c_y"]), dtype=torch.float32, device=dev)
+            pr.conv(self.head, h, 64 * n, 0, 0, 64 * n, out_f32=p.data_ptr())
+            pr.keep += [f, k2, p]
+            pr.run()
+            ocm = CoordMap(k2, cm.log2_stride - 2)
+            ocm.up1, ocm.up2 = 8 * n, n
+            return SparseTensor(_cmap=ocm, _feats=p, _channels=2 * self.cfg["c_y"])
         f = self.up0(f, relu=True)
         cm = cm.children()
         f = self.up1(f, relu=True)

@@ -293,6 +293,29 @@ int pcc_rans_decode(const uint8_t* container, int64_t container_bytes, int32_t s
                     const pcc_cdf_tables_t* tables, int32_t* sym, int32_t* status_dev,
                     pcc_stream_t s);
 
+/* ------------------------------------------------------------------------------------------
+ * (5) launch sequencer: a whole transform as one call (replaces the per-layer
+ *     Python dispatch of codec_pipeline.py:273-354 / codec_parallel.py:302-469 and the thread-per-
+ *     stage queues of codec_pipeline.py:31-54).  Entry i runs the function named by `op` with the
+ *     arguments a[0..] in that function's own order (pointers as integers, stream omitted), all on
+ *     stream s.  Stops at the first failing entry (its index in *failed_op, else -1).
+ * ------------------------------------------------------------------------------------------ */
+#define PCC_OP_SPCONV_UMMA 1
+#define PCC_OP_KMAP_DOWN2 2
+#define PCC_OP_BLOCKMAP_BUILD 3
+#define PCC_OP_KMAP_K3_BLOCKS 4
+#define PCC_OP_ROWS_F32_TO_BF16 5
+#define PCC_OP_COORDS_CHILDREN 6
+#define PCC_OP_GATHER_ROWS_BF16 7
+#define PCC_OP_GATHER_KEYS 8
+#define PCC_OP_FRAME_OFFSETS 9
+#define PCC_OP_TOPK_SELECT 10
+typedef struct {
+  int64_t op;
+  int64_t a[19];
+} pcc_op_t;
+int pcc_run_program(const pcc_op_t* ops, int32_t n_ops, pcc_stream_t s, int32_t* failed_op);
+
 #ifdef __cplusplus
 }
 #endif

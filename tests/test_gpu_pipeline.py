@@ -134,3 +134,24 @@ def test_synthesis_stagewise_vs_oracle(model, dev, frames):
     exp = set(map(tuple, C_ref))
     agree = len(got & exp) / len(exp)
     assert agree > 0.97, agree
+
+
+def test_launch_programs_equal_per_layer_path(model, dev, frames):
+    """pcc_run_program (whole transforms as one call) vs one Python call per layer: identical
+    bitstreams and reconstructions, bit for bit."""
+    from b200pcc import model as M
+    from b200pcc.pipeline import CompressionPipeline, DecompressionPipeline
+    enc = CompressionPipeline([[1.0, 1.0], [0.25, 0.5]], device=dev, model=model)
+    dec = DecompressionPipeline(device=dev, model=model)
+    res = {}
+    try:
+        for flag in (True, False):
+            M.USE_PROGRAMS = flag
+            comp, _ = enc.compress(_gop(frames))
+            out, _ = dec.decompress(comp[1])
+            res[flag] = (comp, out)
+    finally:
+        M.USE_PROGRAMS = True
+    assert res[True][0][1] == res[False][0][1] and res[True][0][2] == res[False][0][2]
+    for a, b in zip(res[True][1], res[False][1]):
+        assert np.array_equal(a["points"], b["points"]) and np.array_equal(a["colors"], b["colors"])
