@@ -42,6 +42,8 @@ SIGNATURES = {
     "pcc_keys_from_coords_i32": (INT, [P, I64, P, P]),
     "pcc_keys_from_coords_f32": (INT, [P, I64, P, P]),
     "pcc_ingest_frame": (INT, [P, P, I64, I32, P, P, P]),
+    "pcc_ingest_points": (INT, [P, I64, I32, P, P]),
+    "pcc_ingest_features": (INT, [P, P, I64, P, INT, P]),
     "pcc_unpack_output": (INT, [P, P, I64, P, P, P]),
     "pcc_coords_from_keys": (INT, [P, I64, P, P]),
     "pcc_sort_unique_workspace_bytes": (I64, [I64]),

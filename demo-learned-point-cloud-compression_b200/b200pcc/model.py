@@ -287,7 +287,7 @@ class SynthesisTransform(_Module):
         dev = cm.device
         f = y_hat.feats_bf16(self.pre.cin_pad)
         if USE_PROGRAMS and not return_intermediates and getattr(y_hat, "frame_counts", None) is not None and cm.n > 0:
-            out = self._program(f, cm, k, num_frames, list(y_hat.frame_counts))
+            out = self._program(f, cm, k, num_frames, list(y_hat.frame_counts), getattr(y_hat, "on_geometry", None))
             if out is not None:
                 return out
         f = self.pre(f, None, cm.n, relu=True)
@@ -322,7 +322,7 @@ class SynthesisTransform(_Module):
         return out
 
 
-def _synthesis_program(self, f, cm, k, num_frames, prev):
+def _synthesis_program(self, f, cm, k, num_frames, prev, on_geometry=None):
     """g_s as one launch program (decoder: every kept-row count follows from k and the per-frame latent
     counts, so all sizes are known on the host).  Per level: generative up-conv, children coordinates,
     block table + k3 map, residual blocks, occupancy head, per-frame top-k, prune; then the colour head.
@@ -376,6 +376,9 @@ def _synthesis_program(self, f, cm, k, num_frames, prev):
         pf = pr.alloc(m * c * 2)
         pr.add(prg.OP_GATHER_ROWS_BF16, cur, c, keep, m, pf)
         keys_ptr, n, cur = pk, m, pf
+    if on_geometry is not None:
+        pr.flush()                 # the geometry is final here: the caller may start shipping it
+        on_geometry(out_keys)
     nb, ld = pr.kmap_k3(keys_ptr, n, l2, up2 if up2 is not None else up1)
     colors = torch.empty((n, 3), dtype=torch.float32, device=dev)
     pr.conv(self.color, cur, n, nb, ld, n, out_f32=colors.data_ptr())

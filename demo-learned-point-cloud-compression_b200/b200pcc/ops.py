@@ -135,15 +135,30 @@ def ingest_frame(points_i16: torch.Tensor, colors_f64: torch.Tensor, batch: int,
                                _stream()))
 
 
-def unpack_output(keys: torch.Tensor, feats3: torch.Tensor):
-    """-> (points int32 [n,3], colours float32 [n,3] clipped like the reference's pack_batches)."""
+def ingest_points(points_i16: torch.Tensor, batch: int, keys_out: torch.Tensor) -> None:
+    _need_cuda(points_i16, torch.int16)
+    check(lib.pcc_ingest_points(_ptr(points_i16), points_i16.shape[0], batch, _ptr(keys_out), _stream()))
+
+
+def ingest_features(colors_f64: torch.Tensor, src_row: Optional[torch.Tensor], m: int, c_dst: int = 16) -> torch.Tensor:
+    """bf16 feature rows (1,r,g,b,0...) [m, c_dst] of the colour rows src_row[i]."""
+    _need_cuda(colors_f64, torch.float64)
+    out = torch.empty((m, c_dst), dtype=torch.bfloat16, device=colors_f64.device)
+    check(lib.pcc_ingest_features(_ptr(colors_f64), _ptr(src_row), m, _ptr(out), c_dst, _stream()))
+    return out
+
+
+def unpack_output(keys: torch.Tensor, feats3: Optional[torch.Tensor], want_points: bool = True):
+    """-> (points int32 [n,3] or None, colours float32 [n,3] clipped like the reference's pack_batches, or
+    None when feats3 is None)."""
     _need_cuda(keys, torch.int64)
-    _need_cuda(feats3, torch.float32)
     n = keys.shape[0]
-    if feats3.shape != (n, 3):
-        raise _lib.PccError(f"unpack_output: expected [{n}, 3] colours, got {tuple(feats3.shape)}")
-    pts = torch.empty((n, 3), dtype=torch.int32, device=keys.device)
-    col = torch.empty((n, 3), dtype=torch.float32, device=keys.device)
+    if feats3 is not None:
+        _need_cuda(feats3, torch.float32)
+        if feats3.shape != (n, 3):
+            raise _lib.PccError(f"unpack_output: expected [{n}, 3] colours, got {tuple(feats3.shape)}")
+    pts = torch.empty((n, 3), dtype=torch.int32, device=keys.device) if want_points else None
+    col = torch.empty((n, 3), dtype=torch.float32, device=keys.device) if feats3 is not None else None
     check(lib.pcc_unpack_output(_ptr(keys), _ptr(feats3), n, _ptr(pts), _ptr(col), _stream()))
     return pts, col
 
@@ -191,7 +206,7 @@ def clear_deferred():
     _TLS.deferred = []
 
 
-def sort_unique(keys: torch.Tensor, want_src: bool = True, expect: Optional[int] = None):
+def sort_unique(keys: torch.Tensor, want_src: bool = True, expect: Optional[int] = None, sync: bool = True):
     """-> (unique sorted keys, src_row or None).  One host sync for the count, none with `expect`."""
     _need_cuda(keys, torch.int64)
     n = keys.shape[0]
@@ -206,6 +221,8 @@ def sort_unique(keys: torch.Tensor, want_src: bool = True, expect: Optional[int]
     if expect is not None:
         m = int(expect)
         _defer(cnt, m, "sort_unique")
+    elif not sync:
+        return out, src, cnt             # the caller reads cnt when it needs the size
     else:
         m = int(cnt.item())
     return out[:m], (src[:m] if want_src else None)
@@ -246,10 +263,12 @@ def coords_pyramid_expect(keys: torch.Tensor, log2_stride: int, levels: int, exp
 _SIDE = {}
 
 
-def _side_stream(device) -> torch.cuda.Stream:
-    st = _SIDE.get(str(device))
+def _side_stream(device, name: str = "readback") -> torch.cuda.Stream:
+    """Side streams per device: "readback" (small device->host copies the host waits for) and "h2d"
+    (bulk host->device copies) are separate so a 20 MB copy never sits in front of a 100-byte one."""
+    st = _SIDE.get((str(device), name))
     if st is None:
-        st = _SIDE[str(device)] = torch.cuda.Stream(device=device)
+        st = _SIDE[(str(device), name)] = torch.cuda.Stream(device=device)
     return st
 
 

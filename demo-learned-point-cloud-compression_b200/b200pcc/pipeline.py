@@ -121,6 +121,67 @@ class _Stager:
         return outs
 
 
+import os as _os
+_STAGE_PIECE = int(_os.environ.get("PCC_STAGE_PIECE_MB", "6")) << 20      # host copy and DMA are pipelined in pieces of about this size
+_STAGE_MODE = _os.environ.get("PCC_STAGE_MODE", "split")
+
+
+def _stage_concat(stager: "_Stager", arrays: List[np.ndarray], torch_dtype, width: int, dev_buf: torch.Tensor, stream=None,
+                  after=None, background=False):
+    """Rows of all arrays back to back through pinned memory into dev_buf (viewed [rows, width]), on
+    `stream` (after event `after`) when given, else on the current stream.  The host copy into pinned
+    memory and the DMA run at similar speeds, so the data moves in pieces: each worker thread copies a
+    piece and enqueues its DMA itself, and the bus is busy while the next pieces are being copied.
+    -> (device view, completion event or None)."""
+    global _COPY_POOL
+    total = sum(a.nbytes for a in arrays)
+    if stager.buf is None or stager.buf.numel() < total:
+        stager.buf = torch.empty(max(total, 1 << 20), dtype=torch.uint8, pin_memory=True)
+    hv = stager.buf.numpy()
+    pinned = stager.buf
+    st = stream if stream is not None else torch.cuda.current_stream()
+    if stream is not None and after is not None:
+        stream.wait_event(after)
+    jobs, pos = [], 0
+    for a in arrays:
+        b = a.view(np.uint8).reshape(-1)
+        for o in range(0, b.size, _STAGE_PIECE):
+            jobs.append((b, o, min(o + _STAGE_PIECE, b.size), pos))
+        pos += b.size
+
+    def job(j):
+        b, o, e, base = j
+        hv[base + o:base + e] = b[o:e]
+        with torch.cuda.stream(st):
+            dev_buf[base + o:base + e].copy_(pinned[base + o:base + e], non_blocking=True)
+    view = dev_buf[:total].view(torch_dtype).view(-1, width)
+    if _COPY_POOL is None:
+        from concurrent.futures import ThreadPoolExecutor
+        _COPY_POOL = ThreadPoolExecutor(max_workers=_COPY_THREADS, thread_name_prefix="b200pcc-stage")
+    if background:
+        # the caller keeps enqueuing GPU work while the workers copy; wait() joins them and returns the
+        # event that marks the last DMA
+        futures = [_COPY_POOL.submit(job, j) for j in jobs]
+
+        def wait():
+            for f in futures:
+                f.result()
+            ev = torch.cuda.Event()
+            ev.record(st)
+            return ev
+        return view, wait
+    if len(jobs) <= 1:
+        for j in jobs:
+            job(j)
+    else:
+        list(_COPY_POOL.map(job, jobs))
+    done = None
+    if stream is not None:
+        done = torch.cuda.Event()
+        done.record(stream)
+    return view, done
+
+
 _TORCH_DT = {"int16": torch.int16, "float64": torch.float64, "int32": torch.int32, "float32": torch.float32,
              "uint8": torch.uint8, "int64": torch.int64}
 
@@ -132,7 +193,7 @@ class CompressionPipeline:
         self.compression_model = model if model is not None else _shared_model(self.device, config)
         self._lock = threading.Lock()
         self._stager = _Stager()
-        self._copy_stream = None
+        self._stager_c = _Stager()      # colours have their own pinned buffer (copied while the points are in flight)
         self.h2d_bytes = 0
         self.d2h_bytes = 0
         self.keep_debug = False     # tests: keep stage tensors of the last call in self.debug
@@ -152,10 +213,56 @@ class CompressionPipeline:
         nf = len(pts)
         return {"points": staged[:nf], "colors": staged[nf:]}
 
-    def unpack_batch(self, gop, staged=None):
+    def _unpack_host_frames(self, frames, defer_features):
+        """Host frames -> sparse tensor with the copies pipelined against the coordinate work: the points
+        (20 % of the bytes) go first and their keys are sorted while the host is still copying the float64
+        colours into pinned memory; the colours travel on a side stream and are only waited for when the
+        feature rows are built (after the coordinate pyramid when defer_features is set)."""
+        pts, cols = [], []
+        for item in frames:
+            if "points" not in item:      # "Sometimes we miss a frame?" (codec_pipeline.py:247-249)
+                continue
+            pts.append(np.ascontiguousarray(item["points"], dtype=np.int16))
+            cols.append(np.ascontiguousarray(item["colors"], dtype=np.float64))
+        nf = len(pts)
+        counts = [int(p.shape[0]) for p in pts]
+        total = sum(counts)
+        dev = self.device
+        pts_buf = torch.empty(max(total * 6, 8), dtype=torch.uint8, device=dev)
+        cols_buf = torch.empty(max(total * 24, 8), dtype=torch.uint8, device=dev)
+        keys = torch.empty(total, dtype=torch.int64, device=dev)
+        allocated = torch.cuda.Event()
+        allocated.record()
+        pts_d, _ = _stage_concat(self._stager, pts, torch.int16, 3, pts_buf)
+        pos = 0
+        for b in range(nf):
+            ops.ingest_points(pts_d[pos:pos + counts[b]], b, keys[pos:pos + counts[b]])
+            pos += counts[b]
+        ukeys_all, src_all, cnt = ops.sort_unique(keys, want_src=True, sync=False)
+        cols_d, arrived = _stage_concat(self._stager_c, cols, torch.float64, 3, cols_buf, stream=ops._side_stream(dev, "h2d"),
+                                        after=allocated, background=True)
+        self.h2d_bytes += total * 30
+        m = int(cnt.item())
+        x = SparseTensor(_cmap=CoordMap(ukeys_all[:m], 0), _feats=None, _channels=4)
+        x.num_frames = nf
+        src = src_all[:m]
+
+        def finish_features():
+            torch.cuda.current_stream().wait_event(arrived())      # joins the copy workers
+            x._feats = ops.ingest_features(cols_d, src, m, 16)
+        if defer_features:
+            x._finish_features = finish_features
+        else:
+            finish_features()
+        return x
+
+    def unpack_batch(self, gop, staged=None, defer_features=False):
         """frames list -> batched sparse tensor (codec_pipeline.py:239-267, shared/utils.py:10-42).
-        `staged` (from stage_frames) skips the host->device copy: inputs already resident in HBM."""
+        `staged` (from stage_frames) skips the host->device copy: inputs already resident in HBM.
+        defer_features: the caller runs x._finish_features() once it needs the feature rows."""
         frames = gop.pop("frames")
+        if staged is None and _STAGE_MODE != "simple":
+            return self._unpack_host_frames(frames, defer_features), gop
         if staged is None:
             staged = self.stage_frames(frames)
         pts, cols = staged["points"], staged["colors"]
@@ -224,7 +331,7 @@ class CompressionPipeline:
             compressed_data = {0: data["frames"]}
             tm = _StageTimer()
             tm.mark("start")
-            x, sideinfo = self.unpack_batch(data, staged)
+            x, sideinfo = self.unpack_batch(data, staged, defer_features=True)
             num_points = x.cmap.n
             nf = x.num_frames
             # every coarser coordinate map (g_a: 3, h_a: 2) with one host sync
@@ -232,6 +339,9 @@ class CompressionPipeline:
             # waits for the level sizes)
             x.cmap.build_pyramid(5, nf, overlap=x.cmap.nbr3)
             ycm = x.cmap.coarse.coarse.coarse
+            if getattr(x, "_finish_features", None) is not None:
+                x._finish_features()          # waits for the colours, which travelled during the coordinate work
+                x._finish_features = None
             tm.mark("unpack")
             y, k = self.analysis_step(x)
             tm.mark("analysis")
@@ -343,15 +453,39 @@ class DecompressionPipeline:
         """Step 6 (the reference names the synthesis step `hyper_synthesis`, codec_parallel.py:465-472)."""
         return self.decompression_model.g_s(y_hat, k=ks)
 
+    def _ship_points_early(self, keys):
+        """Called by g_s once the output coordinates are final (before the colour head): points leave for
+        the host on a side stream while the colour head runs."""
+        n = keys.shape[0]
+        pts_d, _ = ops.unpack_output(keys, None)
+        ready = torch.cuda.Event()
+        ready.record()
+        pts_h = torch.empty((n, 3), dtype=torch.int32, pin_memory=True)
+        side = ops._side_stream(self.device, "d2h")
+        with torch.cuda.stream(side):
+            side.wait_event(ready)
+            pts_h.copy_(pts_d, non_blocking=True)
+            done = torch.cuda.Event()
+            done.record()
+        pts_d.record_stream(side)
+        self._early = (keys, pts_h, done)
+
     def pack_batches(self, pointcloud, num_frames):
         """codec_parallel.py:474-502: split per frame, NaN -> 0, clip colours to [0,1].  The clip runs
         on the device; points (int32 [N,3]) and colours (float32 [N,3]) land in pinned host memory that
         the returned arrays own."""
         n = pointcloud.cmap.n
-        pts_d, col_d = ops.unpack_output(pointcloud.cmap.keys, pointcloud._feats)
-        pts_h = torch.empty((n, 3), dtype=torch.int32, pin_memory=True)
+        early = getattr(self, "_early", None)
+        self._early = None
+        if early is not None and early[0] is pointcloud.cmap.keys:
+            _, pts_h, self._pts_done = early
+            _, col_d = ops.unpack_output(pointcloud.cmap.keys, pointcloud._feats, want_points=False)
+        else:
+            pts_d, col_d = ops.unpack_output(pointcloud.cmap.keys, pointcloud._feats)
+            pts_h = torch.empty((n, 3), dtype=torch.int32, pin_memory=True)
+            pts_h.copy_(pts_d, non_blocking=True)
+            self._pts_done = None
         col_h = torch.empty((n, 3), dtype=torch.float32, pin_memory=True)
-        pts_h.copy_(pts_d, non_blocking=True)
         col_h.copy_(col_d, non_blocking=True)
         counts = getattr(pointcloud, "frame_counts", None)
         if counts is None:
@@ -390,6 +524,9 @@ class DecompressionPipeline:
             tm.mark("hyper_synthesis")
             y_hat, st_y = self.gaussian_model_step_batched(y_dev, y_strings[0][:16], ycm, q, gaussian_params)
             y_hat.frame_counts = frame_counts
+            self._early = None
+            if to_host:
+                y_hat.on_geometry = self._ship_points_early
             tm.mark("guassian_model")
             x_hat = self.hyper_synthesis(y_hat, ks)
             tm.mark("synthesis_transform")
@@ -397,6 +534,9 @@ class DecompressionPipeline:
             # the call's single blocking point: every deferred size check and both decoder status words
             ops.verify_deferred([(st_geo, "coordinate stream decode failed"), (st_z, "entropy decode of z failed"),
                                  (st_y, "entropy decode of y failed")])
+            if to_host and getattr(self, "_pts_done", None) is not None:
+                self._pts_done.synchronize()          # the side-stream copy of the points
+                self._pts_done = None
             final_data = self._finish_batches(*packed, nf) if to_host else x_hat
             st = tm.resolve()
             sideinfo = {"time_measurements": {}, "timestamps": {}}

@@ -162,6 +162,12 @@ class Program:
         return {OP_KMAP_DOWN2: "kmap_down2", OP_ROWS_F32_TO_BF16: "rows_f32_to_bf16", OP_COORDS_CHILDREN: "coords_children",
                 OP_GATHER_ROWS_BF16: "gather_rows", OP_GATHER_KEYS: "gather_keys", OP_FRAME_OFFSETS: "frame_offsets"}[op], 0, 0
 
+    def flush(self) -> None:
+        """Run the entries recorded so far and start an empty table over the SAME arena (the caller wants
+        to act between two parts of a transform, e.g. start a copy on another stream)."""
+        self.run()
+        self.n = 0
+
     def run(self) -> None:
         if self.n == 0:
             return

@@ -40,6 +40,28 @@ __global__ void k_ingest(const int16_t* __restrict__ p, const double* __restrict
   keys[i] = pack_key(batch, x, y, z);
   feats[i] = make_float4(1.0f, (float)col[3 * i], (float)col[3 * i + 1], (float)col[3 * i + 2]);
 }
+__global__ void k_ingest_points(const int16_t* __restrict__ p, int64_t n, int batch, uint64_t* __restrict__ keys) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  keys[i] = pack_key(batch, p[3 * i], p[3 * i + 1], p[3 * i + 2]);
+}
+// feature row i = bf16(1, r, g, b, 0 ...) of colour row src_row[i] (same rounding as k_ingest followed by
+// k_rows_f32_to_bf16: double -> float -> bf16 RN); chunks16 = 16-byte chunks per output row
+__global__ void k_ingest_features(const double* __restrict__ col, const int32_t* __restrict__ src_row, int64_t m,
+                                  uint4* __restrict__ out, int chunks16) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  const int64_t r = src_row ? (int64_t)src_row[i] : i;
+  float c0 = 0.f, c1 = 0.f, c2 = 0.f;
+  if (r >= 0) {
+    c0 = (float)col[3 * r];
+    c1 = (float)col[3 * r + 1];
+    c2 = (float)col[3 * r + 2];
+  }
+  __nv_bfloat162 a = __floats2bfloat162_rn(1.0f, c0), b = __floats2bfloat162_rn(c1, c2);
+  out[i * chunks16] = make_uint4(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b), 0u, 0u);
+  for (int k = 1; k < chunks16; ++k) out[i * chunks16 + k] = make_uint4(0u, 0u, 0u, 0u);
+}
 __global__ void k_coords_from_keys(const uint64_t* __restrict__ keys, int64_t n, int4* __restrict__ c) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -54,11 +76,14 @@ __global__ void k_unpack_output(const uint64_t* __restrict__ keys, const float* 
                                 int32_t* __restrict__ pts, float* __restrict__ col) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
-  int b, x, y, z;
-  unpack_key(keys[i], b, x, y, z);
-  pts[3 * i] = x;
-  pts[3 * i + 1] = y;
-  pts[3 * i + 2] = z;
+  if (pts) {
+    int b, x, y, z;
+    unpack_key(keys[i], b, x, y, z);
+    pts[3 * i] = x;
+    pts[3 * i + 1] = y;
+    pts[3 * i + 2] = z;
+  }
+  if (!col) return;
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
     float v = feats[3 * i + c];
@@ -270,11 +295,28 @@ int pcc_ingest_frame(const int16_t* points, const double* colors, int64_t n, int
   PCC_LAUNCHED();
   return PCC_OK;
 }
+int pcc_ingest_points(const int16_t* points, int64_t n, int32_t batch, uint64_t* keys, pcc_stream_t s) {
+  PCC_CHECK_ARG(n >= 0 && batch >= 0 && batch < 65535);
+  if (n == 0) return PCC_OK;
+  PCC_CHECK_ARG(points && keys);
+  k_ingest_points<<<blocks_for(n), kThreads, 0, as_stream(s)>>>(points, n, batch, keys);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+int pcc_ingest_features(const double* colors, const int32_t* src_row, int64_t m, void* feats_bf16, int c_dst,
+                        pcc_stream_t s) {
+  PCC_CHECK_ARG(m >= 0 && c_dst >= 8 && c_dst % 8 == 0);
+  if (m == 0) return PCC_OK;
+  PCC_CHECK_ARG(colors && feats_bf16 && ((uintptr_t)feats_bf16 % 16) == 0);
+  k_ingest_features<<<blocks_for(m), kThreads, 0, as_stream(s)>>>(colors, src_row, m, (uint4*)feats_bf16, c_dst / 8);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
 int pcc_unpack_output(const uint64_t* keys, const float* feats3, int64_t n, int32_t* points, float* colors,
                       pcc_stream_t s) {
   PCC_CHECK_ARG(n >= 0);
   if (n == 0) return PCC_OK;
-  PCC_CHECK_ARG(keys && feats3 && points && colors);
+  PCC_CHECK_ARG((points || colors) && (!points || keys) && (!colors || feats3));
   k_unpack_output<<<blocks_for(n), kThreads, 0, as_stream(s)>>>(keys, feats3, n, points, colors);
   PCC_LAUNCHED();
   return PCC_OK;

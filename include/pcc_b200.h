@@ -55,8 +55,16 @@ int pcc_keys_from_coords_f32(const float* coords, int64_t n, uint64_t* keys, pcc
  * codec_pipeline.py:257-260 (shared/utils.py:10-42). */
 int pcc_ingest_frame(const int16_t* points, const double* colors, int64_t n, int32_t batch,
                      uint64_t* keys, float* feats4, pcc_stream_t s);
+/* The same in two steps, so that the coordinate work (sort, pyramid, kernel maps) can start while the
+ * colours -- 80 % of a raw frame's bytes -- are still on their way to the device: keys from the points
+ * alone, then feature rows bf16 (1,r,g,b,0...) [m, c_dst] gathered through src_row (the first-wins rows
+ * of pcc_sort_unique; NULL = identity; same rounding as pcc_ingest_frame + pcc_rows_f32_to_bf16). */
+int pcc_ingest_points(const int16_t* points, int64_t n, int32_t batch, uint64_t* keys, pcc_stream_t s);
+int pcc_ingest_features(const double* colors, const int32_t* src_row, int64_t m, void* feats_bf16,
+                        int c_dst, pcc_stream_t s);
 /* Decoder output packing (pack_batches, codec_parallel.py:474-502): keys -> int32 [n,3] (x,y,z) and
- * colours [n,3] with NaN -> 0 and clip(c * 255, 0, 255) / 255 evaluated in fp32. */
+ * colours [n,3] with NaN -> 0 and clip(c * 255, 0, 255) / 255 evaluated in fp32.  Either output may
+ * be NULL (the decoder sends the points to the host while the colour head still runs). */
 int pcc_unpack_output(const uint64_t* keys, const float* feats3, int64_t n, int32_t* points, float* colors,
                       pcc_stream_t s);
 /* keys -> int32 [n,4] (b,x,y,z): the `.C` attribute. */

@@ -26,8 +26,13 @@ def main():
         c, _ = enc.compress({"frames": [frame]}, staged=staged)
         dec.decompress(c[1], to_host=False)
     torch.cuda.synchronize()
-    with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
-        c, _ = enc.compress({"frames": [frame]}, staged=staged)
+    e2e = "--e2e" in sys.argv
+    if e2e:
+        for _ in range(3):
+            c, _ = enc.compress({"frames": [frame]})
+        torch.cuda.synchronize()
+    with profile(activities=[ProfilerActivity.CUDA] + ([] if e2e else [ProfilerActivity.CPU])) as prof:
+        c, _ = (enc.compress({"frames": [frame]}) if e2e else enc.compress({"frames": [frame]}, staged=staged))
         torch.cuda.synchronize()
         dec.decompress(c[1], to_host=False)
         torch.cuda.synchronize()
@@ -45,6 +50,9 @@ def main():
         gaps.append((a1 - b0, (b0 - t0) / 1e3, n0[:50], n1[:50]))
     small = sum(g for g, *_ in gaps if 0 < g <= 10)
     print(f"sum of gaps <= 10 us: {small / 1e3:.3f} ms over {sum(1 for g, *_ in gaps if 0 < g <= 10)} gaps")
+    if e2e:
+        for a, b, n in ks[:60]:
+            print(f"  +{(a - t0) / 1e3:7.3f} ms  {(b - a):8.1f} us  {n[:80]}")
     for g, at, n0, n1 in sorted(gaps, key=lambda x: -x[0])[:40]:
         print(f"gap {g:8.1f} us at {at:7.3f} ms  after {n0:50s} before {n1}")
 
