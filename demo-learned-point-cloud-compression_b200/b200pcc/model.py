@@ -227,8 +227,15 @@ def _analysis_program(self, f, cm, nlev):
     the residual blocks, then the 1x1 head.  -> (y features fp32 tensor, stride-8 CoordMap)."""
     pr = prg.Program(f.device)
     nbr0 = cm.nbr3()
-    cur = pr.alloc(cm.n * self.stem.cout * 2)
-    pr.conv(self.stem, f.data_ptr(), cm.n, nbr0.data_ptr(), nbr0.stride(0), cm.n, out_bf16=cur, relu=True)
+    stem_out = getattr(cm, "_stem_out", None)
+    if stem_out is not None:      # launched ahead of the pyramid read-back (prelaunch_stem)
+        cm._stem_out = None
+        cur = stem_out.data_ptr()
+        pr.keep.append(stem_out)
+    else:
+        cur = pr.alloc(cm.n * self.stem.cout * 2)
+        pr.conv(self.stem, f.data_ptr(), cm.n, nbr0.data_ptr(), nbr0.stride(0), cm.n, out_bf16=cur, relu=True)
+        pr.flush()          # the stem runs while the rest of the program is recorded
     for i in range(nlev):
         coarse = cm.coarse
         nd, ld = pr.kmap_down2(cm)
@@ -238,6 +245,8 @@ def _analysis_program(self, f, cm, nlev):
         cm, cur = coarse, o
         nb, ld3 = pr.kmap_k3(cm.keys.data_ptr(), cm.n, cm.log2_stride, _block_bound(cm))
         cur = pr.resblocks(self.blocks[i], cur, cm.n, c, nb, ld3)
+        if i == 0:
+            pr.flush()
     yf = torch.empty((cm.n, self.cfg["c_y"]), dtype=torch.float32, device=f.device)
     pr.conv(self.head, cur, cm.n, 0, 0, cm.n, out_f32=yf.data_ptr())
     pr.keep += [f, nbr0, yf]
@@ -245,7 +254,17 @@ def _analysis_program(self, f, cm, nlev):
     return yf, cm
 
 
+def _prelaunch_stem(self, x):
+    """Kernel map of the input coordinates + the stem convolution, enqueued before the host waits for the
+    pyramid's level sizes (neither depends on them).  g_a picks the result up from the coordinate map."""
+    cm = x.cmap
+    nbr0 = cm.nbr3()
+    if USE_PROGRAMS and x._feats is not None and cm.n > 0:
+        cm._stem_out = self.stem(x.feats_bf16(self.stem.cin_pad), nbr0, cm.n, relu=True)
+
+
 AnalysisTransform._program = _analysis_program
+AnalysisTransform.prelaunch_stem = _prelaunch_stem
 
 
 class SynthesisTransform(_Module):
@@ -376,6 +395,8 @@ def _synthesis_program(self, f, cm, k, num_frames, prev, on_geometry=None):
         pf = pr.alloc(m * c * 2)
         pr.add(prg.OP_GATHER_ROWS_BF16, cur, c, keep, m, pf)
         keys_ptr, n, cur = pk, m, pf
+        if i < 2:
+            pr.flush()          # this level runs while the next one is recorded
     if on_geometry is not None:
         pr.flush()                 # the geometry is final here: the caller may start shipping it
         on_geometry(out_keys)

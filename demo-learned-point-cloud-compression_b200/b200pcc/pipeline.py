@@ -335,9 +335,9 @@ class CompressionPipeline:
             num_points = x.cmap.n
             nf = x.num_frames
             # every coarser coordinate map (g_a: 3, h_a: 2) with one host sync
-            # (the stride-1 kernel map of the stem does not depend on the pyramid: it is built while the host
-            # waits for the level sizes)
-            x.cmap.build_pyramid(5, nf, overlap=x.cmap.nbr3)
+            # (the stride-1 kernel map and the stem convolution do not depend on the pyramid: they run while
+            # the host waits for the level sizes and does its bookkeeping)
+            x.cmap.build_pyramid(5, nf, overlap=lambda: self.compression_model.g_a.prelaunch_stem(x))
             ycm = x.cmap.coarse.coarse.coarse
             if getattr(x, "_finish_features", None) is not None:
                 x._finish_features()          # waits for the colours, which travelled during the coordinate work

@@ -9,6 +9,7 @@ buffers are raw addresses inside a per-thread arena -- and hands the table to C 
 change from frame to frame, so programs are rebuilt per call (a few us); nothing is cached or captured.
 With ``ops.PROFILER`` set the entries run one by one under CUDA events (bench.py's roofline leg).
 """
+import array
 import ctypes as C
 import threading
 
@@ -77,10 +78,13 @@ def arena(device) -> Arena:
     return a
 
 
+_PAD = [(0,) * k for k in range(_ROW + 1)]
+
+
 class Program:
-    def __init__(self, device, capacity: int = 96):
+    def __init__(self, device):
         self.device = device
-        self.table = np.zeros((capacity, _ROW), dtype=np.int64)
+        self.words = array.array("q")     # entries back to back, _ROW int64 words each
         self.n = 0
         self.arena = arena(device)
         self.arena.reset()
@@ -90,11 +94,10 @@ class Program:
         return self.arena.alloc(nbytes)
 
     def add(self, op: int, *args) -> None:
-        if self.n == self.table.shape[0]:
-            self.table = np.concatenate([self.table, np.zeros_like(self.table)])
-        row = self.table[self.n]
-        row[0] = op
-        row[1:1 + len(args)] = args
+        w = self.words
+        w.append(op)
+        w.extend(args)
+        w.extend(_PAD[_ROW - 1 - len(args)])
         self.n += 1
 
     # ---- typed helpers -------------------------------------------------------------------------------
@@ -163,9 +166,11 @@ class Program:
                 OP_GATHER_ROWS_BF16: "gather_rows", OP_GATHER_KEYS: "gather_keys", OP_FRAME_OFFSETS: "frame_offsets"}[op], 0, 0
 
     def flush(self) -> None:
-        """Run the entries recorded so far and start an empty table over the SAME arena (the caller wants
-        to act between two parts of a transform, e.g. start a copy on another stream)."""
+        """Run the entries recorded so far and start an empty table over the SAME arena: the GPU gets the
+        first layers while the host is still recording the rest, and callers can act between two parts of a
+        transform (e.g. start a copy on another stream)."""
         self.run()
+        self.words = array.array("q")
         self.n = 0
 
     def run(self) -> None:
@@ -173,13 +178,15 @@ class Program:
             return
         failed = C.c_int32(-1)
         st = ops._stream()
+        addr, _ = self.words.buffer_info()
         if ops.PROFILER is None:
-            rc = lib.pcc_run_program(self.table.ctypes.data, self.n, st, C.byref(failed))
+            rc = lib.pcc_run_program(addr, self.n, st, C.byref(failed))
             if rc:
-                raise PccError(f"program entry {failed.value} (op {int(self.table[max(failed.value, 0), 0])}): "
-                               f"{ops._lib.last_error()}")
+                op = self.words[max(failed.value, 0) * _ROW]
+                raise PccError(f"program entry {failed.value} (op {op}): {ops._lib.last_error()}")
             return
+        table = np.frombuffer(self.words, dtype=np.int64).reshape(self.n, _ROW)
         for i in range(self.n):
-            fam, nbytes, flops = self._family(self.table[i])
+            fam, nbytes, flops = self._family(table[i])
             with ops._prof(fam, nbytes, flops):
-                check(lib.pcc_run_program(self.table[i:i + 1].ctypes.data, 1, st, C.byref(failed)))
+                check(lib.pcc_run_program(addr + i * _ROW * 8, 1, st, C.byref(failed)))
