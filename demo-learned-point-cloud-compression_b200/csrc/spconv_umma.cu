@@ -567,6 +567,7 @@ static int launch_umma_g(const UmmaParams& p, size_t smem, unsigned grid, cudaSt
 template <int CIN>
 static int launch_umma(const UmmaParams& p, int groups, size_t smem, unsigned grid, cudaStream_t st) {
   switch (groups) {
+    case 5: return launch_umma_g<CIN, 5>(p, smem, grid, st);
     case 4: return launch_umma_g<CIN, 4>(p, smem, grid, st);
     case 2: return launch_umma_g<CIN, 2>(p, smem, grid, st);
     default: return launch_umma_g<CIN, 1>(p, smem, grid, st);
@@ -576,7 +577,7 @@ static int launch_umma(const UmmaParams& p, int groups, size_t smem, unsigned gr
 
 int pcc_spconv_set_tuning(int groups, int max_tiles, int use_cg) {
   PCC_CHECK_ARG(max_tiles == 1 || max_tiles == 2 || max_tiles == 4);
-  PCC_CHECK_ARG(groups == 0 || groups == 1 || groups == 2 || groups == 4);
+  PCC_CHECK_ARG(groups == 0 || groups == 1 || groups == 2 || groups == 4 || groups == 5);
   PCC_CHECK_ARG(use_cg == 0);   // the cp.async.cg gather variant was measured slower (571 vs 363 us) and removed
   g_max_t = max_tiles;
   g_groups = groups;
@@ -634,11 +635,16 @@ int pcc_spconv_umma(const void* in_bf16, int64_t n_in, int cin, const int32_t* n
   // gather groups (= ring slots) and T tiles per stage.  T is bounded by TMEM (2 x T accumulators of
   // acc_cols columns in 512), by shared memory (G slots of T tiles), by the tuning cap and by the
   // tile count (keep >= 2 rounds per SM so the persistent grid stays balanced).
-  int groups = g_groups ? g_groups : (cin <= 64 ? 4 : 2);
+  // more gather warps = more rows in flight: 5 groups (928 threads) where five slots fit, i.e. narrow
+  // inputs with the weight panels streamed per stage (363 -> 339 us on the 1.79 M-row c32 layer)
+  int groups = g_groups ? g_groups : (cin <= 32 && kvol > 8 ? 5 : (cin <= 64 ? 4 : 2));
   p.acc_cols = (uint32_t)((cout + 31) / 32 * 32);
   const int64_t a_tile = (int64_t)(kTileM / 8) * (cin / 8) * 144, b_bytes = (int64_t)cin * cout * 2;
   const int64_t budget = 227 * 1024 - 1024;
   p.wres = (kvol * b_bytes <= 72 * 1024) ? 1 : 0;
+  if (groups == 5) {          // five slots only fit when the weight panels travel with their stage
+    if (cin <= 64 && kvol > 1) p.wres = 0; else groups = 4;
+  }
   p.jc = 1;
   for (int d = 2; d <= 4; ++d)
     if (kvol % d == 0) p.jc = d;
@@ -647,7 +653,7 @@ int pcc_spconv_umma(const void* in_bf16, int64_t n_in, int cin, const int32_t* n
     const int64_t nb = nbr ? (int64_t)kNbrBufs * p.jc * T * kTileM * 4 : 0;
     return w + (int64_t)G * T * a_tile + nb + 1024;
   };
-  while (groups > 1 && smem_need(groups, 1) > budget) groups >>= 1;
+  while (groups > 1 && smem_need(groups, 1) > budget) groups = groups == 5 ? 4 : groups >> 1;
   if (smem_need(groups, 1) > budget) {
     set_error("pcc_spconv_umma: cin %d cout %d kvol %d does not fit shared memory", cin, cout, kvol);
     return PCC_E_UNSUPPORTED;

@@ -195,7 +195,7 @@ int pcc_spconv_umma(const void* in_bf16, int64_t n_in, int cin, const int32_t* n
                     const void* residual_bf16, int64_t ldr, int relu, void* out_bf16,
                     float* out_f32, int64_t ldo, int cstore, pcc_stream_t s);
 /* Tuning knobs of pcc_spconv_umma (process wide; defaults 0, 4, 0): number of gather groups = ring
- * slots (0 = chosen from the channel count, else 1, 2 or 4) and the maximum number T of 128-row
+ * slots (0 = chosen from the channel count, else 1, 2, 4 or 5) and the maximum number T of 128-row
  * tiles gathered per stage and accumulated concurrently (1, 2 or 4).  use_cg must be 0 (the
  * cp.async.cg gather variant was measured slower and has been removed). */
 int pcc_spconv_set_tuning(int groups, int max_tiles, int use_cg);

@@ -44,7 +44,7 @@ def main():
         alg = 2 * n * args.cin + 2 * n * args.cout + 4 * 27 * n
         print(f"{name}: n={n} pairs/row={pairs:.2f} algorithmic MB={alg / 1e6:.1f}")
         for groups, mt, cg in (((0, 4, 0),) if args.one else
-                               ((4, 1, 0), (4, 2, 0), (4, 4, 0), (2, 4, 0), (2, 2, 0))):
+                               ((5, 4, 0), (4, 4, 0), (4, 2, 0), (2, 4, 0))):
             if True:
                 _lib.check(_lib.lib.pcc_spconv_set_tuning(groups, mt, cg))
                 ts = []
