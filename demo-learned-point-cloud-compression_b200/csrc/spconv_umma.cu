@@ -159,9 +159,24 @@ struct UmmaParams {
 constexpr int kMmaWarp = 4, kMmaWarps = 4, kLoaderWarp = 8, kProdWarp0 = 9;
 constexpr int kNbrBufs = 3;   // kernel-map ring depth (units)
 
-__device__ __forceinline__ void cp_async16_ca(uint32_t dst, const void* src, uint32_t src_bytes) {
-  // .ca on purpose: with .cg (L1 bypass) the 1.79 M-row c32 layer takes 571 us instead of 363 us
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+// One 16-byte chunk of a gathered row, global -> shared (LDGSTS).  `r` is the map entry (source row, or
+// >= n_in when the neighbour is absent), `base` the input + the chunk's byte offset.  A present row is
+// copied; an absent one writes zeros (ignore-src form) and only if `dirty_bit` says the slot still holds
+// data from the previous use of the stage.  Written in PTX so the predicate logic stays in predicates
+// (ISETP, LOP3.P, ISETP.OR, SEL, address, LDGSTS) instead of being materialised as integers.
+// .ca on purpose: with .cg (L1 bypass) the 1.79 M-row c32 layer takes 571 us instead of 363 us
+template <int ROW_BYTES>
+__device__ __forceinline__ void gather_chunk(uint32_t dst, uint64_t base, uint32_t r, uint32_t n_in, uint32_t dirty_bit) {
+  asm volatile(
+      "{\n\t.reg .pred ok, q, ig;\n\t.reg .b32 rc;\n\t.reg .b64 src;\n\t"
+      "setp.lt.u32 ok, %2, %3;\n\t"
+      "setp.ne.or.u32 q, %4, 0, ok;\n\t"
+      "not.pred ig, ok;\n\t"
+      "selp.b32 rc, %2, 0, ok;\n\t"
+      "mad.wide.u32 src, rc, %5, %1;\n\t"
+      "@q cp.async.ca.shared.global [%0], [src], 16, ig;\n\t}" ::"r"(dst),
+      "l"(base), "r"(r), "r"(n_in), "r"(dirty_bit), "n"(ROW_BYTES)
+      : "memory");
 }
 __device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr) {
   uint32_t v;
@@ -248,7 +263,7 @@ k_spconv_umma(const UmmaParams p) {
     const int pw = (warp - kProdWarp0) & 3;    // row quarter inside a tile
     const int sub = lane % CPR, rl0 = lane / CPR;
     const uint32_t n_in32 = (uint32_t)p.n_in;
-    const char* in_b = reinterpret_cast<const char*>(p.in) + sub * 16;
+    const uint64_t in_b64 = reinterpret_cast<uint64_t>(p.in) + (uint64_t)(sub * 16);
     // lane -> (row group rg4 = lane / CPR, chunk sub): the thread copies chunk `sub` of the CPR
     // consecutive rows 32*pw + rg4*CPR + it, so their CPR kernel-map entries are one vector load
     uint32_t dst_c[CPR];   // per-thread constant part of the destination address
@@ -286,13 +301,19 @@ k_spconv_umma(const UmmaParams p) {
         mbar_expect_tx(fullb, b_bytes);
         bulk_g2s(w0 + (uint32_t)gi * b_bytes, p.w + (size_t)j * b_bytes, b_bytes, fullb);
       }
-      uint32_t now = 0;
-      const bool has_nbr = p.nbr != nullptr;
+      // `absent` collects the sign bits of the map entries (-1 = no neighbour) by funnel shift, one
+      // instruction per chunk; the k-th chunk processed ends at bit N-1-k (N = T * CPR chunks per thread)
+      constexpr int N = T * CPR;
+      uint32_t absent = 0;
+      auto chunk = [&](uint32_t r, int t, int it) {
+        absent = __funnelshift_l(r, absent, 1);
+        gather_chunk<CIN * 2>(a_dst[it] + (uint32_t)t * a_tile, in_b64, r, n_in32, dirty & (1u << (N - 1 - (t * CPR + it))));
+      };
+      if (p.nbr != nullptr) {
 #pragma unroll
-      for (int t = 0; t < T; ++t) {
-        uint32_t rr[CPR];
-        if (has_nbr) {
+        for (int t = 0; t < T; ++t) {
           // (tiles past the end of the map hold -1: the loader fills them)
+          uint32_t rr[CPR];
           const uint32_t ia = nb_addr + (uint32_t)(t * kTileM + rowb) * 4u;
           if (CPR >= 4) {
 #pragma unroll
@@ -304,22 +325,19 @@ k_spconv_umma(const UmmaParams p) {
           } else {
             asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(rr[0]), "=r"(rr[1]) : "r"(ia) : "memory");
           }
-        } else {
+#pragma unroll
+          for (int it = 0; it < CPR; ++it) chunk(rr[it], t, it);
+        }
+      } else {
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
           const int64_t o0 = (((rg << lt) + t) * kTileM) + rowb;
 #pragma unroll
-          for (int it = 0; it < CPR; ++it) rr[it] = (o0 + it < p.n_out) ? (uint32_t)(o0 + it) : 0xffffffffu;
-        }
-#pragma unroll
-        for (int it = 0; it < CPR; ++it) {
-          const bool ok = rr[it] < n_in32;
-          const uint32_t bit = 1u << (t * CPR + it);
-          if (ok) now |= bit;
-          if (ok || (dirty & bit)) {
-            const uint32_t rc = ok ? rr[it] : 0u;
-            cp_async16_ca(a_dst[it] + (uint32_t)t * a_tile, in_b + (size_t)rc * (CIN * 2), ok ? 16u : 0u);
-          }
+          for (int it = 0; it < CPR; ++it) chunk((o0 + it < p.n_out) ? (uint32_t)(o0 + it) : 0xffffffffu, t, it);
         }
       }
+      // a chunk is dirty (holds data) iff its entry was a row: bit clear in `absent`
+      const uint32_t now = ~absent & (N == 32 ? 0xffffffffu : ((1u << (N & 31)) - 1u));
       dirty = now;
       cp_async_commit();
       if (p.nbr) {          // kernel-map reads of this stage are done
