@@ -30,6 +30,10 @@ INT = C.c_int
 F32 = C.c_float
 
 
+class Span(C.Structure):
+    _fields_ = [("data", P), ("len", I64)]
+
+
 class CdfTables(C.Structure):
     _fields_ = [("cdf", P), ("cdf_off", P), ("cdf_size", P), ("offset", P), ("lut", P), ("num_tables", I32), ("cdf_total", I32)]
 
@@ -92,6 +96,12 @@ SIGNATURES = {
     "pcc_rans_encode": (INT, [P, P, I64, I64, I32, C.POINTER(CdfTables), P, P, P, I64, P]),
     "pcc_rans_decode": (INT, [P, I64, I32, P, I64, I64, C.POINTER(CdfTables), P, P, P]),
     "pcc_run_program": (INT, [P, I32, P, P]),
+    "pcc_container_batched_bytes": (I64, [I32, I64, I64, P]),
+    "pcc_container_write_batched": (INT, [I32, C.c_double, C.c_double, I32, I32, Span, Span, P, P, I32, P, I64, P]),
+    "pcc_container_parse_batched": (INT, [P, I64, I32, P, P, P, P, P, P, P, P, P, I32]),
+    "pcc_container_frames_bytes": (I64, [I32, P, P, P]),
+    "pcc_container_write_frames": (INT, [I32, C.c_double, C.c_double, P, P, P, P, P, P, I32, P, I64, P]),
+    "pcc_container_parse_frames": (INT, [P, I64, I32, P, P, P, P, P, P, P, P, P, I32]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

@@ -161,6 +161,9 @@ def _stage_concat(stager: "_Stager", arrays: List[np.ndarray], torch_dtype, widt
     if background:
         # the caller keeps enqueuing GPU work while the workers copy; wait() joins them and returns the
         # event that marks the last DMA
+        if len(jobs) == 1:       # small frame: a worker would only get the GIL when this thread blocks
+            job(jobs[0])
+            jobs = []
         futures = [_COPY_POOL.submit(job, j) for j in jobs]
 
         def wait():

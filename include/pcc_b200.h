@@ -324,6 +324,39 @@ typedef struct {
 } pcc_op_t;
 int pcc_run_program(const pcc_op_t* ops, int32_t n_ops, pcc_stream_t s, int32_t* failed_op);
 
+/* ------------------------------------------------------------------------------------------
+ * (6) bitstream containers of the reference, host side only: no GPU, no
+ *     allocation.  Field order, widths and endianness are the reference's (int32 / float64, big endian).
+ *     Batched layout  = make_bitstream_batched / read_bitstream_batched
+ *                       (sender/encoder/codec_pipeline.py:464-517, receiver/decoder/codec_parallel.py:173-216);
+ *     per-frame layout = make_bitstream / read_bitstream
+ *                       (sender/encoder/codec_single.py:269-337, receiver/decoder/codec_single.py:90-136).
+ *     The y/z strings are PCL1 lane containers (4), points_i is the OCT2 stream of (1b).
+ *     ks holds three rows of per-frame point counts: ks[level * ks_ld + frame], level 0..2.
+ *     The parse functions return spans that point INTO `data`; PCC_E_INVALID for a truncated or
+ *     inconsistent blob (negative length, more than max_frames frames).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  const uint8_t* data;
+  int64_t len;
+} pcc_span_t;
+int64_t pcc_container_batched_bytes(int32_t num_frames, int64_t y_len, int64_t z_len, const pcc_span_t* points);
+int pcc_container_write_batched(int32_t num_frames, double q_geo, double q_att, int32_t y_shape, int32_t z_shape,
+                                pcc_span_t y, pcc_span_t z, const pcc_span_t* points, const int32_t* ks,
+                                int32_t ks_ld, uint8_t* out, int64_t out_cap, int64_t* written);
+int pcc_container_parse_batched(const uint8_t* data, int64_t nbytes, int32_t max_frames, int32_t* num_frames,
+                                double* q_geo, double* q_att, int32_t* y_shape, int32_t* z_shape, pcc_span_t* y,
+                                pcc_span_t* z, pcc_span_t* points, int32_t* ks, int32_t ks_ld);
+int64_t pcc_container_frames_bytes(int32_t num_frames, const pcc_span_t* y, const pcc_span_t* z,
+                                   const pcc_span_t* points);
+int pcc_container_write_frames(int32_t num_frames, double q_geo, double q_att, const int32_t* y_shapes,
+                               const int32_t* z_shapes, const pcc_span_t* y, const pcc_span_t* z,
+                               const pcc_span_t* points, const int32_t* ks, int32_t ks_ld, uint8_t* out,
+                               int64_t out_cap, int64_t* written);
+int pcc_container_parse_frames(const uint8_t* data, int64_t nbytes, int32_t max_frames, int32_t* num_frames,
+                               double* q_geo, double* q_att, int32_t* y_shapes, int32_t* z_shapes, pcc_span_t* y,
+                               pcc_span_t* z, pcc_span_t* points, int32_t* ks, int32_t ks_ld);
+
 #ifdef __cplusplus
 }
 #endif

@@ -181,6 +181,37 @@ def test_container_roundtrip_and_layout():
     assert out[0] == [b"y0", b"y1"] and out[1] == [b"z0", b"z1"] and out[2] == [5, 6] and out[5] == ks
 
 
+def test_container_c_abi_equals_struct_version():
+    """include/pcc_b200.h section 6: the C reader/writer and container.py agree byte
+    for byte on both layouts, including empty strings, and reject every truncation."""
+    from b200pcc import container
+    rng = np.random.default_rng(5)
+    for nf in (0, 1, 3, 17):
+        pts = [rng.integers(0, 256, int(rng.integers(0, 90)), dtype=np.uint8).tobytes() for _ in range(nf)]
+        ks = [[int(rng.integers(0, 2 ** 31 - 1)) for _ in range(nf)] for _ in range(3)]
+        y = rng.integers(0, 256, 1000, dtype=np.uint8).tobytes()
+        z = b"" if nf == 1 else rng.integers(0, 256, 33, dtype=np.uint8).tobytes()
+        q = (float(rng.random()), -0.5)
+        blob = container.make_bitstream_batched(y, z, 12345, -7, pts, ks, q)
+        assert container.make_bitstream_batched_native(y, z, 12345, -7, pts, ks, q) == blob
+        assert container.read_bitstream_batched_native(blob, max_frames=32) == container.read_bitstream_batched(blob)
+        ys = [rng.integers(0, 256, int(rng.integers(0, 50)), dtype=np.uint8).tobytes() for _ in range(nf)]
+        zs = [rng.integers(0, 256, int(rng.integers(0, 9)), dtype=np.uint8).tobytes() for _ in range(nf)]
+        ysh, zsh = list(range(10, 10 + nf)), list(range(nf))
+        b2 = container.make_bitstream(ys, zs, ysh, zsh, pts, ks, q)
+        assert container.make_bitstream_native(ys, zs, ysh, zsh, pts, ks, q) == b2
+        assert container.read_bitstream_native(b2, max_frames=32) == container.read_bitstream(b2)
+        for cut in sorted({1, 19, 35, len(blob) // 2, len(blob) - 1} & set(range(len(blob)))):
+            with pytest.raises(ValueError):
+                container.read_bitstream_batched_native(blob[:cut], max_frames=32)
+        if nf:
+            with pytest.raises(ValueError):
+                container.read_bitstream_native(b2[:-1], max_frames=32)
+    with pytest.raises(ValueError):     # more frames than the caller has room for
+        container.read_bitstream_batched_native(container.make_bitstream_batched(b"", b"", 0, 0, [b"a"] * 5, [[0] * 5] * 3, (0, 0)),
+                                                max_frames=4)
+
+
 def test_scale_nn_host_matches_oracle():
     from b200pcc import config as cfgmod
     from b200pcc.model import ScaleNN

@@ -15,7 +15,9 @@ from b200pcc.pipeline import load_model
 
 dev = torch.device("cuda:0")
 model = load_model(dev)
-frame = synth.frame_8ivfb(seed=1)
+which = next((a.split("=")[1] for a in sys.argv if a.startswith("--frame=")), "8ivfb")
+frame = {"8ivfb": lambda: synth.frame_8ivfb(seed=1), "zed": lambda: synth.frame_zed(seed=2),
+         "100k": lambda: synth.frame_cpu100k(seed=0)}[which]()
 enc = CompressionPipeline([[1.0, 1.0]], device=dev, model=model)
 dec = DecompressionPipeline(device=dev, model=model)
 for _ in range(4):

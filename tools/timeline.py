@@ -18,7 +18,9 @@ from b200pcc.pipeline import load_model
 def main():
     dev = torch.device("cuda:0")
     model = load_model(dev)
-    frame = synth.frame_8ivfb(seed=1)
+    which = next((a.split("=")[1] for a in sys.argv if a.startswith("--frame=")), "8ivfb")
+    frame = {"8ivfb": lambda: synth.frame_8ivfb(seed=1), "zed": lambda: synth.frame_zed(seed=2),
+             "100k": lambda: synth.frame_cpu100k(seed=0)}[which]()
     enc = CompressionPipeline([[1.0, 1.0]], device=dev, model=model)
     dec = DecompressionPipeline(device=dev, model=model)
     staged = enc.stage_frames([frame])
@@ -30,11 +32,12 @@ def main():
     if e2e:
         for _ in range(3):
             c, _ = enc.compress({"frames": [frame]})
+            dec.decompress(c[1])
         torch.cuda.synchronize()
     with profile(activities=[ProfilerActivity.CUDA] + ([] if e2e else [ProfilerActivity.CPU])) as prof:
         c, _ = (enc.compress({"frames": [frame]}) if e2e else enc.compress({"frames": [frame]}, staged=staged))
         torch.cuda.synchronize()
-        dec.decompress(c[1], to_host=False)
+        dec.decompress(c[1], to_host=e2e)
         torch.cuda.synchronize()
     evs = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
     ks = sorted(((e.time_range.start, e.time_range.end, e.name) for e in evs), key=lambda t: t[0])
