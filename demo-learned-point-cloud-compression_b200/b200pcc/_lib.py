@@ -48,6 +48,7 @@ SIGNATURES = {
     "pcc_ingest_frame": (INT, [P, P, I64, I32, P, P, P]),
     "pcc_ingest_points": (INT, [P, I64, I32, P, P]),
     "pcc_ingest_features": (INT, [P, P, I64, P, INT, P]),
+    "pcc_ingest_features_bf16": (INT, [P, P, I64, P, INT, P]),
     "pcc_unpack_output": (INT, [P, P, I64, P, P, P]),
     "pcc_coords_from_keys": (INT, [P, I64, P, P]),
     "pcc_sort_unique_workspace_bytes": (I64, [I64]),
@@ -102,6 +103,8 @@ SIGNATURES = {
     "pcc_container_frames_bytes": (I64, [I32, P, P, P]),
     "pcc_container_write_frames": (INT, [I32, C.c_double, C.c_double, P, P, P, P, P, P, I32, P, I64, P]),
     "pcc_container_parse_frames": (INT, [P, I64, I32, P, P, P, P, P, P, P, P, P, I32]),
+    "pcc_stage_h2d": (INT, [P, P, I32, P, P, I64, I32, I32, P]),
+    "pcc_host_f64_to_bf16": (None, [P, I64, P]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

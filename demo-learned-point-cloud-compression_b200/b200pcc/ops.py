@@ -148,6 +148,14 @@ def ingest_features(colors_f64: torch.Tensor, src_row: Optional[torch.Tensor], m
     return out
 
 
+def ingest_features_bf16(colors_bf16: torch.Tensor, src_row: Optional[torch.Tensor], m: int, c_dst: int = 16) -> torch.Tensor:
+    """The same from colours already rounded to bf16 [n,3] (staged with PCC_STAGE_F64_TO_BF16)."""
+    _need_cuda(colors_bf16, torch.bfloat16)
+    out = torch.empty((m, c_dst), dtype=torch.bfloat16, device=colors_bf16.device)
+    check(lib.pcc_ingest_features_bf16(_ptr(colors_bf16), _ptr(src_row), m, _ptr(out), c_dst, _stream()))
+    return out
+
+
 def unpack_output(keys: torch.Tensor, feats3: Optional[torch.Tensor], want_points: bool = True):
     """-> (points int32 [n,3] or None, colours float32 [n,3] clipped like the reference's pack_batches, or
     None when feats3 is None)."""

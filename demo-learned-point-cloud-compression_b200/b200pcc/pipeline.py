@@ -122,62 +122,61 @@ class _Stager:
 
 
 import os as _os
-_STAGE_PIECE = int(_os.environ.get("PCC_STAGE_PIECE_MB", "6")) << 20      # host copy and DMA are pipelined in pieces of about this size
+_STAGE_PIECE = int(float(_os.environ.get("PCC_STAGE_PIECE_MB", "1")) * (1 << 20))   # host copy and DMA are pipelined in pieces of this size
+_STAGE_THREADS = int(_os.environ.get("PCC_STAGE_THREADS", "6"))
 _STAGE_MODE = _os.environ.get("PCC_STAGE_MODE", "split")
 
 
 def _stage_concat(stager: "_Stager", arrays: List[np.ndarray], torch_dtype, width: int, dev_buf: torch.Tensor, stream=None,
-                  after=None, background=False):
+                  after=None, background=False, to_bf16=False):
     """Rows of all arrays back to back through pinned memory into dev_buf (viewed [rows, width]), on
     `stream` (after event `after`) when given, else on the current stream.  The host copy into pinned
-    memory and the DMA run at similar speeds, so the data moves in pieces: each worker thread copies a
-    piece and enqueues its DMA itself, and the bus is busy while the next pieces are being copied.
-    -> (device view, completion event or None)."""
+    memory and the DMA run at similar speeds, so the data moves in pieces (`pcc_stage_h2d`: native
+    threads copy a piece and enqueue its DMA themselves -- Python threads doing the same serialised on
+    the interpreter lock, one acquisition per piece).  to_bf16: float64 sources are converted on the way
+    (double -> float -> bf16, the device path's roundings) and arrive as 2 bytes per value; torch_dtype
+    then names the device view.  background=True: the call runs on a helper thread
+    (it releases the GIL) while the caller keeps enqueuing GPU work; the returned wait() joins it.
+    -> (device view, completion event / wait function / None)."""
     global _COPY_POOL
-    total = sum(a.nbytes for a in arrays)
+    import ctypes as C
+    from ._lib import lib, check
+    total = sum(a.nbytes for a in arrays) // (4 if to_bf16 else 1)
     if stager.buf is None or stager.buf.numel() < total:
         stager.buf = torch.empty(max(total, 1 << 20), dtype=torch.uint8, pin_memory=True)
-    hv = stager.buf.numpy()
-    pinned = stager.buf
     st = stream if stream is not None else torch.cuda.current_stream()
     if stream is not None and after is not None:
         stream.wait_event(after)
-    jobs, pos = [], 0
-    for a in arrays:
-        b = a.view(np.uint8).reshape(-1)
-        for o in range(0, b.size, _STAGE_PIECE):
-            jobs.append((b, o, min(o + _STAGE_PIECE, b.size), pos))
-        pos += b.size
+    n = len(arrays)
+    srcs = (C.c_void_p * max(n, 1))(*[a.ctypes.data for a in arrays])
+    sizes = (C.c_int64 * max(n, 1))(*[a.nbytes for a in arrays])
+    pinned_ptr, dev_ptr, st_ptr, device = stager.buf.data_ptr(), dev_buf.data_ptr(), st.cuda_stream, dev_buf.device
 
-    def job(j):
-        b, o, e, base = j
-        hv[base + o:base + e] = b[o:e]
-        with torch.cuda.stream(st):
-            dev_buf[base + o:base + e].copy_(pinned[base + o:base + e], non_blocking=True)
+    def job():
+        with torch.cuda.device(device):      # a helper thread starts on device 0
+            check(lib.pcc_stage_h2d(srcs, sizes, n, pinned_ptr, dev_ptr, _STAGE_PIECE, _STAGE_THREADS, int(to_bf16), st_ptr))
+        return arrays       # the sources stay alive until their copies are enqueued
     view = dev_buf[:total].view(torch_dtype).view(-1, width)
-    if _COPY_POOL is None:
-        from concurrent.futures import ThreadPoolExecutor
-        _COPY_POOL = ThreadPoolExecutor(max_workers=_COPY_THREADS, thread_name_prefix="b200pcc-stage")
-    if background:
-        # the caller keeps enqueuing GPU work while the workers copy; wait() joins them and returns the
-        # event that marks the last DMA
-        if len(jobs) == 1:       # small frame: a worker would only get the GIL when this thread blocks
-            job(jobs[0])
-            jobs = []
-        futures = [_COPY_POOL.submit(job, j) for j in jobs]
+    if background and total > _STAGE_PIECE:
+        if _COPY_POOL is None:
+            from concurrent.futures import ThreadPoolExecutor
+            _COPY_POOL = ThreadPoolExecutor(max_workers=_COPY_THREADS, thread_name_prefix="b200pcc-stage")
+        future = _COPY_POOL.submit(job)
 
         def wait():
-            for f in futures:
-                f.result()
+            future.result()
             ev = torch.cuda.Event()
             ev.record(st)
             return ev
         return view, wait
-    if len(jobs) <= 1:
-        for j in jobs:
-            job(j)
-    else:
-        list(_COPY_POOL.map(job, jobs))
+    if total:
+        job()
+    if background:       # small frame: copied inline (a helper would only get the GIL when this thread blocks)
+        def wait():
+            ev = torch.cuda.Event()
+            ev.record(st)
+            return ev
+        return view, wait
     done = None
     if stream is not None:
         done = torch.cuda.Event()
@@ -218,9 +217,11 @@ class CompressionPipeline:
 
     def _unpack_host_frames(self, frames, defer_features):
         """Host frames -> sparse tensor with the copies pipelined against the coordinate work: the points
-        (20 % of the bytes) go first and their keys are sorted while the host is still copying the float64
-        colours into pinned memory; the colours travel on a side stream and are only waited for when the
-        feature rows are built (after the coordinate pyramid when defer_features is set)."""
+        go first and their keys are sorted while native threads round the float64 colours to bf16 (the
+        precision the stem convolution reads them in: double -> float -> bf16, the device path's roundings)
+        into pinned memory, piece by piece, each piece's DMA following on a side stream; the colours are
+        only waited for when the feature rows are built (after the coordinate pyramid when defer_features
+        is set).  A frame of n points moves 12 n bytes instead of 30 n."""
         pts, cols = [], []
         for item in frames:
             if "points" not in item:      # "Sometimes we miss a frame?" (codec_pipeline.py:247-249)
@@ -232,7 +233,7 @@ class CompressionPipeline:
         total = sum(counts)
         dev = self.device
         pts_buf = torch.empty(max(total * 6, 8), dtype=torch.uint8, device=dev)
-        cols_buf = torch.empty(max(total * 24, 8), dtype=torch.uint8, device=dev)
+        cols_buf = torch.empty(max(total * 6, 8), dtype=torch.uint8, device=dev)     # bf16 [n,3]: converted while staged
         keys = torch.empty(total, dtype=torch.int64, device=dev)
         allocated = torch.cuda.Event()
         allocated.record()
@@ -242,9 +243,9 @@ class CompressionPipeline:
             ops.ingest_points(pts_d[pos:pos + counts[b]], b, keys[pos:pos + counts[b]])
             pos += counts[b]
         ukeys_all, src_all, cnt = ops.sort_unique(keys, want_src=True, sync=False)
-        cols_d, arrived = _stage_concat(self._stager_c, cols, torch.float64, 3, cols_buf, stream=ops._side_stream(dev, "h2d"),
-                                        after=allocated, background=True)
-        self.h2d_bytes += total * 30
+        cols_d, arrived = _stage_concat(self._stager_c, cols, torch.bfloat16, 3, cols_buf, stream=ops._side_stream(dev, "h2d"),
+                                        after=allocated, background=True, to_bf16=True)
+        self.h2d_bytes += total * 12
         m = int(cnt.item())
         x = SparseTensor(_cmap=CoordMap(ukeys_all[:m], 0), _feats=None, _channels=4)
         x.num_frames = nf
@@ -252,7 +253,7 @@ class CompressionPipeline:
 
         def finish_features():
             torch.cuda.current_stream().wait_event(arrived())      # joins the copy workers
-            x._feats = ops.ingest_features(cols_d, src, m, 16)
+            x._feats = ops.ingest_features_bf16(cols_d, src, m, 16)
         if defer_features:
             x._finish_features = finish_features
         else:

@@ -62,6 +62,20 @@ __global__ void k_ingest_features(const double* __restrict__ col, const int32_t*
   out[i * chunks16] = make_uint4(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b), 0u, 0u);
   for (int k = 1; k < chunks16; ++k) out[i * chunks16 + k] = make_uint4(0u, 0u, 0u, 0u);
 }
+__global__ void k_ingest_features_bf16(const uint16_t* __restrict__ col, const int32_t* __restrict__ src_row, int64_t m,
+                                       uint4* __restrict__ out, int chunks16) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  const int64_t r = src_row ? (int64_t)src_row[i] : i;
+  uint32_t c0 = 0, c1 = 0, c2 = 0;
+  if (r >= 0) {
+    c0 = col[3 * r];
+    c1 = col[3 * r + 1];
+    c2 = col[3 * r + 2];
+  }
+  out[i * chunks16] = make_uint4(0x3f80u | (c0 << 16), c1 | (c2 << 16), 0u, 0u);   // bf16(1) = 0x3f80
+  for (int k = 1; k < chunks16; ++k) out[i * chunks16 + k] = make_uint4(0u, 0u, 0u, 0u);
+}
 __global__ void k_coords_from_keys(const uint64_t* __restrict__ keys, int64_t n, int4* __restrict__ c) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -309,6 +323,16 @@ int pcc_ingest_features(const double* colors, const int32_t* src_row, int64_t m,
   if (m == 0) return PCC_OK;
   PCC_CHECK_ARG(colors && feats_bf16 && ((uintptr_t)feats_bf16 % 16) == 0);
   k_ingest_features<<<blocks_for(m), kThreads, 0, as_stream(s)>>>(colors, src_row, m, (uint4*)feats_bf16, c_dst / 8);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+int pcc_ingest_features_bf16(const void* colors_bf16, const int32_t* src_row, int64_t m, void* feats_bf16, int c_dst,
+                             pcc_stream_t s) {
+  PCC_CHECK_ARG(m >= 0 && c_dst >= 8 && c_dst % 8 == 0);
+  if (m == 0) return PCC_OK;
+  PCC_CHECK_ARG(colors_bf16 && feats_bf16 && ((uintptr_t)feats_bf16 % 16) == 0 && ((uintptr_t)colors_bf16 % 2) == 0);
+  k_ingest_features_bf16<<<blocks_for(m), kThreads, 0, as_stream(s)>>>((const uint16_t*)colors_bf16, src_row, m,
+                                                                      (uint4*)feats_bf16, c_dst / 8);
   PCC_LAUNCHED();
   return PCC_OK;
 }

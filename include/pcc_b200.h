@@ -62,6 +62,9 @@ int pcc_ingest_frame(const int16_t* points, const double* colors, int64_t n, int
 int pcc_ingest_points(const int16_t* points, int64_t n, int32_t batch, uint64_t* keys, pcc_stream_t s);
 int pcc_ingest_features(const double* colors, const int32_t* src_row, int64_t m, void* feats_bf16,
                         int c_dst, pcc_stream_t s);
+/* The same from colours already rounded to bf16 [n,3] (PCC_STAGE_F64_TO_BF16 staging). */
+int pcc_ingest_features_bf16(const void* colors_bf16, const int32_t* src_row, int64_t m, void* feats_bf16,
+                             int c_dst, pcc_stream_t s);
 /* Decoder output packing (pack_batches, codec_parallel.py:474-502): keys -> int32 [n,3] (x,y,z) and
  * colours [n,3] with NaN -> 0 and clip(c * 255, 0, 255) / 255 evaluated in fp32.  Either output may
  * be NULL (the decoder sends the points to the host while the colour head still runs). */
@@ -356,6 +359,24 @@ int pcc_container_write_frames(int32_t num_frames, double q_geo, double q_att, c
 int pcc_container_parse_frames(const uint8_t* data, int64_t nbytes, int32_t max_frames, int32_t* num_frames,
                                double* q_geo, double* q_att, int32_t* y_shapes, int32_t* z_shapes, pcc_span_t* y,
                                pcc_span_t* z, pcc_span_t* points, int32_t* ks, int32_t ks_ld);
+
+/* ------------------------------------------------------------------------------------------
+ * (7) host -> device staging of a raw frame (replaces torch.tensor(numpy, device=) of
+ *     sender/encoder/codec_pipeline.py:252-266, a pageable synchronous copy).  The n_src host arrays are
+ *     laid back to back; a pool of `threads` native threads (the caller is one of them) copies them into
+ *     `pinned` (page-locked, same layout) in pieces of piece_bytes and enqueues each piece's DMA to `dev`
+ *     on stream s as soon as that piece is copied.  Returns when every DMA is enqueued; the data is on
+ *     the device when s reaches that point.  Safe to call from several host threads.
+ *     convert = PCC_STAGE_F64_TO_BF16: the sources are float64 arrays and every value is converted on the way
+ *     (double -> float -> bf16, both round to nearest even: the roundings pcc_ingest_features applies), so
+ *     a colour travels as 2 bytes instead of 8; pinned / dev then hold nbytes / 4 per source, back to back.
+ * ------------------------------------------------------------------------------------------ */
+#define PCC_STAGE_COPY 0
+#define PCC_STAGE_F64_TO_BF16 1
+int pcc_stage_h2d(const void* const* srcs, const int64_t* nbytes, int32_t n_src, void* pinned, void* dev,
+                  int64_t piece_bytes, int32_t threads, int32_t convert, pcc_stream_t s);
+/* Host helper behind PCC_STAGE_F64_TO_BF16 (exported for tests and C hosts that stage by themselves). */
+void pcc_host_f64_to_bf16(const double* src, int64_t n, uint16_t* dst);
 
 #ifdef __cplusplus
 }

@@ -155,3 +155,51 @@ def test_launch_programs_equal_per_layer_path(model, dev, frames):
     assert res[True][0][1] == res[False][0][1] and res[True][0][2] == res[False][0][2]
     for a, b in zip(res[True][1], res[False][1]):
         assert np.array_equal(a["points"], b["points"]) and np.array_equal(a["colors"], b["colors"])
+
+
+def test_host_staging_equals_resident_frames(model, dev):
+    """compress(gop) stages host frames through pcc_stage_h2d (colours rounded double -> float -> bf16 by
+    native threads on the way) while compress(gop, staged=...) reads float64 colours already in HBM
+    (pcc_ingest_frame + pcc_rows_f32_to_bf16): same bitstream, for a frame large enough to be staged in
+    several pieces, with duplicate points (first wins) and awkward colour values."""
+    from b200pcc import synth
+    from b200pcc.pipeline import CompressionPipeline
+    big = synth.small_frame(seed=23, n_target=150_000)
+    rng = np.random.default_rng(3)
+    dup = rng.integers(0, len(big["points"]), 2000)
+    big["points"] = np.concatenate([big["points"], big["points"][dup]])
+    big["colors"] = np.concatenate([big["colors"], rng.random((2000, 3))])
+    big["colors"][:6, 0] = [0.0, 1.0, 0.00390625 * 1.001, 1e-45, 0.3 + 2.0 ** -10, 1.0 - 2.0 ** -9]   # ties and denormals
+    small = synth.small_frame(seed=24, n_target=5000)
+    enc = CompressionPipeline([[1.0, 1.0]], device=dev, model=model)
+    for frames in ([big], [small, big]):
+        host, _ = enc.compress({"frames": copy.deepcopy(frames)})
+        staged = enc.stage_frames(frames)
+        resident, _ = enc.compress({"frames": copy.deepcopy(frames)}, staged=staged)
+        assert host[1] == resident[1]
+
+
+def test_stage_h2d_copy_and_convert(dev):
+    """pcc_stage_h2d: several sources back to back, both modes, piece boundaries inside a source."""
+    import ctypes as C
+    from b200pcc._lib import lib, check
+    rng = np.random.default_rng(11)
+    srcs = [rng.random(n) * 2 - 0.5 for n in (1, 70_001, 0, 300_000)]
+    srcs[1][:3] = [np.nan, np.inf, -0.0]
+    total = sum(a.nbytes for a in srcs)
+    pinned = torch.empty(total, dtype=torch.uint8, pin_memory=True)
+    for convert in (0, 1):
+        out = torch.zeros(total, dtype=torch.uint8, device=dev)
+        ptrs = (C.c_void_p * len(srcs))(*[a.ctypes.data for a in srcs])
+        sizes = (C.c_int64 * len(srcs))(*[a.nbytes for a in srcs])
+        st = torch.cuda.current_stream()
+        check(lib.pcc_stage_h2d(ptrs, sizes, len(srcs), pinned.data_ptr(), out.data_ptr(), 64 << 10, 3, convert, st.cuda_stream))
+        st.synchronize()
+        flat = np.concatenate(srcs)
+        if convert:
+            got = out[: total // 4].view(torch.bfloat16).cpu()
+            want = torch.from_numpy(flat).to(torch.float32).to(torch.bfloat16)
+            ok = torch.isnan(want) | (got.view(torch.int16) == want.view(torch.int16))
+            assert bool(ok.all()) and bool(torch.isnan(got[1]))
+        else:
+            assert np.array_equal(out.cpu().numpy().view(np.float64), flat, equal_nan=True)

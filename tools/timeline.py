@@ -54,8 +54,10 @@ def main():
     small = sum(g for g, *_ in gaps if 0 < g <= 10)
     print(f"sum of gaps <= 10 us: {small / 1e3:.3f} ms over {sum(1 for g, *_ in gaps if 0 < g <= 10)} gaps")
     if e2e:
-        for a, b, n in ks[:60]:
-            print(f"  +{(a - t0) / 1e3:7.3f} ms  {(b - a):8.1f} us  {n[:80]}")
+        first_dec = next((i for i, k in enumerate(ks) if "octree_decode" in k[2]), len(ks))
+        for i, (a, b, n) in enumerate(ks):
+            if i < 12 or "Memcpy" in n or "ingest" in n or abs(i - first_dec) < 3 or i >= len(ks) - 4:
+                print(f"  +{(a - t0) / 1e3:7.3f} ms  {(b - a):8.1f} us  {n[:80]}")
     for g, at, n0, n1 in sorted(gaps, key=lambda x: -x[0])[:40]:
         print(f"gap {g:8.1f} us at {at:7.3f} ms  after {n0:50s} before {n1}")
 
