@@ -105,6 +105,7 @@ SIGNATURES = {
     "pcc_container_parse_frames": (INT, [P, I64, I32, P, P, P, P, P, P, P, P, P, I32]),
     "pcc_stage_h2d": (INT, [P, P, I32, P, P, I64, I32, I32, P]),
     "pcc_host_f64_to_bf16": (None, [P, I64, P]),
+    "pcc_host_copy_stream": (None, [P, I64, P]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

@@ -237,14 +237,51 @@ class CompressionPipeline:
         keys = torch.empty(total, dtype=torch.int64, device=dev)
         allocated = torch.cuda.Event()
         allocated.record()
-        pts_d, _ = _stage_concat(self._stager, pts, torch.int16, 3, pts_buf)
+        if total * 24 > _STAGE_PIECE:
+            # one helper thread drives both copies back to back (the native calls release the GIL): points
+            # first, then the colours, which therefore start converting at once instead of after this
+            # thread has enqueued the sort -- they are on the device before the pyramid is
+            global _COPY_POOL
+            if _COPY_POOL is None:
+                from concurrent.futures import ThreadPoolExecutor
+                _COPY_POOL = ThreadPoolExecutor(max_workers=_COPY_THREADS, thread_name_prefix="b200pcc-stage")
+            side = ops._side_stream(dev, "h2d")
+            side.wait_event(allocated)
+            pts_ready = threading.Event()
+            state = {}
+
+            def job():
+                try:
+                    with torch.cuda.device(dev):
+                        state["pts_view"], _ = _stage_concat(self._stager, pts, torch.int16, 3, pts_buf, stream=side)
+                        state["pts"] = torch.cuda.Event()
+                        state["pts"].record(side)
+                        pts_ready.set()
+                        state["cols_view"], state["cols"] = _stage_concat(self._stager_c, cols, torch.bfloat16, 3, cols_buf,
+                                                                          stream=side, to_bf16=True)
+                finally:
+                    pts_ready.set()
+            future = _COPY_POOL.submit(job)
+            pts_ready.wait()
+            if "pts" not in state:
+                future.result()          # raises what the helper raised
+            torch.cuda.current_stream().wait_event(state["pts"])
+            pts_d = state["pts_view"]
+
+            def arrived():
+                future.result()
+                return state["cols"]
+            cols_view = lambda: state["cols_view"]
+        else:
+            pts_d, _ = _stage_concat(self._stager, pts, torch.int16, 3, pts_buf)
+            cols_d0, arrived = _stage_concat(self._stager_c, cols, torch.bfloat16, 3, cols_buf,
+                                             stream=ops._side_stream(dev, "h2d"), after=allocated, background=True, to_bf16=True)
+            cols_view = lambda: cols_d0
         pos = 0
         for b in range(nf):
             ops.ingest_points(pts_d[pos:pos + counts[b]], b, keys[pos:pos + counts[b]])
             pos += counts[b]
         ukeys_all, src_all, cnt = ops.sort_unique(keys, want_src=True, sync=False)
-        cols_d, arrived = _stage_concat(self._stager_c, cols, torch.bfloat16, 3, cols_buf, stream=ops._side_stream(dev, "h2d"),
-                                        after=allocated, background=True, to_bf16=True)
         self.h2d_bytes += total * 12
         m = int(cnt.item())
         x = SparseTensor(_cmap=CoordMap(ukeys_all[:m], 0), _feats=None, _channels=4)
@@ -253,7 +290,7 @@ class CompressionPipeline:
 
         def finish_features():
             torch.cuda.current_stream().wait_event(arrived())      # joins the copy workers
-            x._feats = ops.ingest_features_bf16(cols_d, src, m, 16)
+            x._feats = ops.ingest_features_bf16(cols_view(), src, m, 16)
         if defer_features:
             x._finish_features = finish_features
         else:

@@ -75,7 +75,7 @@ class Pool {
       if (b.convert)
         pcc_host_f64_to_bf16((const double*)p.src, p.len / 8, (uint16_t*)p.pinned);
       else
-        memcpy(p.pinned, p.src, (size_t)p.len);
+        pcc_host_copy_stream(p.src, p.len, p.pinned);
       if (cur != b.device) {
         if (cudaSetDevice(b.device) != cudaSuccess) b.err.store(1);
         cur = b.device;

@@ -375,8 +375,11 @@ int pcc_container_parse_frames(const uint8_t* data, int64_t nbytes, int32_t max_
 #define PCC_STAGE_F64_TO_BF16 1
 int pcc_stage_h2d(const void* const* srcs, const int64_t* nbytes, int32_t n_src, void* pinned, void* dev,
                   int64_t piece_bytes, int32_t threads, int32_t convert, pcc_stream_t s);
-/* Host helper behind PCC_STAGE_F64_TO_BF16 (exported for tests and C hosts that stage by themselves). */
+/* Host helpers behind pcc_stage_h2d (exported for tests and C hosts that stage by themselves): the
+ * conversion of PCC_STAGE_F64_TO_BF16, and a memcpy with cache-bypassing stores (the DMA engine reads the
+ * pinned buffer next; lines left dirty in the CPU caches slow that read down). */
 void pcc_host_f64_to_bf16(const double* src, int64_t n, uint16_t* dst);
+void pcc_host_copy_stream(const void* src, int64_t nbytes, void* dst);
 
 #ifdef __cplusplus
 }
