@@ -106,6 +106,8 @@ SIGNATURES = {
     "pcc_stage_h2d": (INT, [P, P, I32, P, P, I64, I32, I32, P]),
     "pcc_host_f64_to_bf16": (None, [P, I64, P]),
     "pcc_host_copy_stream": (None, [P, I64, P]),
+    "pcc_pack_strings_header_bytes": (I64, [I32]),
+    "pcc_pack_strings": (INT, [P, P, I32, P, I64, P]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

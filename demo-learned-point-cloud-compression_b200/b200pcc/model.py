@@ -15,6 +15,7 @@ The layer graph is the canonical stand-in of config.py.  All sparse convolutions
 libpcc_b200.so: the persistent tcgen05 gather-GEMM kernel (narrow heads zero-padded to N = 16).
 """
 import math
+import threading
 from typing import List, Optional
 
 import numpy as np
@@ -24,6 +25,7 @@ from . import ops
 from . import config as cfgmod
 from . import program as prg
 from .sparse import CoordMap, SparseTensor
+from ._lib import lib, check, PccError
 
 SCALE_MIN, SCALE_MAX, SCALE_LEVELS = 0.11, 256.0, 64
 SCALE_BOUND = 0.11
@@ -535,19 +537,51 @@ class _CodedModel:
         return sym, status
 
 
+_FETCH = threading.local()
+
+
 def fetch_strings(pending, as_bytes: bool = True):
-    """[(device buffer, device size)] -> [bytes] with two host syncs for the whole list: one for the
-    sizes, one for the payloads (copied through a single packed device buffer).  as_bytes=False returns
-    memoryviews over the one host copy (the container writer joins them without another copy)."""
+    """[(device buffer, device int32 size)] -> [bytes] with ONE host wait in the steady state: the strings
+    are packed back to back on the device (`pcc_pack_strings`: lengths + payloads in one buffer) and the
+    host copies as many bytes as the previous call of this thread needed, plus a quarter; only when the
+    header then says there is more does a second copy follow.  as_bytes=False returns memoryviews over the
+    pinned host buffer, valid until this thread's next call (the container writer joins them at once)."""
     if not pending:
         return []
-    sizes = torch.cat([nb for _, nb in pending]).cpu().numpy()
-    packed = memoryview(torch.cat([buf[: int(nb)] for (buf, _), nb in zip(pending, sizes)]).cpu().numpy())
-    out, pos = [], 0
+    import ctypes as C
+    n = len(pending)
+    dev = pending[0][0].device
+    hdr = int(lib.pcc_pack_strings_header_bytes(n))
+    cap = hdr + sum((int(buf.numel()) + 15) // 16 * 16 for buf, _ in pending)
+    packed = torch.empty(cap, dtype=torch.uint8, device=dev)
+    bufs = (C.c_void_p * n)(*[buf.data_ptr() for buf, _ in pending])
+    lens = (C.c_void_p * n)(*[nb.data_ptr() for _, nb in pending])
+    check(lib.pcc_pack_strings(bufs, lens, n, packed.data_ptr(), cap, ops._stream()))
+    guess = min(cap, hdr + getattr(_FETCH, "guess", 1 << 18))
+    host = getattr(_FETCH, "host", None)
+    if host is None or host.numel() < guess:
+        host = _FETCH.host = torch.empty(max(guess * 2, 1 << 20), dtype=torch.uint8, pin_memory=True)
+    host[:guess].copy_(packed[:guess], non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    h32 = host[:hdr].numpy().view(np.uint32)
+    sizes = h32[:n].tolist()
+    end = int(h32[n + (n + 63) // 64 - 1])
+    if end > cap:
+        raise PccError(f"fetch_strings: the strings need {end} bytes, their buffers hold {cap}")
+    if end > guess:            # first call, or a GOP much larger than the last one
+        if host.numel() < end:
+            bigger = torch.empty(end * 2, dtype=torch.uint8, pin_memory=True)
+            bigger[:guess].copy_(host[:guess])
+            host = _FETCH.host = bigger
+        host[guess:end].copy_(packed[guess:end], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+    _FETCH.guess = (end - hdr) + (end - hdr) // 4 + 4096
+    mv = memoryview(host.numpy())
+    out, pos = [], hdr
     for nb in sizes:
-        v = packed[pos:pos + int(nb)]
+        v = mv[pos:pos + nb]
         out.append(v.tobytes() if as_bytes else v)
-        pos += int(nb)
+        pos += (nb + 15) // 16 * 16
     return out
 
 

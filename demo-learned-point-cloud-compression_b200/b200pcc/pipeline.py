@@ -123,7 +123,14 @@ class _Stager:
 
 import os as _os
 _STAGE_PIECE = int(float(_os.environ.get("PCC_STAGE_PIECE_MB", "1")) * (1 << 20))   # host copy and DMA are pipelined in pieces of this size
-_STAGE_THREADS = int(_os.environ.get("PCC_STAGE_THREADS", "6"))
+def _default_stage_threads() -> int:
+    # six threads saturate the host copy on one GPU; ranks of one node share the cores (torchrun exports
+    # LOCAL_WORLD_SIZE), so each takes its share but never fewer than two
+    ranks = max(int(_os.environ.get("LOCAL_WORLD_SIZE", _os.environ.get("WORLD_SIZE", "1")) or 1), 1)
+    return max(2, min(6, (_os.cpu_count() or 8) // ranks))
+
+
+_STAGE_THREADS = int(_os.environ.get("PCC_STAGE_THREADS", "0")) or _default_stage_threads()
 _STAGE_MODE = _os.environ.get("PCC_STAGE_MODE", "split")
 
 

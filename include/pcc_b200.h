@@ -381,6 +381,19 @@ int pcc_stage_h2d(const void* const* srcs, const int64_t* nbytes, int32_t n_src,
 void pcc_host_f64_to_bf16(const double* src, int64_t n, uint16_t* dst);
 void pcc_host_copy_stream(const void* src, int64_t nbytes, void* dst);
 
+/* ------------------------------------------------------------------------------------------
+ * (8) all byte strings of a GOP in one device buffer, so the host fetches them with a single copy
+ *     (the reference brings every string to the host on its own: codec_pipeline.py:305-306, 426-432,
+ *     441-462).  bufs[i] / lens[i] are device pointers to string i and to its int32 length counter (host
+ *     arrays of n pointers).  out = u32 len[n] | u32 end[ceil(n / 64)] | pad to 16 | payloads, each
+ *     starting on a 16-byte boundary, string 0 at pcc_pack_strings_header_bytes(n); end[last] is the
+ *     number of bytes used.  A string that does not fit in out_cap is left out (its length is still
+ *     written and end[] still advances: the caller compares end with what it copied).
+ * ------------------------------------------------------------------------------------------ */
+int64_t pcc_pack_strings_header_bytes(int32_t n);
+int pcc_pack_strings(const void* const* bufs, const int32_t* const* lens, int32_t n, uint8_t* out,
+                     int64_t out_cap, pcc_stream_t s);
+
 #ifdef __cplusplus
 }
 #endif

@@ -167,3 +167,46 @@ def test_rans_corrupt_stream_is_reported(model, dev):
     assert int(status.item()) != 0
     _, status = ops.rans_decode(good, 4096, torch.from_numpy(idx).to(dev), 1, n + 1, gc.tables)
     assert int(status.item()) == 3
+
+
+def test_pack_strings_one_buffer(dev):
+    """pcc_pack_strings: n strings with device-side lengths -> lengths + 16-byte aligned payloads in one
+    buffer; more than one launch batch (n > 64), empty strings, unaligned sources, capacity overflow."""
+    import ctypes as C
+    from b200pcc._lib import lib, check
+    rng = np.random.default_rng(9)
+    n = 150
+    lens = [0, 1, 15, 16, 17, 100_003] + [int(v) for v in rng.integers(0, 3000, n - 6)]
+    srcs = [rng.integers(0, 256, l + 3, dtype=np.uint8) for l in lens]
+    # odd-indexed strings start at an unaligned device address
+    bufs_d = [torch.from_numpy(s).to(dev)[(i & 1) * 3:] for i, s in enumerate(srcs)]
+    lens_d = [torch.tensor([l], dtype=torch.int32, device=dev) for l in lens]
+    hdr = lib.pcc_pack_strings_header_bytes(n)
+    assert hdr % 16 == 0 and hdr >= 4 * (n + 3)
+    need = hdr + sum((l + 15) // 16 * 16 for l in lens)
+    for cap in (need, need - 32):
+        out = torch.zeros(cap, dtype=torch.uint8, device=dev)
+        bp = (C.c_void_p * n)(*[b.data_ptr() for b in bufs_d])
+        lp = (C.c_void_p * n)(*[l.data_ptr() for l in lens_d])
+        check(lib.pcc_pack_strings(bp, lp, n, out.data_ptr(), cap, torch.cuda.current_stream().cuda_stream))
+        h = out.cpu().numpy()
+        h32 = h[:hdr].view(np.uint32)
+        assert h32[:n].tolist() == lens and int(h32[n + 2]) == need          # end[] says what a full copy needs
+        pos = hdr
+        for i, l in enumerate(lens):
+            if pos + l <= cap:
+                assert np.array_equal(h[pos:pos + l], srcs[i][(i & 1) * 3:(i & 1) * 3 + l]), i
+            pos += (l + 15) // 16 * 16
+
+
+def test_fetch_strings_guess_grows_and_shrinks(dev):
+    from b200pcc.model import fetch_strings
+    rng = np.random.default_rng(10)
+    for sizes in ([10, 0, 5000], [2_000_000, 3], [7], [300_000] * 3):
+        data = [rng.integers(0, 256, s, dtype=np.uint8) for s in sizes]
+        pending = [(torch.from_numpy(np.concatenate([d, np.zeros(64, np.uint8)])).to(dev),
+                    torch.tensor([len(d)], dtype=torch.int32, device=dev)) for d in data]
+        got = fetch_strings(pending)
+        assert [bytes(g) for g in got] == [d.tobytes() for d in data]
+        views = fetch_strings(pending, as_bytes=False)
+        assert [bytes(v) for v in views] == [d.tobytes() for d in data]
