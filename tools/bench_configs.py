@@ -110,8 +110,9 @@ def cfg5(model, dev, reps):
             enc.compress({"frames": [fresh(frame)]})
         ts = []
         for _ in range(reps):
+            gop = {"frames": [fresh(frame)]}
             t0 = time.perf_counter()
-            comp, side = enc.compress({"frames": [fresh(frame)]})
+            comp, side = enc.compress(gop)
             ts.append((time.perf_counter() - t0) * 1e3)
         bpp = [8.0 * len(comp[i + 1]) / n for i in range(len(settings))]
         tds = []
