@@ -220,7 +220,9 @@ def sort_unique(keys: torch.Tensor, want_src: bool = True, expect: Optional[int]
     n = keys.shape[0]
     dev = keys.device
     out = torch.empty(n, dtype=torch.int64, device=dev)
-    src = torch.empty(n, dtype=torch.int32, device=dev) if want_src else None
+    # sync=False callers may read all n rows before they know the count: rows past it must be benign (-1 = no row)
+    src = (torch.empty(n, dtype=torch.int32, device=dev) if sync or expect is not None else
+           torch.full((n,), -1, dtype=torch.int32, device=dev)) if want_src else None
     cnt = torch.empty(1, dtype=torch.int32, device=dev)
     wsb = lib.pcc_sort_unique_workspace_bytes(n)
     ws = workspace(wsb, dev)
@@ -280,13 +282,14 @@ def _side_stream(device, name: str = "readback") -> torch.cuda.Stream:
     return st
 
 
-def coords_pyramid(keys: torch.Tensor, log2_stride: int, levels: int, num_frames: int, overlap=None):
+def coords_pyramid(keys: torch.Tensor, log2_stride: int, levels: int, num_frames: int, overlap=None, extra=None):
     """All `levels` stride-2 coarsenings of a sorted key set with ONE host sync.
     -> (list of level keys, list of parent_row [rows of the finer level], host counts [levels],
         host frame offsets [(levels+1), num_frames+1] (row 0 = the input set), the same on the device).
     overlap: optional callable that enqueues independent work on the current stream; it runs after the
     pyramid kernels are launched, and the counts are read back on a side stream, so the host wait (and
-    the host-side bookkeeping that follows) is covered by that work instead of leaving the GPU idle."""
+    the host-side bookkeeping that follows) is covered by that work instead of leaving the GPU idle.
+    extra: optional device int32 counter fetched with the same wait (appended to the returned tuple)."""
     _need_cuda(keys, torch.int64)
     n = keys.shape[0]
     dev = keys.device
@@ -299,27 +302,38 @@ def coords_pyramid(keys: torch.Tensor, log2_stride: int, levels: int, num_frames
         check(lib.pcc_coords_pyramid(_ptr(keys), n, log2_stride, levels, _ptr(kout), _ptr(par), _ptr(meta),
                                      num_frames, meta.data_ptr() + 4 * levels if num_frames else None, _ptr(ws),
                                      ws.numel(), _stream()))
+    extra_host = None
     if overlap is None:
-        host = meta.cpu().numpy()              # the one sync
+        if extra is not None:
+            both = torch.cat([meta, extra.view(-1)[:1]]).cpu().numpy()
+            host, extra_host = both[:-1], int(both[-1])
+        else:
+            host = meta.cpu().numpy()              # the one sync
     else:
         ready = torch.cuda.Event()
         ready.record()
         overlap()
         side = _side_stream(dev)
-        host_t = torch.empty(meta.shape, dtype=meta.dtype, pin_memory=True)
+        host_t = torch.empty(meta.numel() + 1, dtype=meta.dtype, pin_memory=True)
         with torch.cuda.stream(side):
             side.wait_event(ready)
-            host_t.copy_(meta, non_blocking=True)
+            host_t[:-1].copy_(meta, non_blocking=True)
+            if extra is not None:
+                host_t[-1:].copy_(extra.view(-1)[:1], non_blocking=True)
             done = torch.cuda.Event()
             done.record()
         done.synchronize()                     # the one sync (pyramid kernels + 100-byte copy only)
-        host = host_t.numpy()
+        host = host_t.numpy()[:-1]
+        if extra is not None:
+            extra_host = int(host_t[-1])
     counts = [int(c) for c in host[:levels]]
     offs = host[levels:].reshape(levels + 1, nf1) if num_frames else None
     keys_l = [kout[l, :counts[l]] for l in range(levels)]
     n_fine = [n] + counts[:-1]
     par_l = [par[l, :n_fine[l]] for l in range(levels)]
     offs_dev = meta[levels:].view(levels + 1, nf1) if num_frames else None
+    if extra is not None:
+        return keys_l, par_l, counts, offs, offs_dev, extra_host
     return keys_l, par_l, counts, offs, offs_dev
 
 

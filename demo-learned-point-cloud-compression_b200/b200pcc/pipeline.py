@@ -222,7 +222,7 @@ class CompressionPipeline:
         nf = len(pts)
         return {"points": staged[:nf], "colors": staged[nf:]}
 
-    def _unpack_host_frames(self, frames, defer_features):
+    def _unpack_host_frames(self, frames, defer_features, speculate=False):
         """Host frames -> sparse tensor with the copies pipelined against the coordinate work: the points
         go first and their keys are sorted while native threads round the float64 colours to bf16 (the
         precision the stem convolution reads them in: double -> float -> bf16, the device path's roundings)
@@ -290,27 +290,30 @@ class CompressionPipeline:
             pos += counts[b]
         ukeys_all, src_all, cnt = ops.sort_unique(keys, want_src=True, sync=False)
         self.h2d_bytes += total * 12
-        m = int(cnt.item())
+        # speculate: capturer frames hold no duplicate points, so carry on as if all rows were unique and
+        # let compress() check the device count with the pyramid's read-back (one host wait fewer)
+        m = total if speculate else int(cnt.item())
         x = SparseTensor(_cmap=CoordMap(ukeys_all[:m], 0), _feats=None, _channels=4)
         x.num_frames = nf
-        src = src_all[:m]
+        x._unique = (cnt, ukeys_all, src_all) if speculate else None
 
         def finish_features():
             torch.cuda.current_stream().wait_event(arrived())      # joins the copy workers
-            x._feats = ops.ingest_features_bf16(cols_view(), src, m, 16)
+            rows = x.cmap.n
+            x._feats = ops.ingest_features_bf16(cols_view(), src_all[:rows], rows, 16)
         if defer_features:
             x._finish_features = finish_features
         else:
             finish_features()
         return x
 
-    def unpack_batch(self, gop, staged=None, defer_features=False):
+    def unpack_batch(self, gop, staged=None, defer_features=False, speculate=False):
         """frames list -> batched sparse tensor (codec_pipeline.py:239-267, shared/utils.py:10-42).
         `staged` (from stage_frames) skips the host->device copy: inputs already resident in HBM.
         defer_features: the caller runs x._finish_features() once it needs the feature rows."""
         frames = gop.pop("frames")
         if staged is None and _STAGE_MODE != "simple":
-            return self._unpack_host_frames(frames, defer_features), gop
+            return self._unpack_host_frames(frames, defer_features, speculate), gop
         if staged is None:
             staged = self.stage_frames(frames)
         pts, cols = staged["points"], staged["colors"]
@@ -324,10 +327,46 @@ class CompressionPipeline:
             n = int(pts[b].shape[0])
             ops.ingest_frame(pts[b], cols[b], b, keys[pos:pos + n], feats[pos:pos + n])
             pos += n
-        ukeys, src = ops.sort_unique(keys, want_src=True)
-        x = SparseTensor(_cmap=CoordMap(ukeys, 0), _feats=ops.rows_f32_to_bf16(feats, 16, src), _channels=4)
+        if speculate:      # see _unpack_host_frames
+            ukeys_all, src_all, cnt = ops.sort_unique(keys, want_src=True, sync=False)
+            x = SparseTensor(_cmap=CoordMap(ukeys_all, 0), _feats=ops.rows_f32_to_bf16(feats, 16, src_all), _channels=4)
+            x._unique = (cnt, ukeys_all, src_all)
+        else:
+            ukeys, src = ops.sort_unique(keys, want_src=True)
+            x = SparseTensor(_cmap=CoordMap(ukeys, 0), _feats=ops.rows_f32_to_bf16(feats, 16, src), _channels=4)
         x.num_frames = nf
         return x, gop
+
+    def _coordinate_pyramid(self, x, nf):
+        """Every coarser coordinate map (g_a: 3, h_a: 2) with one host wait, which also settles the number
+        of unique input points when unpack_batch() speculated on it.  The stride-1 kernel map and the stem
+        convolution do not depend on the pyramid: they run while the host waits and does its bookkeeping."""
+        g_a = self.compression_model.g_a
+        unique = getattr(x, "_unique", None)
+        x.cmap.build_pyramid(5, nf, overlap=lambda: g_a.prelaunch_stem(x), extra=unique[0] if unique else None)
+        if unique is None:
+            return x
+        x._unique = None
+        m = int(x.cmap.extra_host)
+        if m == x.cmap.n:
+            return x
+        # duplicate input points (first wins): everything enqueued so far ran on rows that do not exist --
+        # redo the coordinate work for the m unique rows
+        _, ukeys_all, src_all = unique
+        y = SparseTensor(_cmap=CoordMap(ukeys_all[:m], 0), _feats=None if x._feats is None else x._feats[:m],
+                         _channels=x._channels)
+        y.num_frames = nf
+        y._finish_features = getattr(x, "_finish_features", None)
+        if y._finish_features is not None:
+            finish, y._finish_features = y._finish_features, None
+
+            def finish_features():
+                x.cmap = y.cmap
+                finish()
+                y._feats = x._feats
+            y._finish_features = finish_features
+        y.cmap.build_pyramid(5, nf, overlap=lambda: g_a.prelaunch_stem(y))
+        return y
 
     def analysis_step(self, x):
         return self.compression_model.g_a(x)
@@ -379,13 +418,10 @@ class CompressionPipeline:
             compressed_data = {0: data["frames"]}
             tm = _StageTimer()
             tm.mark("start")
-            x, sideinfo = self.unpack_batch(data, staged, defer_features=True)
-            num_points = x.cmap.n
+            x, sideinfo = self.unpack_batch(data, staged, defer_features=True, speculate=True)
             nf = x.num_frames
-            # every coarser coordinate map (g_a: 3, h_a: 2) with one host sync
-            # (the stride-1 kernel map and the stem convolution do not depend on the pyramid: they run while
-            # the host waits for the level sizes and does its bookkeeping)
-            x.cmap.build_pyramid(5, nf, overlap=lambda: self.compression_model.g_a.prelaunch_stem(x))
+            x = self._coordinate_pyramid(x, nf)
+            num_points = x.cmap.n
             ycm = x.cmap.coarse.coarse.coarse
             if getattr(x, "_finish_features", None) is not None:
                 x._finish_features()          # waits for the colours, which travelled during the coordinate work

@@ -77,16 +77,19 @@ class CoordMap:
             self.parent_row = parent
         return self.coarse
 
-    def build_pyramid(self, levels: int, num_frames: int = 0, overlap=None):
+    def build_pyramid(self, levels: int, num_frames: int = 0, overlap=None, extra=None):
         """Precompute the next `levels` coarser maps (and per-frame row counts of every level) with a
         single host sync, instead of one sync per downsample().  Returns the host frame offsets
-        [(levels+1), num_frames+1] (row 0 = this map) or None."""
+        [(levels+1), num_frames+1] (row 0 = this map) or None.  extra: a device int32 counter fetched with
+        the same wait; its value is left in self.extra_host."""
         have, cm = 0, self
         while cm.coarse is not None and have < levels:
             cm, have = cm.coarse, have + 1
         if have >= levels and (num_frames == 0 or self.frame_off_host is not None):
             return self.frame_off_host
-        keys_l, par_l, counts, offs, offs_dev = ops.coords_pyramid(self.keys, self.log2_stride, levels, num_frames, overlap)
+        res = ops.coords_pyramid(self.keys, self.log2_stride, levels, num_frames, overlap, extra)
+        keys_l, par_l, counts, offs, offs_dev = res[:5]
+        self.extra_host = res[5] if extra is not None else None
         cm = self
         for l in range(levels):
             cm.coarse = CoordMap(keys_l[l], cm.log2_stride + 1)

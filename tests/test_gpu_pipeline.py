@@ -203,3 +203,31 @@ def test_stage_h2d_copy_and_convert(dev):
             assert bool(ok.all()) and bool(torch.isnan(got[1]))
         else:
             assert np.array_equal(out.cpu().numpy().view(np.float64), flat, equal_nan=True)
+
+
+def test_duplicate_input_points_first_wins(model, dev):
+    """compress() speculates that the input holds no duplicate points and checks the device count with the
+    pyramid's read-back; a frame WITH duplicates must fall back and code exactly what its de-duplicated
+    (first occurrence wins, ME.SparseTensor semantics) version codes -- host buffers and resident frames."""
+    from b200pcc import synth
+    from b200pcc.pipeline import CompressionPipeline, DecompressionPipeline
+    base = synth.small_frame(seed=25, n_target=30_000)
+    rng = np.random.default_rng(4)
+    dup = rng.integers(0, len(base["points"]), 500)
+    frame = {"points": np.concatenate([base["points"], base["points"][dup]]),
+             "colors": np.concatenate([base["colors"], rng.random((500, 3))])}
+    order = rng.permutation(len(frame["points"]))
+    frame = {"points": frame["points"][order], "colors": frame["colors"][order]}
+    _, first = np.unique(frame["points"], axis=0, return_index=True)
+    first.sort()
+    dedup = {"points": frame["points"][first], "colors": frame["colors"][first]}
+    assert len(dedup["points"]) == len(base["points"]) < len(frame["points"])
+    enc = CompressionPipeline([[1.0, 1.0]], device=dev, model=model)
+    dec = DecompressionPipeline(device=dev, model=model)
+    want, side_w = enc.compress({"frames": [copy.deepcopy(dedup)]})
+    got, side_g = enc.compress({"frames": [copy.deepcopy(frame)]})
+    assert got[1] == want[1] and side_g["gop_info"]["num_points"] == len(dedup["points"])
+    resident, _ = enc.compress({"frames": [copy.deepcopy(frame)]}, staged=enc.stage_frames([frame]))
+    assert resident[1] == want[1]
+    out, _ = dec.decompress(got[1])
+    assert out[0]["points"].shape == (len(dedup["points"]), 3)
