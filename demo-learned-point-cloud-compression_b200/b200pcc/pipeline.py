@@ -68,27 +68,17 @@ def _require_cuda(device):
 
 _COPY_POOL = None
 _COPY_THREADS = 4
-_COPY_CHUNK = 2 << 20
 
 
 def _parallel_copy(dst: np.ndarray, src: np.ndarray) -> None:
-    """dst[:] = src for flat uint8 arrays; large copies are split over a few threads (numpy releases
-    the GIL inside the memcpy), because one core moves a 24 MB frame at ~15 GB/s at best and that host
-    copy is the largest single item of the end-to-end encode."""
-    global _COPY_POOL
+    """dst[:] = src for flat uint8 arrays headed for a DMA: anything sizeable goes through
+    pcc_host_copy_stream (non-temporal stores, so the DMA engine does not read cache-dirty lines)."""
     n = src.size
-    if n < 2 * _COPY_CHUNK:
+    if n < (64 << 10):
         dst[:n] = src
         return
-    if _COPY_POOL is None:
-        from concurrent.futures import ThreadPoolExecutor
-        _COPY_POOL = ThreadPoolExecutor(max_workers=_COPY_THREADS, thread_name_prefix="b200pcc-stage")
-    step = (n + _COPY_THREADS - 1) // _COPY_THREADS
-    step = (step + 4095) // 4096 * 4096
-
-    def job(a):
-        dst[a:min(a + step, n)] = src[a:min(a + step, n)]
-    list(_COPY_POOL.map(job, range(0, n, step)))
+    from ._lib import lib
+    lib.pcc_host_copy_stream(src.ctypes.data, n, dst.ctypes.data)
 
 
 class _Stager:
