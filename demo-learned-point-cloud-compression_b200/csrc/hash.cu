@@ -224,6 +224,10 @@ k_kmap_k3_blocks(const uint64_t* __restrict__ keys, int64_t n, int l, const uint
   const int ly = (uy - 1) >> 2, hy = (uy + 1) >> 2;
   const int lz = (uz - 1) >> 2, hz = (uz + 1) >> 2;
   const uint64_t fbits = ((uint64_t)(uint32_t)b << 48) >> (3 * l + 6);
+  // Morton bits of the two candidate block coordinates per axis, spread once (not once per corner)
+  const uint64_t sx[2] = {spread3_16((uint32_t)lx), spread3_16((uint32_t)hx)};
+  const uint64_t sy[2] = {spread3_16((uint32_t)ly) << 1, spread3_16((uint32_t)hy) << 1};
+  const uint64_t sz[2] = {spread3_16((uint32_t)lz) << 2, spread3_16((uint32_t)hz) << 2};
 #pragma unroll
   for (int c = 0; c < 8; ++c) {
     const int ax = c & 1, ay = (c >> 1) & 1, az = c >> 2;
@@ -235,8 +239,7 @@ k_kmap_k3_blocks(const uint64_t* __restrict__ keys, int64_t n, int l, const uint
     uint4 e = make_uint4(0u, 0u, 0u, 0u);
     if (bx >= 0 && by >= 0 && bz >= 0 && bx <= bmax && by <= bmax && bz <= bmax) {
       // block key = pack_key(b, block corner) >> (3l + 6) = frame bits | morton(bx, by, bz)
-      const uint64_t bkey = fbits | spread3_16((uint32_t)bx) | (spread3_16((uint32_t)by) << 1) |
-                            (spread3_16((uint32_t)bz) << 2);
+      const uint64_t bkey = fbits | sx[ax] | sy[ay] | sz[az];
       const BlockEntry be = block_lookup(bkey, tk, tv, cap_mask);
       const uint32_t lo = (uint32_t)be.mask, hi = (uint32_t)(be.mask >> 32);
       e = make_uint4(lo, hi, (uint32_t)be.base, (uint32_t)be.base + (uint32_t)__popc(lo));

@@ -10,6 +10,8 @@
 #include <thread>
 #include <vector>
 
+#include <unistd.h>
+
 #include "common.cuh"
 
 // host_convert.cpp (declared in include/pcc_b200.h)
@@ -36,16 +38,28 @@ struct Batch {
 
 class Pool {
  public:
+  // one pool per process: a child created by fork() inherits the object but not its threads, so it gets a
+  // fresh pool (the inherited one is abandoned, never destroyed: its mutex state is unknown)
   static Pool& get() {
-    static Pool p;
-    return p;
+    static std::mutex guard;
+    static Pool* pool = nullptr;
+    static pid_t owner = 0;
+    std::lock_guard<std::mutex> lk(guard);
+    if (!pool || owner != getpid()) {
+      pool = new Pool();
+      owner = getpid();
+    }
+    return *pool;
   }
   // runs the batch on `threads` workers (the caller is one of them) and returns when every piece is enqueued
   int run(Batch& b, int threads) {
     const int helpers = threads - 1;
     {
       std::lock_guard<std::mutex> lk(mu);
-      while ((int)workers.size() < helpers) workers.emplace_back([this] { loop(); });
+      while (nworkers < helpers) {
+        std::thread([this] { loop(); }).detach();
+        ++nworkers;
+      }
       b.pending = helpers;
       for (int i = 0; i < helpers; ++i) queue.push_back(&b);
     }
@@ -57,15 +71,7 @@ class Pool {
   }
 
  private:
-  Pool() = default;
-  ~Pool() {
-    {
-      std::lock_guard<std::mutex> lk(mu);
-      stop = true;
-    }
-    cv.notify_all();
-    for (auto& t : workers) t.join();
-  }
+  Pool() = default;     // lives until the process exits; its idle workers are detached
   static void work(Batch& b) {
     int cur = -1;
     for (;;) {
@@ -88,8 +94,7 @@ class Pool {
       Batch* b = nullptr;
       {
         std::unique_lock<std::mutex> lk(mu);
-        cv.wait(lk, [&] { return stop || !queue.empty(); });
-        if (stop) return;
+        cv.wait(lk, [&] { return !queue.empty(); });
         b = queue.back();
         queue.pop_back();
       }
@@ -103,9 +108,8 @@ class Pool {
   }
   std::mutex mu;
   std::condition_variable cv, done;
-  std::vector<std::thread> workers;
+  int nworkers = 0;
   std::vector<Batch*> queue;
-  bool stop = false;
 };
 
 }  // namespace
