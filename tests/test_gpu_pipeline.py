@@ -231,3 +231,51 @@ def test_duplicate_input_points_first_wins(model, dev):
     assert resident[1] == want[1]
     out, _ = dec.decompress(got[1])
     assert out[0]["points"].shape == (len(dedup["points"]), 3)
+
+
+def test_malformed_bitstreams_raise_and_leave_the_device_usable(model, dev):
+    """decompress() on damaged input: truncated blobs, flipped bytes in the y / z strings and in the
+    coordinate stream, inconsistent counts.  Every case either raises (ValueError / PccError) or returns
+    frames of the advertised shape -- never a CUDA fault -- and a clean blob decodes identically afterwards."""
+    import struct
+    from b200pcc import synth, container
+    from b200pcc._lib import PccError
+    from b200pcc.pipeline import CompressionPipeline, DecompressionPipeline
+    frame = synth.small_frame(seed=26, n_target=12_000)
+    enc = CompressionPipeline([[1.0, 1.0]], device=dev, model=model)
+    dec = DecompressionPipeline(device=dev, model=model)
+    comp, _ = enc.compress({"frames": [copy.deepcopy(frame)]})
+    blob = comp[1]
+    want, _ = dec.decompress(blob)
+    y, z, ysh, zsh, pts, ks, q = container.read_bitstream_batched(blob)
+    y0 = 36                      # App. B.1: 20-byte head + 16 bytes of shapes / lengths
+    z0 = y0 + len(y[0])
+    p0 = z0 + len(z[0]) + 16
+    rng = np.random.default_rng(8)
+
+    def damaged(lo, hi, count):
+        b = bytearray(blob)
+        for pos in rng.integers(lo, hi, count):
+            b[pos] ^= 0xFF
+        return bytes(b)
+
+    cases = [blob[:10], blob[:y0 + 50], blob[:-1], blob[:p0 + 3],
+             damaged(y0 + 400, z0, 1), damaged(y0 + 400, z0, 40), damaged(y0, y0 + 16, 2),      # y payload / header
+             damaged(z0 + 150, p0 - 16, 3), damaged(z0, z0 + 16, 1),                             # z payload / header
+             damaged(p0 + 40, len(blob), 2), damaged(p0, p0 + 12, 1),                            # octree bytes / header
+             blob[:28] + struct.pack(">i", ysh + 1) + blob[32:],                                  # y shape off by one
+             container.make_bitstream_batched(y[0], z[0], ysh, zsh, pts, [[2 ** 31 - 1], [0], [7]], q),   # absurd k
+             container.make_bitstream_batched(y[0], z[0], ysh, zsh + 5, pts, ks, q)]             # wrong z shape
+    outcomes = []
+    for i, bad in enumerate(cases):
+        try:
+            out, _ = dec.decompress(bad)
+            assert len(out) == 1 and out[0]["points"].ndim == 2 and out[0]["points"].shape[1] == 3, i
+            assert out[0]["colors"].shape == out[0]["points"].shape, i
+            outcomes.append("decoded")
+        except (ValueError, PccError) as e:
+            outcomes.append(type(e).__name__)
+        torch.cuda.synchronize()          # a device fault would surface here
+    assert outcomes[:4] == ["ValueError"] * 4 and "decoded" not in outcomes[11:12] + outcomes[13:], outcomes
+    again, _ = dec.decompress(blob)
+    assert np.array_equal(again[0]["points"], want[0]["points"]) and np.array_equal(again[0]["colors"], want[0]["colors"])
