@@ -50,6 +50,7 @@ SIGNATURES = {
     "pcc_ingest_features": (INT, [P, P, I64, P, INT, P]),
     "pcc_ingest_features_bf16": (INT, [P, P, I64, P, INT, P]),
     "pcc_unpack_output": (INT, [P, P, I64, P, P, P]),
+    "pcc_pack_visualizer": (INT, [P, P, I64, F32, P, P, P]),
     "pcc_coords_from_keys": (INT, [P, I64, P, P]),
     "pcc_sort_unique_workspace_bytes": (I64, [I64]),
     "pcc_sort_unique": (INT, [P, I64, P, P, P, P, I64, P]),

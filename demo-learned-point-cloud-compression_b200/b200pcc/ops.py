@@ -148,6 +148,18 @@ def ingest_features(colors_f64: torch.Tensor, src_row: Optional[torch.Tensor], m
     return out
 
 
+def pack_visualizer(keys: torch.Tensor, feats3: torch.Tensor, offset: float = 100.0):
+    """-> (points float32 [n,3] = xyz + offset, colours uint8 [n,3]): the client's playout buffer
+    (receiver/client/client.py:139-146) built on the device."""
+    _need_cuda(keys, torch.int64)
+    _need_cuda(feats3, torch.float32)
+    n = keys.shape[0]
+    pts = torch.empty((n, 3), dtype=torch.float32, device=keys.device)
+    col = torch.empty((n, 3), dtype=torch.uint8, device=keys.device)
+    check(lib.pcc_pack_visualizer(_ptr(keys), _ptr(feats3), n, float(offset), _ptr(pts), _ptr(col), _stream()))
+    return pts, col
+
+
 def ingest_features_bf16(colors_bf16: torch.Tensor, src_row: Optional[torch.Tensor], m: int, c_dst: int = 16) -> torch.Tensor:
     """The same from colours already rounded to bf16 [n,3] (staged with PCC_STAGE_F64_TO_BF16)."""
     _need_cuda(colors_bf16, torch.bfloat16)

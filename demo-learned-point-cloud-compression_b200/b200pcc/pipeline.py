@@ -575,6 +575,26 @@ class DecompressionPipeline:
         P, Cc = pts_h.numpy(), col_h.numpy()
         return [{"points": P[off[i]:off[i + 1]], "colors": Cc[off[i]:off[i + 1]]} for i in range(num_frames)]
 
+    def playout_buffers(self, x_hat, num_frames: int = None, offset: float = 100.0):
+        """Device reconstruction (decompress(..., to_host=False)) -> one playout buffer per frame, as the
+        client builds them for the visualizer (receiver/client/client.py:139-146): float32 (points + offset)
+        bytes followed by uint8 (255 * colours) bytes.  Packed on the device: 15 bytes per point cross
+        the bus instead of 24, and the host neither scales nor converts."""
+        with self._lock, torch.cuda.device(self.device), ops.stream_scope():
+            keys = x_hat.cmap.keys
+            n = x_hat.cmap.n
+            nf = num_frames if num_frames is not None else (int((keys[-1:] >> 48).item()) + 1 if n else 0)
+            pts_d, col_d = ops.pack_visualizer(keys, x_hat._feats, offset)
+            pts_h = torch.empty((n, 3), dtype=torch.float32, pin_memory=True)
+            col_h = torch.empty((n, 3), dtype=torch.uint8, pin_memory=True)
+            pts_h.copy_(pts_d, non_blocking=True)
+            col_h.copy_(col_d, non_blocking=True)
+            off = ops.frame_offsets(keys, nf).cpu().numpy()          # (synchronises: the copies above are done)
+            torch.cuda.current_stream().synchronize()
+            self.d2h_bytes += 15 * n
+            P, Cc = pts_h.numpy(), col_h.numpy()
+            return [P[off[i]:off[i + 1]].tobytes() + Cc[off[i]:off[i + 1]].tobytes() for i in range(nf)]
+
     def decompress(self, compressed_data, to_host=True):
         """bytes -> (frames, sideinfo).  to_host=False leaves the reconstruction on the device (returns
         the SparseTensor instead of the per-frame numpy dicts)."""

@@ -108,6 +108,28 @@ __global__ void k_unpack_output(const uint64_t* __restrict__ keys, const float* 
   }
 }
 
+// playout buffer of the client (receiver/client/client.py:139-146): points + offset as float32 [n,3], then
+// colours uint8 [n,3] = trunc(255 * colour) with colour as pack_batches leaves it (k_unpack_output), every
+// step in fp32 like numpy does it
+__global__ void k_pack_visualizer(const uint64_t* __restrict__ keys, const float* __restrict__ feats, int64_t n,
+                                  float offset, float* __restrict__ pts, uint8_t* __restrict__ col) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int b, x, y, z;
+  unpack_key(keys[i], b, x, y, z);
+  pts[3 * i] = __fadd_rn((float)x, offset);
+  pts[3 * i + 1] = __fadd_rn((float)y, offset);
+  pts[3 * i + 2] = __fadd_rn((float)z, offset);
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    float v = feats[3 * i + c];
+    if (v != v) v = 0.0f;
+    float t = fminf(fmaxf(__fmul_rn(v, 255.0f), 0.0f), 255.0f);
+    t = __fmul_rn(255.0f, __fdiv_rn(t, 255.0f));
+    col[3 * i + c] = (uint8_t)(int)t;      // 0 <= t <= 255: truncation like ndarray.astype(uint8)
+  }
+}
+
 __global__ void k_iota(int32_t* v, int64_t n) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i < n) v[i] = (int32_t)i;
@@ -342,6 +364,15 @@ int pcc_unpack_output(const uint64_t* keys, const float* feats3, int64_t n, int3
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG((points || colors) && (!points || keys) && (!colors || feats3));
   k_unpack_output<<<blocks_for(n), kThreads, 0, as_stream(s)>>>(keys, feats3, n, points, colors);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+int pcc_pack_visualizer(const uint64_t* keys, const float* feats3, int64_t n, float offset, float* points_f32,
+                        uint8_t* colors_u8, pcc_stream_t s) {
+  PCC_CHECK_ARG(n >= 0);
+  if (n == 0) return PCC_OK;
+  PCC_CHECK_ARG(keys && feats3 && points_f32 && colors_u8);
+  k_pack_visualizer<<<blocks_for(n), kThreads, 0, as_stream(s)>>>(keys, feats3, n, offset, points_f32, colors_u8);
   PCC_LAUNCHED();
   return PCC_OK;
 }

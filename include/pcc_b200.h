@@ -70,6 +70,11 @@ int pcc_ingest_features_bf16(const void* colors_bf16, const int32_t* src_row, in
  * be NULL (the decoder sends the points to the host while the colour head still runs). */
 int pcc_unpack_output(const uint64_t* keys, const float* feats3, int64_t n, int32_t* points, float* colors,
                       pcc_stream_t s);
+/* The client's playout buffer straight from the decoder output (receiver/client/client.py:139-146, SURVEY
+ * 8f row f-4): points + offset as float32 [n,3] and colours as uint8 [n,3] = trunc(255 * colour), colour as
+ * pcc_unpack_output leaves it -- 15 bytes per point to bring to the host instead of 24. */
+int pcc_pack_visualizer(const uint64_t* keys, const float* feats3, int64_t n, float offset, float* points_f32,
+                        uint8_t* colors_u8, pcc_stream_t s);
 /* keys -> int32 [n,4] (b,x,y,z): the `.C` attribute. */
 int pcc_coords_from_keys(const uint64_t* keys, int64_t n, int32_t* coords, pcc_stream_t s);
 

@@ -279,3 +279,22 @@ def test_malformed_bitstreams_raise_and_leave_the_device_usable(model, dev):
     assert outcomes[:4] == ["ValueError"] * 4 and "decoded" not in outcomes[11:12] + outcomes[13:], outcomes
     again, _ = dec.decompress(blob)
     assert np.array_equal(again[0]["points"], want[0]["points"]) and np.array_equal(again[0]["colors"], want[0]["colors"])
+
+
+def test_playout_buffers_match_client_packing(model, dev, frames):
+    """DecompressionPipeline.playout_buffers == what receiver/client/client.py:139-146 builds from the
+    decoded frames: float32 (points + 100) bytes + uint8 (255 * colours) bytes, per frame."""
+    from b200pcc.pipeline import CompressionPipeline, DecompressionPipeline
+    enc = CompressionPipeline([[1.0, 1.0]], device=dev, model=model)
+    dec = DecompressionPipeline(device=dev, model=model)
+    comp, _ = enc.compress(_gop(frames))
+    host, _ = dec.decompress(comp[1])
+    x_hat, _ = dec.decompress(comp[1], to_host=False)
+    got = dec.playout_buffers(x_hat)
+    assert len(got) == len(host) == len(frames)
+    for buf, frame in zip(got, host):
+        points = frame["points"] + 100
+        colors = 255 * frame["colors"]
+        want = np.array(points, dtype=np.float32).tobytes() + np.array(colors, dtype=np.uint8).tobytes()
+        assert buf == want
+    assert dec.playout_buffers(x_hat, num_frames=len(frames)) == got
