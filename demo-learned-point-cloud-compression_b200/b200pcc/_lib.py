@@ -109,6 +109,8 @@ SIGNATURES = {
     "pcc_host_copy_stream": (None, [P, I64, P]),
     "pcc_pack_strings_header_bytes": (I64, [I32]),
     "pcc_pack_strings": (INT, [P, P, I32, P, I64, P]),
+    "pcc_capture_voxelize_workspace_bytes": (I64, [I64]),
+    "pcc_capture_voxelize": (INT, [P, I64, C.c_double, F32, I32, P, P, I64, P, P, I64, P]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

@@ -226,6 +226,29 @@ def clear_deferred():
     _TLS.deferred = []
 
 
+def capture_voxelize(xyzrgba: torch.Tensor, voxel_size: float, depth_clip: float, max_points: Optional[int] = None):
+    """XYZRGBA measure float32 [n_px, 4] -> (points int16 [cap,3], colours float64 [cap,3], count int32 [1]), all on
+    the device, nothing waited for (sender/capturer/capturer.py:84-120; see pcc_capture_voxelize)."""
+    _need_cuda(xyzrgba, torch.float32)
+    if xyzrgba.dim() != 2 or xyzrgba.shape[1] != 4:
+        raise _lib.PccError(f"capture_voxelize: expected [n, 4] float32, got {tuple(xyzrgba.shape)}")
+    n = xyzrgba.shape[0]
+    dev = xyzrgba.device
+    mp = int(max_points) if max_points is not None else 0
+    if mp < 0:
+        raise _lib.PccError("capture_voxelize: max_points must be positive or None")
+    cap = min(n, mp) if mp > 0 else n
+    pts = torch.empty((cap, 3), dtype=torch.int16, device=dev)
+    col = torch.empty((cap, 3), dtype=torch.float64, device=dev)
+    cnt = torch.empty(1, dtype=torch.int32, device=dev)
+    wsb = lib.pcc_capture_voxelize_workspace_bytes(n)
+    ws = workspace(wsb, dev)
+    with _prof("capture_voxelize", n * 16 + cap * 30):
+        check(lib.pcc_capture_voxelize(_ptr(xyzrgba), n, float(voxel_size), float(depth_clip), mp, _ptr(pts), _ptr(col),
+                                       cap, _ptr(cnt), _ptr(ws), ws.numel(), _stream()))
+    return pts, col, cnt
+
+
 def sort_unique(keys: torch.Tensor, want_src: bool = True, expect: Optional[int] = None, sync: bool = True):
     """-> (unique sorted keys, src_row or None).  One host sync for the count, none with `expect`."""
     _need_cuda(keys, torch.int64)

@@ -399,6 +399,27 @@ int64_t pcc_pack_strings_header_bytes(int32_t n);
 int pcc_pack_strings(const void* const* bufs, const int32_t* const* lens, int32_t n, uint8_t* out,
                      int64_t out_cap, pcc_stream_t s);
 
+/* ------------------------------------------------------------------------------------------
+ * (9) capturer frame preparation on the device (capture half; replaces the numpy +
+ *     Open3D body of Capturer.get_zed_frames, sender/capturer/capturer.py:84-120).  xyzrgba = the camera's
+ *     XYZRGBA measure, float32 [n_px, 4] on the device (16-byte aligned; the colour float carries r, g, b in
+ *     its three low bytes, :87-90).  Pixels that are not finite or farther than depth_clip (float32 norm,
+ *     :93-94) are dropped; the rest is voxel-down-sampled as Open3D does it in float64 (:99-106: bound =
+ *     min - voxel_size / 2, index = floor((p - bound) / voxel_size), running sums in input order, mean),
+ *     rounded half-to-even to the voxel grid as int16 (:107), de-duplicated keeping the first row in
+ *     (x,y,z) order (:110-112) and, when max_points > 0 and more rows are left, cut to the max_points rows of
+ *     largest z (:117-120).  Where the reference leaves an order to its libraries (unordered_map iteration,
+ *     argpartition ties) this follows oracle/capture_ref.py: voxels in ascending index order, z ties to the
+ *     earlier row, output in (x,y,z) order.
+ *     Output: points int16 [m,3], colors float64 [m,3] (capacity rows each), *n_out_dev = m, or -1 when a
+ *     voxel index needs more than 21 bits, -2 when a rounded coordinate leaves int16; rows beyond capacity
+ *     are not written (m is still reported).  No host synchronisation.
+ * ------------------------------------------------------------------------------------------ */
+int64_t pcc_capture_voxelize_workspace_bytes(int64_t n_px);
+int pcc_capture_voxelize(const float* xyzrgba, int64_t n_px, double voxel_size, float depth_clip,
+                         int32_t max_points, int16_t* points, double* colors, int64_t capacity,
+                         int32_t* n_out_dev, void* ws, int64_t ws_bytes, pcc_stream_t s);
+
 #ifdef __cplusplus
 }
 #endif
