@@ -11,15 +11,16 @@
 // index, one thread walks a voxel's run), and the two orders the reference leaves open are the oracle's:
 // voxels in ascending (ix,iy,iz) order, z ties to the earlier (x,y,z) row.
 //
-// HBM-bound integer/byte work of a few MB per frame: two 64-bit radix sorts over h*w entries, four scans,
-// a sequential-run accumulate.  No host synchronisation; the row count comes back through a device counter.
+// HBM-bound integer/byte work of a few MB per frame: two radix sorts over h*w entries (key widths follow
+// depth_clip / voxel_size: 31 and 31 bits at the demo's settings instead of 64 and 49), two scans, a
+// sequential-run accumulate.  No host synchronisation; the row count comes back through a device counter.
 #include "common.cuh"
 #include <cub/cub.cuh>
 
 namespace pcc {
 
 constexpr int kCapThreads = 256;
-constexpr int kIdxBits = 21;                       // voxel index bits per axis in the sort key
+constexpr int kIdxBits = 21;                       // most voxel index bits per axis in the sort key
 constexpr uint64_t kCapPad = ~0ull;
 constexpr int kZBins = 65536;
 
@@ -62,16 +63,25 @@ k_cap_min(const float4* __restrict__ px, int64_t n, float clip, CapState* __rest
   m0 = __reduce_min_sync(0xffffffffu, m0);
   m1 = __reduce_min_sync(0xffffffffu, m1);
   m2 = __reduce_min_sync(0xffffffffu, m2);
-  if ((threadIdx.x & 31) == 0 && m0 != 0xffffffffu) {
-    atomicMin(&st->min_ord[0], m0);
-    atomicMin(&st->min_ord[1], m1);
-    atomicMin(&st->min_ord[2], m2);
+  __shared__ uint32_t wmin[kCapThreads / 32][3];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (lane == 0) {
+    wmin[wid][0] = m0;
+    wmin[wid][1] = m1;
+    wmin[wid][2] = m2;
+  }
+  __syncthreads();
+  if (threadIdx.x < 3) {                       // one atomic per axis per block
+    uint32_t m = wmin[0][threadIdx.x];
+    for (int w = 1; w < kCapThreads / 32; ++w) m = min(m, wmin[w][threadIdx.x]);
+    if (m != 0xffffffffu) atomicMin(&st->min_ord[threadIdx.x], m);
   }
 }
 
-// voxel index of every valid pixel -> sort key (ix << 42 | iy << 21 | iz); invalid pixels sort last
+// voxel index of every valid pixel -> sort key (ix << 2 vb | iy << vb | iz), vb bits per axis (from depth_clip /
+// voxel_size, at most 21); invalid pixels carry the padding key, whose bit 3 vb is set: they sort last
 __global__ void __launch_bounds__(kCapThreads)
-k_cap_keys(const float4* __restrict__ px, int64_t n, float clip, double vs, CapState* __restrict__ st,
+k_cap_keys(const float4* __restrict__ px, int64_t n, float clip, double vs, int vb, CapState* __restrict__ st,
            uint64_t* __restrict__ keys, int32_t* __restrict__ pix) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -83,9 +93,9 @@ k_cap_keys(const float4* __restrict__ px, int64_t n, float clip, double vs, CapS
                  bz = (double)ord2f(st->min_ord[2]) - half;
     const double fx = floor(((double)p.x - bx) / vs), fy = floor(((double)p.y - by) / vs),
                  fz = floor(((double)p.z - bz) / vs);
-    const double lim = (double)(1 << kIdxBits);
+    const double lim = (double)(1 << vb);
     if (fx >= 0.0 && fy >= 0.0 && fz >= 0.0 && fx < lim && fy < lim && fz < lim) {
-      key = ((uint64_t)fx << (2 * kIdxBits)) | ((uint64_t)fy << kIdxBits) | (uint64_t)fz;
+      key = ((uint64_t)fx << (2 * vb)) | ((uint64_t)fy << vb) | (uint64_t)fz;
     } else {
       st->error = 1;
     }
@@ -104,10 +114,11 @@ k_cap_heads(const uint64_t* __restrict__ skeys, int64_t n, int32_t* __restrict__
 }
 
 // One thread per voxel walks its run in input order: sums of the float64 points and colours, then the
-// grid cell of the mean point.  cell key = (x + 32768) << 32 | (y + 32768) << 16 | (z + 32768).
+// grid cell of the mean point.  cell key = (x + bias) << 2 cb | (y + bias) << cb | (z + bias), bias = 2^(cb-1),
+// cb bits per axis (from depth_clip / voxel_size, at most 16).
 __global__ void __launch_bounds__(kCapThreads)
 k_cap_accumulate(const float4* __restrict__ px, const uint64_t* __restrict__ skeys, const int32_t* __restrict__ spix,
-                 const int32_t* __restrict__ flags, const int32_t* __restrict__ rank, int64_t n, double vs,
+                 const int32_t* __restrict__ flags, const int32_t* __restrict__ rank, int64_t n, double vs, int cb,
                  CapState* __restrict__ st, uint64_t* __restrict__ cell_keys, int32_t* __restrict__ vox_id,
                  double* __restrict__ vox_col) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -139,35 +150,58 @@ k_cap_accumulate(const float4* __restrict__ px, const uint64_t* __restrict__ ske
   const double d = (double)cnt;
   const double qx = rint((sx / d) / vs), qy = rint((sy / d) / vs), qz = rint((sz / d) / vs);
   const int32_t v = rank[i] - 1;
-  if (fabs(qx) > 32767.0 || fabs(qy) > 32767.0 || fabs(qz) > 32767.0) {
+  const int bias = 1 << (cb - 1);
+  const double lim = (double)(bias - 1);           // cb <= 16: within int16
+  if (!(fabs(qx) <= lim && fabs(qy) <= lim && fabs(qz) <= lim)) {
     st->error = 2;
     return;                                    // cell key stays padding
   }
-  cell_keys[v] = ((uint64_t)((int)qx + 32768) << 32) | ((uint64_t)((int)qy + 32768) << 16) | (uint64_t)((int)qz + 32768);
+  cell_keys[v] = ((uint64_t)((int)qx + bias) << (2 * cb)) | ((uint64_t)((int)qy + bias) << cb) | (uint64_t)((int)qz + bias);
   vox_col[3 * (int64_t)v + 0] = sr / d;
   vox_col[3 * (int64_t)v + 1] = sg / d;
   vox_col[3 * (int64_t)v + 2] = sb / d;
 }
 
-// heads of the sorted cell keys + histogram of their z (for the max_points threshold)
+// histogram of z over the heads of the sorted cell keys (for the max_points threshold)
 __global__ void __launch_bounds__(kCapThreads)
-k_cap_cell_heads(const uint64_t* __restrict__ skeys, int64_t n, int32_t* __restrict__ flags, int32_t* __restrict__ zhist) {
+k_cap_cell_hist(const uint64_t* __restrict__ skeys, int64_t n, int cb, int32_t* __restrict__ zhist) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint64_t k = skeys[i];
-  const bool head = k != kCapPad && (i == 0 || skeys[i - 1] != k);
-  flags[i] = head ? 1 : 0;
-  if (head) atomicAdd(&zhist[(int)(k & 0xffffu)], 1);
+  if (k != kCapPad && (i == 0 || skeys[i - 1] != k)) atomicAdd(&zhist[(int)(k & ((1u << cb) - 1u))], 1);
 }
 
-// Single block.  rank[n - 1] = number of cells.  Finds the z threshold of capturer.py:117-120: the largest
-// bin t with (rows of z >= t) >= max_points; rows above it are all kept, thr_take of the rows in it.
+// Single block.  Number of cells = sum of the histogram.  Finds the z threshold of capturer.py:117-120: the
+// largest bin t with (rows of z >= t) >= max_points; rows above it are all kept, thr_take of the rows in it.
+// Only the 2^cb bins the cell keys can reach are read (1024 at the demo's settings: one per thread).
 __global__ void __launch_bounds__(1024)
-k_cap_threshold(const int32_t* __restrict__ zhist, const int32_t* __restrict__ rank, int64_t n, int32_t max_points,
-                CapState* __restrict__ st) {
-  __shared__ int32_t part[1024];
-  const int t = threadIdx.x;
-  const int32_t n_cells = rank[n - 1];
+k_cap_threshold(const int32_t* __restrict__ zhist, int cb, int32_t max_points, CapState* __restrict__ st) {
+  __shared__ int32_t warp_tot[32];
+  const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
+  const int bins = 1 << cb;
+  const int per = bins > 1024 ? bins / 1024 : 1;
+  const int top = bins - 1 - t * per;            // this thread's bins: top, top - 1, ..., top - per + 1 (descending z)
+  int32_t local = 0;
+  if (top >= 0)
+    for (int b = 0; b < per; ++b) local += zhist[top - b];
+  int32_t incl = local;                          // inclusive scan over threads
+  for (int off = 1; off < 32; off <<= 1) {
+    const int32_t v = __shfl_up_sync(0xffffffffu, incl, off);
+    if (lane >= off) incl += v;
+  }
+  if (lane == 31) warp_tot[wid] = incl;
+  __syncthreads();
+  if (wid == 0) {
+    int32_t w = warp_tot[lane];
+    for (int off = 1; off < 32; off <<= 1) {
+      const int32_t v = __shfl_up_sync(0xffffffffu, w, off);
+      if (lane >= off) w += v;
+    }
+    warp_tot[lane] = w;
+  }
+  __syncthreads();
+  if (wid) incl += warp_tot[wid - 1];
+  const int32_t n_cells = warp_tot[31];
   if (t == 0) st->n_cells = n_cells;
   if (max_points <= 0 || n_cells <= max_points) {
     if (t == 0) {
@@ -176,22 +210,10 @@ k_cap_threshold(const int32_t* __restrict__ zhist, const int32_t* __restrict__ r
     }
     return;
   }
-  constexpr int kPer = kZBins / 1024;
-  const int top = kZBins - 1 - t * kPer;         // this thread's bins: top, top - 1, ..., top - kPer + 1
-  int32_t local = 0;
-  for (int b = 0; b < kPer; ++b) local += zhist[top - b];
-  part[t] = local;
-  __syncthreads();
-  for (int off = 1; off < 1024; off <<= 1) {     // inclusive scan over threads (descending z)
-    const int32_t add = t >= off ? part[t - off] : 0;
-    __syncthreads();
-    part[t] += add;
-    __syncthreads();
-  }
-  const int32_t incl = part[t], excl = incl - local;
+  const int32_t excl = incl - local;
   if (excl < max_points && incl >= max_points) {
     int32_t above = excl;
-    for (int b = 0; b < kPer; ++b) {
+    for (int b = 0; b < per; ++b) {
       const int32_t h = zhist[top - b];
       if (above + h >= max_points) {
         st->thr_z = top - b;
@@ -203,45 +225,44 @@ k_cap_threshold(const int32_t* __restrict__ zhist, const int32_t* __restrict__ r
   }
 }
 
-// eq[i] = head with z == threshold
+// mark[i] = (head with z above the threshold) | (head with z at the threshold) << 32: one 64-bit scan ranks both
 __global__ void __launch_bounds__(kCapThreads)
-k_cap_eq(const uint64_t* __restrict__ skeys, const int32_t* __restrict__ flags, int64_t n, const CapState* __restrict__ st,
-         int32_t* __restrict__ eq) {
+k_cap_mark(const uint64_t* __restrict__ skeys, int64_t n, int cb, const CapState* __restrict__ st, uint64_t* __restrict__ mark) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  eq[i] = (flags[i] && (int)(skeys[i] & 0xffffu) == st->thr_z) ? 1 : 0;
-}
-
-// keep[i] (written over eq's scan): head with z above the threshold, or one of the first thr_take at it
-__global__ void __launch_bounds__(kCapThreads)
-k_cap_keep(const uint64_t* __restrict__ skeys, const int32_t* __restrict__ flags, int64_t n, const CapState* __restrict__ st,
-           int32_t* __restrict__ eq_rank_keep) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  int keep = 0;
-  if (flags[i]) {
-    const int z = (int)(skeys[i] & 0xffffu);
-    keep = z > st->thr_z || (z == st->thr_z && eq_rank_keep[i] <= st->thr_take);
-  }
-  eq_rank_keep[i] = keep;
-}
-
-__global__ void __launch_bounds__(kCapThreads)
-k_cap_emit(const uint64_t* __restrict__ skeys, const int32_t* __restrict__ svox, const int32_t* __restrict__ flags,
-           const int32_t* __restrict__ out_rank, const double* __restrict__ vox_col, int64_t n, int64_t cap,
-           const CapState* __restrict__ st, int16_t* __restrict__ points, double* __restrict__ colors,
-           int32_t* __restrict__ n_out) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const int32_t r = out_rank[i];
-  if (i == n - 1) *n_out = st->error ? -st->error : r;
-  const int32_t prev = i ? out_rank[i - 1] : 0;
-  if (!flags[i] || r == prev || r > cap) return;       // not a kept head (or beyond the caller's capacity)
   const uint64_t k = skeys[i];
-  const int64_t o = 3 * (int64_t)(r - 1);
-  points[o + 0] = (int16_t)((int)((k >> 32) & 0xffffu) - 32768);
-  points[o + 1] = (int16_t)((int)((k >> 16) & 0xffffu) - 32768);
-  points[o + 2] = (int16_t)((int)(k & 0xffffu) - 32768);
+  uint64_t m = 0;
+  if (k != kCapPad && (i == 0 || skeys[i - 1] != k)) {
+    const int z = (int)(k & ((1u << cb) - 1u));
+    m = z > st->thr_z ? 1ull : (z == st->thr_z ? (1ull << 32) : 0ull);
+  }
+  mark[i] = m;
+}
+
+// Kept rows: every head above the threshold and the first thr_take heads at it, in (x,y,z) order.  Row i lands
+// behind the rows above the threshold that precede it plus the (at most thr_take) tied rows that precede it.
+__global__ void __launch_bounds__(kCapThreads)
+k_cap_emit(const uint64_t* __restrict__ skeys, const int32_t* __restrict__ svox, const uint64_t* __restrict__ mark_scan,
+           const double* __restrict__ vox_col, int64_t n, int cb, int64_t cap, const CapState* __restrict__ st,
+           int16_t* __restrict__ points, double* __restrict__ colors, int32_t* __restrict__ n_out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint64_t incl = mark_scan[i], prev = i ? mark_scan[i - 1] : 0ull;
+  const int64_t take = st->thr_take;
+  const int64_t above_incl = (int64_t)(incl & 0xffffffffu), eq_incl = (int64_t)(incl >> 32);
+  const int64_t above_prev = (int64_t)(prev & 0xffffffffu), eq_prev = (int64_t)(prev >> 32);
+  if (i == n - 1) *n_out = st->error ? -st->error : (int32_t)(above_incl + (eq_incl < take ? eq_incl : take));
+  const bool is_above = above_incl != above_prev, is_eq = eq_incl != eq_prev;
+  if (!(is_above || (is_eq && eq_incl <= take))) return;
+  const int64_t r = above_prev + (eq_prev < take ? eq_prev : take);
+  if (r >= cap) return;                                 // beyond the caller's capacity (the count still says so)
+  const uint64_t k = skeys[i];
+  const int bias = 1 << (cb - 1);
+  const uint32_t fm = (1u << cb) - 1u;
+  const int64_t o = 3 * r;
+  points[o + 0] = (int16_t)((int)((k >> (2 * cb)) & fm) - bias);
+  points[o + 1] = (int16_t)((int)((k >> cb) & fm) - bias);
+  points[o + 2] = (int16_t)((int)(k & fm) - bias);
   const int64_t v = 3 * (int64_t)svox[i];
   colors[o + 0] = vox_col[v + 0];
   colors[o + 1] = vox_col[v + 1];
@@ -255,8 +276,18 @@ static size_t cap_sort_bytes(int64_t n) {
   return b;
 }
 static size_t cap_scan_bytes(int64_t n) {
-  size_t b = 0;
-  cub::DeviceScan::InclusiveSum(nullptr, b, (const int32_t*)nullptr, (int32_t*)nullptr, (int)n);
+  size_t b32 = 0, b64 = 0;
+  cub::DeviceScan::InclusiveSum(nullptr, b32, (const int32_t*)nullptr, (int32_t*)nullptr, (int)n);
+  cub::DeviceScan::InclusiveSum(nullptr, b64, (const uint64_t*)nullptr, (uint64_t*)nullptr, (int)n);
+  return b32 > b64 ? b32 : b64;
+}
+
+// bits that hold every value of [0, extent): 1 .. cap
+static int cap_bits(double extent, int cap) {
+  if (!(extent > 2.0)) return 1;
+  if (!(extent < 4.0e9)) return cap;
+  int b = 1;
+  while (b < cap && (double)(1ull << b) < extent) ++b;
   return b;
 }
 
@@ -283,7 +314,7 @@ int64_t pcc_capture_voxelize_workspace_bytes(int64_t n_px) {
   b += align_up(kZBins * 4, 256);                    // z histogram
   b += 2 * align_up(n * 8, 256);                     // keys, sorted keys (reused for the cell keys)
   b += 2 * align_up(n * 4, 256);                     // pixel / voxel ids, sorted
-  b += 3 * align_up(n * 4, 256);                     // flags, rank, keep rank
+  b += 2 * align_up(n * 4, 256);                     // flags, rank
   b += align_up(n * 24, 256);                        // voxel colours
   b += align_up((int64_t)cap_sort_bytes(n), 256);
   b += align_up((int64_t)cap_scan_bytes(n), 256);
@@ -312,52 +343,52 @@ int pcc_capture_voxelize(const float* xyzrgba, int64_t n_px, double voxel_size, 
   int32_t* sids = (int32_t*)w.take(n * 4);
   int32_t* flags = (int32_t*)w.take(n * 4);
   int32_t* rank = (int32_t*)w.take(n * 4);
-  int32_t* keep = (int32_t*)w.take(n * 4);
   double* vox_col = (double*)w.take(n * 24);
   size_t sort_b = cap_sort_bytes(n), scan_b = cap_scan_bytes(n);
   void* sort_ws = w.take((int64_t)sort_b);
   void* scan_ws = w.take((int64_t)scan_b);
-  if (!st || !zhist || !keys || !skeys || !ids || !sids || !flags || !rank || !keep || !vox_col || !sort_ws || !scan_ws) {
+  if (!st || !zhist || !keys || !skeys || !ids || !sids || !flags || !rank || !vox_col || !sort_ws || !scan_ws) {
     set_error("pcc_capture_voxelize: workspace too small (%lld)", (long long)ws_bytes);
     return PCC_E_WORKSPACE;
   }
   const float4* px = (const float4*)xyzrgba;
   const int blocks = (int)((n + kCapThreads - 1) / kCapThreads);
+  // Key widths from the settings: a kept point lies within depth_clip of the origin, so the voxel indices span at
+  // most 2 clip / voxel + 2 and the grid cells lie within +-(clip / voxel + 1).  The kernels still check (error 1 / 2).
+  const double reach = (double)depth_clip / voxel_size;
+  const int vb = cap_bits(2.0 * reach + 4.0, kIdxBits);
+  const int cb0 = cap_bits(2.0 * (reach + 2.0), 16);
+  const int cb = cb0 < 2 ? 2 : cb0;
   // state: minima = all ones (ordered-uint +inf side), the rest and the histogram zero
   PCC_CUDA(cudaMemsetAsync(st, 0, 256 + align_up(kZBins * 4, 256), stm));
   PCC_CUDA(cudaMemsetAsync(st, 0xff, 12, stm));
   k_cap_min<<<blocks, kCapThreads, 0, stm>>>(px, n, depth_clip, st);
   PCC_LAUNCHED();
-  k_cap_keys<<<blocks, kCapThreads, 0, stm>>>(px, n, depth_clip, voxel_size, st, keys, ids);
+  k_cap_keys<<<blocks, kCapThreads, 0, stm>>>(px, n, depth_clip, voxel_size, vb, st, keys, ids);
   PCC_LAUNCHED();
-  // stable: a voxel's pixels stay in input order
-  PCC_CUDA(cub::DeviceRadixSort::SortPairs(sort_ws, sort_b, keys, skeys, ids, sids, (int)n, 0, 64, stm));
+  // stable: a voxel's pixels stay in input order.  3 vb index bits + the padding bit.
+  PCC_CUDA(cub::DeviceRadixSort::SortPairs(sort_ws, sort_b, keys, skeys, ids, sids, (int)n, 0, 3 * vb + 1, stm));
   g_launches.fetch_add(1);
   k_cap_heads<<<blocks, kCapThreads, 0, stm>>>(skeys, n, flags);
   PCC_LAUNCHED();
   PCC_CUDA(cub::DeviceScan::InclusiveSum(scan_ws, scan_b, flags, rank, (int)n, stm));
   g_launches.fetch_add(1);
   PCC_CUDA(cudaMemsetAsync(keys, 0xff, n * 8, stm));          // cell keys: padding beyond the voxel count
-  k_cap_accumulate<<<blocks, kCapThreads, 0, stm>>>(px, skeys, sids, flags, rank, n, voxel_size, st, keys, ids, vox_col);
+  k_cap_accumulate<<<blocks, kCapThreads, 0, stm>>>(px, skeys, sids, flags, rank, n, voxel_size, cb, st, keys, ids, vox_col);
   PCC_LAUNCHED();
-  // 48 key bits + the padding bit; stable: among voxels of one cell the lowest (ix,iy,iz) comes first
-  PCC_CUDA(cub::DeviceRadixSort::SortPairs(sort_ws, sort_b, keys, skeys, ids, sids, (int)n, 0, 49, stm));
+  // 3 cb key bits + the padding bit; stable: among voxels of one cell the lowest (ix,iy,iz) comes first
+  PCC_CUDA(cub::DeviceRadixSort::SortPairs(sort_ws, sort_b, keys, skeys, ids, sids, (int)n, 0, 3 * cb + 1, stm));
   g_launches.fetch_add(1);
-  k_cap_cell_heads<<<blocks, kCapThreads, 0, stm>>>(skeys, n, flags, zhist);
+  k_cap_cell_hist<<<blocks, kCapThreads, 0, stm>>>(skeys, n, cb, zhist);
   PCC_LAUNCHED();
-  PCC_CUDA(cub::DeviceScan::InclusiveSum(scan_ws, scan_b, flags, rank, (int)n, stm));
+  k_cap_threshold<<<1, 1024, 0, stm>>>(zhist, cb, max_points, st);
+  PCC_LAUNCHED();
+  uint64_t* mark = keys;                                      // the unsorted cell keys are no longer needed
+  k_cap_mark<<<blocks, kCapThreads, 0, stm>>>(skeys, n, cb, st, mark);
+  PCC_LAUNCHED();
+  PCC_CUDA(cub::DeviceScan::InclusiveSum(scan_ws, scan_b, mark, mark, (int)n, stm));
   g_launches.fetch_add(1);
-  k_cap_threshold<<<1, 1024, 0, stm>>>(zhist, rank, n, max_points, st);
-  PCC_LAUNCHED();
-  k_cap_eq<<<blocks, kCapThreads, 0, stm>>>(skeys, flags, n, st, keep);
-  PCC_LAUNCHED();
-  PCC_CUDA(cub::DeviceScan::InclusiveSum(scan_ws, scan_b, keep, keep, (int)n, stm));
-  g_launches.fetch_add(1);
-  k_cap_keep<<<blocks, kCapThreads, 0, stm>>>(skeys, flags, n, st, keep);
-  PCC_LAUNCHED();
-  PCC_CUDA(cub::DeviceScan::InclusiveSum(scan_ws, scan_b, keep, rank, (int)n, stm));
-  g_launches.fetch_add(1);
-  k_cap_emit<<<blocks, kCapThreads, 0, stm>>>(skeys, sids, flags, rank, vox_col, n, capacity, st, points, colors, n_out_dev);
+  k_cap_emit<<<blocks, kCapThreads, 0, stm>>>(skeys, sids, mark, vox_col, n, cb, capacity, st, points, colors, n_out_dev);
   PCC_LAUNCHED();
   return PCC_OK;
 }

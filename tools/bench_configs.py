@@ -4,6 +4,10 @@
   cfg-3  zed-300k   ZED-shaped frames (negative coordinates) arriving at 30 fps, one frame per call through
                     compress() -> bytes -> decompress() with HOST buffers; per-frame latency p50/p95/p99 and the
                     worst lag behind the arrival clock
+  cfg-3c capture    the demo's own operating point (shared/config.yaml: 640x480 ZED measure, depth_clip 1.4 m, 5 mm
+                    voxels, max_points 30000) from the camera's XYZRGBA measure in host memory to the client's
+                    playout buffer in host memory: FrameVoxelizer.capture_staged -> compress(staged=) ->
+                    decompress(to_host=False) -> playout_buffers, frames arriving at the given rate
   cfg-5  ladder     one cfg-2 frame, Gaussian stage batched over Q settings (Q = 1, 3 reference ladder, 25 grid):
                     encode time vs Q, bits per point per level, decode of the best level
 
@@ -96,6 +100,58 @@ def cfg3(model, dev, nframes, fps):
             "buffers": "host numpy in, host numpy out; one frame per call"}
 
 
+def cfg3c(model, dev, nframes, fps):
+    sys.path.insert(0, ROOT)
+    from b200pcc import CompressionPipeline, DecompressionPipeline
+    from b200pcc.capture import FrameVoxelizer
+    from oracle.capture_ref import synth_measure          # input generator only (the checker is not on the timed path)
+    measures = [synth_measure(480, 640, seed=100 + i) for i in range(10)]
+    vox = FrameVoxelizer({"voxel_size": 0.005, "depth_clip": 1.4, "max_points": 30000}, device=dev)
+    enc = CompressionPipeline([[1.0, 1.0]], device=dev, model=model)
+    dec = DecompressionPipeline(device=dev, model=model)
+
+    def once(m):
+        t0 = time.perf_counter()
+        frame, staged = vox.capture_staged(m)
+        t1 = time.perf_counter()
+        comp, _ = enc.compress({"frames": [frame]}, staged=staged)
+        t2 = time.perf_counter()
+        x_hat, _ = dec.decompress(comp[1], to_host=False)
+        bufs = dec.playout_buffers(x_hat, num_frames=1)
+        t3 = time.perf_counter()
+        return len(frame["points"]), len(comp[1]), len(bufs[0]), (t1 - t0) * 1e3, (t2 - t1) * 1e3, (t3 - t2) * 1e3
+
+    for i in range(6):
+        once(measures[i % 10])
+    period = 1.0 / fps
+    lat, lag, cap_ms, enc_ms, dec_ms, sizes, pts = [], [], [], [], [], [], []
+    start = time.perf_counter()
+    for i in range(nframes):
+        arrival = start + i * period
+        now = time.perf_counter()
+        if now < arrival:
+            time.sleep(arrival - now)
+        t0 = time.perf_counter()
+        n, nbytes, nplay, tc, te, td = once(measures[i % 10])
+        t1 = time.perf_counter()
+        assert nplay == 15 * n
+        lat.append((t1 - arrival) * 1e3)
+        lag.append((t0 - arrival) * 1e3)
+        cap_ms.append(tc)
+        enc_ms.append(te)
+        dec_ms.append(td)
+        sizes.append(nbytes)
+        pts.append(n)
+    n = float(np.mean(pts))
+    return {"config": "cfg-3c capture-to-playout (shared/config.yaml operating point)", "measure": "640x480 XYZRGBA float32, host",
+            "points_per_frame": n, "frames": nframes, "arrival_fps": fps,
+            "latency_ms": {"p50": pct(lat, 50), "p95": pct(lat, 95), "p99": pct(lat, 99), "max": max(lat)},
+            "capture_ms_p50": pct(cap_ms, 50), "encode_ms_p50": pct(enc_ms, 50), "decode_playout_ms_p50": pct(dec_ms, 50),
+            "start_lag_ms_max": max(lag), "keeps_up": bool(max(lag) < period * 1e3), "bpp_mean": 8.0 * float(np.mean(sizes)) / n,
+            "h2d_bytes_per_frame": 480 * 640 * 16, "d2h_bytes_per_frame": 15 * n + float(np.mean(sizes)),
+            "buffers": "host measure in, host playout buffer out; the voxelised frame never leaves HBM"}
+
+
 def cfg5(model, dev, reps):
     from b200pcc import CompressionPipeline, DecompressionPipeline, synth
     frame = synth.frame_8ivfb(seed=1)
@@ -140,6 +196,7 @@ def main():
     from b200pcc.pipeline import load_model
     model = load_model(dev)
     todo = {"cfg1": lambda: cfg1(model, dev, args.reps), "cfg3": lambda: cfg3(model, dev, args.frames, args.fps),
+            "cfg3c": lambda: cfg3c(model, dev, args.frames, args.fps),
             "cfg5": lambda: cfg5(model, dev, args.reps)}
     for k, fn in todo.items():
         if args.only and k not in args.only.split(","):
