@@ -50,6 +50,8 @@ __device__ __forceinline__ bool cap_valid(const float4 p, float clip) {
 
 __global__ void __launch_bounds__(kCapThreads)
 k_cap_min(const float4* __restrict__ px, int64_t n, float clip, CapState* __restrict__ st) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   uint32_t m0 = 0xffffffffu, m1 = 0xffffffffu, m2 = 0xffffffffu;
   if (i < n) {
@@ -83,6 +85,8 @@ k_cap_min(const float4* __restrict__ px, int64_t n, float clip, CapState* __rest
 __global__ void __launch_bounds__(kCapThreads)
 k_cap_keys(const float4* __restrict__ px, int64_t n, float clip, double vs, int vb, CapState* __restrict__ st,
            uint64_t* __restrict__ keys, int32_t* __restrict__ pix) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const float4 p = __ldg(px + i);
@@ -107,6 +111,8 @@ k_cap_keys(const float4* __restrict__ px, int64_t n, float clip, double vs, int 
 // flags[i] = 1 where a run of equal keys starts (padding excluded)
 __global__ void __launch_bounds__(kCapThreads)
 k_cap_heads(const uint64_t* __restrict__ skeys, int64_t n, int32_t* __restrict__ flags) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint64_t k = skeys[i];
@@ -121,6 +127,8 @@ k_cap_accumulate(const float4* __restrict__ px, const uint64_t* __restrict__ ske
                  const int32_t* __restrict__ flags, const int32_t* __restrict__ rank, int64_t n, double vs, int cb,
                  CapState* __restrict__ st, uint64_t* __restrict__ cell_keys, int32_t* __restrict__ vox_id,
                  double* __restrict__ vox_col) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   vox_id[i] = (int32_t)i;
@@ -165,6 +173,8 @@ k_cap_accumulate(const float4* __restrict__ px, const uint64_t* __restrict__ ske
 // histogram of z over the heads of the sorted cell keys (for the max_points threshold)
 __global__ void __launch_bounds__(kCapThreads)
 k_cap_cell_hist(const uint64_t* __restrict__ skeys, int64_t n, int cb, int32_t* __restrict__ zhist) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint64_t k = skeys[i];
@@ -176,6 +186,8 @@ k_cap_cell_hist(const uint64_t* __restrict__ skeys, int64_t n, int cb, int32_t* 
 // Only the 2^cb bins the cell keys can reach are read (1024 at the demo's settings: one per thread).
 __global__ void __launch_bounds__(1024)
 k_cap_threshold(const int32_t* __restrict__ zhist, int cb, int32_t max_points, CapState* __restrict__ st) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ int32_t warp_tot[32];
   const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
   const int bins = 1 << cb;
@@ -228,6 +240,8 @@ k_cap_threshold(const int32_t* __restrict__ zhist, int cb, int32_t max_points, C
 // mark[i] = (head with z above the threshold) | (head with z at the threshold) << 32: one 64-bit scan ranks both
 __global__ void __launch_bounds__(kCapThreads)
 k_cap_mark(const uint64_t* __restrict__ skeys, int64_t n, int cb, const CapState* __restrict__ st, uint64_t* __restrict__ mark) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint64_t k = skeys[i];
@@ -245,6 +259,8 @@ __global__ void __launch_bounds__(kCapThreads)
 k_cap_emit(const uint64_t* __restrict__ skeys, const int32_t* __restrict__ svox, const uint64_t* __restrict__ mark_scan,
            const double* __restrict__ vox_col, int64_t n, int cb, int64_t cap, const CapState* __restrict__ st,
            int16_t* __restrict__ points, double* __restrict__ colors, int32_t* __restrict__ n_out) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint64_t incl = mark_scan[i], prev = i ? mark_scan[i - 1] : 0ull;
@@ -362,33 +378,33 @@ int pcc_capture_voxelize(const float* xyzrgba, int64_t n_px, double voxel_size, 
   // state: minima = all ones (ordered-uint +inf side), the rest and the histogram zero
   PCC_CUDA(cudaMemsetAsync(st, 0, 256 + align_up(kZBins * 4, 256), stm));
   PCC_CUDA(cudaMemsetAsync(st, 0xff, 12, stm));
-  k_cap_min<<<blocks, kCapThreads, 0, stm>>>(px, n, depth_clip, st);
+  launch_pdl(k_cap_min, dim3(blocks), dim3(kCapThreads), 0, stm, px, n, depth_clip, st);
   PCC_LAUNCHED();
-  k_cap_keys<<<blocks, kCapThreads, 0, stm>>>(px, n, depth_clip, voxel_size, vb, st, keys, ids);
+  launch_pdl(k_cap_keys, dim3(blocks), dim3(kCapThreads), 0, stm, px, n, depth_clip, voxel_size, vb, st, keys, ids);
   PCC_LAUNCHED();
   // stable: a voxel's pixels stay in input order.  3 vb index bits + the padding bit.
   PCC_CUDA(cub::DeviceRadixSort::SortPairs(sort_ws, sort_b, keys, skeys, ids, sids, (int)n, 0, 3 * vb + 1, stm));
   g_launches.fetch_add(1);
-  k_cap_heads<<<blocks, kCapThreads, 0, stm>>>(skeys, n, flags);
+  launch_pdl(k_cap_heads, dim3(blocks), dim3(kCapThreads), 0, stm, skeys, n, flags);
   PCC_LAUNCHED();
   PCC_CUDA(cub::DeviceScan::InclusiveSum(scan_ws, scan_b, flags, rank, (int)n, stm));
   g_launches.fetch_add(1);
   PCC_CUDA(cudaMemsetAsync(keys, 0xff, n * 8, stm));          // cell keys: padding beyond the voxel count
-  k_cap_accumulate<<<blocks, kCapThreads, 0, stm>>>(px, skeys, sids, flags, rank, n, voxel_size, cb, st, keys, ids, vox_col);
+  launch_pdl(k_cap_accumulate, dim3(blocks), dim3(kCapThreads), 0, stm, px, skeys, sids, flags, rank, n, voxel_size, cb, st, keys, ids, vox_col);
   PCC_LAUNCHED();
   // 3 cb key bits + the padding bit; stable: among voxels of one cell the lowest (ix,iy,iz) comes first
   PCC_CUDA(cub::DeviceRadixSort::SortPairs(sort_ws, sort_b, keys, skeys, ids, sids, (int)n, 0, 3 * cb + 1, stm));
   g_launches.fetch_add(1);
-  k_cap_cell_hist<<<blocks, kCapThreads, 0, stm>>>(skeys, n, cb, zhist);
+  launch_pdl(k_cap_cell_hist, dim3(blocks), dim3(kCapThreads), 0, stm, skeys, n, cb, zhist);
   PCC_LAUNCHED();
-  k_cap_threshold<<<1, 1024, 0, stm>>>(zhist, cb, max_points, st);
+  launch_pdl(k_cap_threshold, dim3(1), dim3(1024), 0, stm, zhist, cb, max_points, st);
   PCC_LAUNCHED();
   uint64_t* mark = keys;                                      // the unsorted cell keys are no longer needed
-  k_cap_mark<<<blocks, kCapThreads, 0, stm>>>(skeys, n, cb, st, mark);
+  launch_pdl(k_cap_mark, dim3(blocks), dim3(kCapThreads), 0, stm, skeys, n, cb, st, mark);
   PCC_LAUNCHED();
   PCC_CUDA(cub::DeviceScan::InclusiveSum(scan_ws, scan_b, mark, mark, (int)n, stm));
   g_launches.fetch_add(1);
-  k_cap_emit<<<blocks, kCapThreads, 0, stm>>>(skeys, sids, mark, vox_col, n, cb, capacity, st, points, colors, n_out_dev);
+  launch_pdl(k_cap_emit, dim3(blocks), dim3(kCapThreads), 0, stm, skeys, sids, mark, vox_col, n, cb, capacity, st, points, colors, n_out_dev);
   PCC_LAUNCHED();
   return PCC_OK;
 }

@@ -38,6 +38,30 @@ extern std::atomic<int64_t> g_launches;
     PCC_CUDA(cudaGetLastError());       \
   } while (0)
 
+// Programmatic dependent launch: a kernel launched through launch_pdl may become resident while its
+// predecessor in the stream still runs (as soon as every CTA of the predecessor has executed pdl_trigger() or
+// exited and resources are free); it must execute pdl_wait() before it touches anything a predecessor wrote --
+// the wait returns once the predecessor grid has completed and its writes are visible.  Kernels launched the
+// ordinary way are unaffected by a predecessor's trigger.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                     Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 static inline cudaStream_t as_stream(pcc_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 
 static inline int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }

@@ -21,12 +21,16 @@ static inline unsigned blocks_for(int64_t n, int per_block = kThreads) {
 }
 
 __global__ void k_keys_from_i32(const int4* __restrict__ c, int64_t n, uint64_t* __restrict__ keys) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   int4 v = c[i];
   keys[i] = pack_key(v.x, v.y, v.z, v.w);
 }
 __global__ void k_keys_from_f32(const float4* __restrict__ c, int64_t n, uint64_t* __restrict__ keys) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   float4 v = c[i];
@@ -34,6 +38,8 @@ __global__ void k_keys_from_f32(const float4* __restrict__ c, int64_t n, uint64_
 }
 __global__ void k_ingest(const int16_t* __restrict__ p, const double* __restrict__ col, int64_t n,
                          int batch, uint64_t* __restrict__ keys, float4* __restrict__ feats) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   int x = p[3 * i], y = p[3 * i + 1], z = p[3 * i + 2];
@@ -41,6 +47,8 @@ __global__ void k_ingest(const int16_t* __restrict__ p, const double* __restrict
   feats[i] = make_float4(1.0f, (float)col[3 * i], (float)col[3 * i + 1], (float)col[3 * i + 2]);
 }
 __global__ void k_ingest_points(const int16_t* __restrict__ p, int64_t n, int batch, uint64_t* __restrict__ keys) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   keys[i] = pack_key(batch, p[3 * i], p[3 * i + 1], p[3 * i + 2]);
@@ -49,6 +57,8 @@ __global__ void k_ingest_points(const int16_t* __restrict__ p, int64_t n, int ba
 // k_rows_f32_to_bf16: double -> float -> bf16 RN); chunks16 = 16-byte chunks per output row
 __global__ void k_ingest_features(const double* __restrict__ col, const int32_t* __restrict__ src_row, int64_t m,
                                   uint4* __restrict__ out, int chunks16) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= m) return;
   const int64_t r = src_row ? (int64_t)src_row[i] : i;
@@ -64,6 +74,8 @@ __global__ void k_ingest_features(const double* __restrict__ col, const int32_t*
 }
 __global__ void k_ingest_features_bf16(const uint16_t* __restrict__ col, const int32_t* __restrict__ src_row, int64_t m,
                                        uint4* __restrict__ out, int chunks16) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= m) return;
   const int64_t r = src_row ? (int64_t)src_row[i] : i;
@@ -77,6 +89,8 @@ __global__ void k_ingest_features_bf16(const uint16_t* __restrict__ col, const i
   for (int k = 1; k < chunks16; ++k) out[i * chunks16 + k] = make_uint4(0u, 0u, 0u, 0u);
 }
 __global__ void k_coords_from_keys(const uint64_t* __restrict__ keys, int64_t n, int4* __restrict__ c) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   int b, x, y, z;
@@ -88,6 +102,8 @@ __global__ void k_coords_from_keys(const uint64_t* __restrict__ keys, int64_t n,
 // (pack_batches, receiver/decoder/codec_parallel.py:474-502)
 __global__ void k_unpack_output(const uint64_t* __restrict__ keys, const float* __restrict__ feats, int64_t n,
                                 int32_t* __restrict__ pts, float* __restrict__ col) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   if (pts) {
@@ -113,6 +129,8 @@ __global__ void k_unpack_output(const uint64_t* __restrict__ keys, const float* 
 // step in fp32 like numpy does it
 __global__ void k_pack_visualizer(const uint64_t* __restrict__ keys, const float* __restrict__ feats, int64_t n,
                                   float offset, float* __restrict__ pts, uint8_t* __restrict__ col) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   int b, x, y, z;
@@ -131,6 +149,8 @@ __global__ void k_pack_visualizer(const uint64_t* __restrict__ keys, const float
 }
 
 __global__ void k_iota(int32_t* v, int64_t n) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i < n) v[i] = (int32_t)i;
 }
@@ -138,6 +158,8 @@ __global__ void k_iota(int32_t* v, int64_t n) {
 // flags[i] = 1 where sorted key i starts a new run (after masking low bits)
 __global__ void k_run_flags(const uint64_t* __restrict__ keys, int64_t n, uint64_t mask,
                             int32_t* __restrict__ flags) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   uint64_t k = keys[i] & mask;
@@ -149,6 +171,8 @@ __global__ void k_scatter_runs(const uint64_t* __restrict__ keys, const int32_t*
                                const int32_t* __restrict__ incl, int64_t n, uint64_t mask,
                                uint64_t* __restrict__ keys_out, int32_t* __restrict__ src_out,
                                int32_t* __restrict__ run_of, int32_t* __restrict__ n_out) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   int32_t r = incl[i] - 1;
@@ -165,6 +189,8 @@ __global__ void k_scatter_runs(const uint64_t* __restrict__ keys, const int32_t*
 // n_dev (may be null: then n = nmax) is the true element count; the launch covers nmax >= n.
 __global__ void k_run_flags_dc(const uint64_t* __restrict__ keys, const int32_t* __restrict__ n_dev, int64_t nmax,
                                uint64_t mask, int32_t* __restrict__ flags) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= nmax) return;
   const int64_t n = n_dev ? (int64_t)*n_dev : nmax;
@@ -179,6 +205,8 @@ __global__ void k_scatter_runs_dc(const uint64_t* __restrict__ keys, const int32
                                   const int32_t* __restrict__ n_dev, int64_t nmax, uint64_t mask,
                                   uint64_t* __restrict__ keys_out, int32_t* __restrict__ run_of,
                                   int32_t* __restrict__ n_out) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   const int64_t n = n_dev ? (int64_t)*n_dev : nmax;
   if (i == 0 && n == 0) *n_out = 0;
@@ -191,6 +219,8 @@ __global__ void k_scatter_runs_dc(const uint64_t* __restrict__ keys, const int32
 }
 __global__ void k_frame_offsets_dc(const uint64_t* __restrict__ keys, const int32_t* __restrict__ n_dev,
                                    int64_t nmax, int nf, int32_t* __restrict__ off) {
+  pdl_trigger();
+  pdl_wait();
   int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b > nf) return;
   const int64_t n = n_dev ? (int64_t)*n_dev : nmax;
@@ -205,6 +235,8 @@ __global__ void k_frame_offsets_dc(const uint64_t* __restrict__ keys, const int3
 
 __global__ void k_children(const uint64_t* __restrict__ keys, int64_t n, int shift,
                            uint64_t* __restrict__ out) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;  // over 8n
   if (i >= 8 * n) return;
   out[i] = keys[i >> 3] | ((uint64_t)(i & 7) << shift);
@@ -212,6 +244,8 @@ __global__ void k_children(const uint64_t* __restrict__ keys, int64_t n, int shi
 
 __global__ void k_frame_offsets(const uint64_t* __restrict__ keys, int64_t n, int nf,
                                 int32_t* __restrict__ off) {
+  pdl_trigger();
+  pdl_wait();
   int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b > nf) return;
   uint64_t target = (uint64_t)b << 48;
@@ -225,6 +259,8 @@ __global__ void k_frame_offsets(const uint64_t* __restrict__ keys, int64_t n, in
 
 __global__ void k_lex_keys(const uint64_t* __restrict__ keys, int64_t n, uint64_t* __restrict__ lex,
                            int32_t* __restrict__ row) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   int b, x, y, z;
@@ -238,6 +274,8 @@ __global__ void k_lex_keys(const uint64_t* __restrict__ keys, int64_t n, uint64_
 __global__ void k_rows_f32_to_bf16(const float* __restrict__ src, int c_src,
                                    const int32_t* __restrict__ src_row, int64_t n_out,
                                    __nv_bfloat16* __restrict__ dst, int c_dst) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n_out * c_dst) return;
   int64_t r = i / c_dst;
@@ -248,6 +286,8 @@ __global__ void k_rows_f32_to_bf16(const float* __restrict__ src, int c_src,
 }
 __global__ void k_rows_bf16_to_f32(const __nv_bfloat16* __restrict__ src, int c_src, int64_t n,
                                    float* __restrict__ dst, int c_dst) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n * c_dst) return;
   int64_t r = i / c_dst;
@@ -258,6 +298,8 @@ __global__ void k_rows_bf16_to_f32(const __nv_bfloat16* __restrict__ src, int c_
 __global__ void k_gather_rows16(const uint4* __restrict__ src, int chunks,
                                 const int32_t* __restrict__ src_row, int64_t n_out,
                                 uint4* __restrict__ dst) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n_out * chunks) return;
   int64_t r = i / chunks;
@@ -268,6 +310,8 @@ __global__ void k_gather_rows16(const uint4* __restrict__ src, int chunks,
 __global__ void k_gather_rows_f32(const float* __restrict__ src, int c,
                                   const int32_t* __restrict__ src_row, int64_t n_out,
                                   float* __restrict__ dst) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n_out * c) return;
   int64_t r = i / c;
@@ -277,6 +321,8 @@ __global__ void k_gather_rows_f32(const float* __restrict__ src, int c,
 }
 __global__ void k_gather_keys(const uint64_t* __restrict__ src, const int32_t* __restrict__ src_row,
                               int64_t n_out, uint64_t* __restrict__ dst) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i < n_out) dst[i] = src[src_row[i]];
 }
@@ -309,7 +355,7 @@ int pcc_keys_from_coords_i32(const int32_t* coords, int64_t n, uint64_t* keys, p
   PCC_CHECK_ARG(n >= 0);
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(coords && keys);
-  k_keys_from_i32<<<blocks_for(n), kThreads, 0, as_stream(s)>>>((const int4*)coords, n, keys);
+  launch_pdl(k_keys_from_i32, dim3(blocks_for(n)), dim3(kThreads), 0, as_stream(s), (const int4*)coords, n, keys);
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -317,7 +363,7 @@ int pcc_keys_from_coords_f32(const float* coords, int64_t n, uint64_t* keys, pcc
   PCC_CHECK_ARG(n >= 0);
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(coords && keys);
-  k_keys_from_f32<<<blocks_for(n), kThreads, 0, as_stream(s)>>>((const float4*)coords, n, keys);
+  launch_pdl(k_keys_from_f32, dim3(blocks_for(n)), dim3(kThreads), 0, as_stream(s), (const float4*)coords, n, keys);
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -326,7 +372,7 @@ int pcc_ingest_frame(const int16_t* points, const double* colors, int64_t n, int
   PCC_CHECK_ARG(n >= 0 && batch >= 0 && batch < 65535);
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(points && colors && keys && feats4);
-  k_ingest<<<blocks_for(n), kThreads, 0, as_stream(s)>>>(points, colors, n, batch, keys,
+  launch_pdl(k_ingest, dim3(blocks_for(n)), dim3(kThreads), 0, as_stream(s), points, colors, n, batch, keys,
                                                          (float4*)feats4);
   PCC_LAUNCHED();
   return PCC_OK;
@@ -335,7 +381,7 @@ int pcc_ingest_points(const int16_t* points, int64_t n, int32_t batch, uint64_t*
   PCC_CHECK_ARG(n >= 0 && batch >= 0 && batch < 65535);
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(points && keys);
-  k_ingest_points<<<blocks_for(n), kThreads, 0, as_stream(s)>>>(points, n, batch, keys);
+  launch_pdl(k_ingest_points, dim3(blocks_for(n)), dim3(kThreads), 0, as_stream(s), points, n, batch, keys);
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -344,7 +390,7 @@ int pcc_ingest_features(const double* colors, const int32_t* src_row, int64_t m,
   PCC_CHECK_ARG(m >= 0 && c_dst >= 8 && c_dst % 8 == 0);
   if (m == 0) return PCC_OK;
   PCC_CHECK_ARG(colors && feats_bf16 && ((uintptr_t)feats_bf16 % 16) == 0);
-  k_ingest_features<<<blocks_for(m), kThreads, 0, as_stream(s)>>>(colors, src_row, m, (uint4*)feats_bf16, c_dst / 8);
+  launch_pdl(k_ingest_features, dim3(blocks_for(m)), dim3(kThreads), 0, as_stream(s), colors, src_row, m, (uint4*)feats_bf16, c_dst / 8);
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -353,7 +399,7 @@ int pcc_ingest_features_bf16(const void* colors_bf16, const int32_t* src_row, in
   PCC_CHECK_ARG(m >= 0 && c_dst >= 8 && c_dst % 8 == 0);
   if (m == 0) return PCC_OK;
   PCC_CHECK_ARG(colors_bf16 && feats_bf16 && ((uintptr_t)feats_bf16 % 16) == 0 && ((uintptr_t)colors_bf16 % 2) == 0);
-  k_ingest_features_bf16<<<blocks_for(m), kThreads, 0, as_stream(s)>>>((const uint16_t*)colors_bf16, src_row, m,
+  launch_pdl(k_ingest_features_bf16, dim3(blocks_for(m)), dim3(kThreads), 0, as_stream(s), (const uint16_t*)colors_bf16, src_row, m,
                                                                       (uint4*)feats_bf16, c_dst / 8);
   PCC_LAUNCHED();
   return PCC_OK;
@@ -363,7 +409,7 @@ int pcc_unpack_output(const uint64_t* keys, const float* feats3, int64_t n, int3
   PCC_CHECK_ARG(n >= 0);
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG((points || colors) && (!points || keys) && (!colors || feats3));
-  k_unpack_output<<<blocks_for(n), kThreads, 0, as_stream(s)>>>(keys, feats3, n, points, colors);
+  launch_pdl(k_unpack_output, dim3(blocks_for(n)), dim3(kThreads), 0, as_stream(s), keys, feats3, n, points, colors);
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -372,7 +418,7 @@ int pcc_pack_visualizer(const uint64_t* keys, const float* feats3, int64_t n, fl
   PCC_CHECK_ARG(n >= 0);
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(keys && feats3 && points_f32 && colors_u8);
-  k_pack_visualizer<<<blocks_for(n), kThreads, 0, as_stream(s)>>>(keys, feats3, n, offset, points_f32, colors_u8);
+  launch_pdl(k_pack_visualizer, dim3(blocks_for(n)), dim3(kThreads), 0, as_stream(s), keys, feats3, n, offset, points_f32, colors_u8);
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -380,7 +426,7 @@ int pcc_coords_from_keys(const uint64_t* keys, int64_t n, int32_t* coords, pcc_s
   PCC_CHECK_ARG(n >= 0);
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(coords && keys);
-  k_coords_from_keys<<<blocks_for(n), kThreads, 0, as_stream(s)>>>(keys, n, (int4*)coords);
+  launch_pdl(k_coords_from_keys, dim3(blocks_for(n)), dim3(kThreads), 0, as_stream(s), keys, n, (int4*)coords);
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -431,17 +477,17 @@ int pcc_sort_unique(const uint64_t* keys_in, int64_t n, uint64_t* keys_out, int3
     set_error("pcc_sort_unique: workspace too small (%lld)", (long long)ws_bytes);
     return PCC_E_WORKSPACE;
   }
-  k_iota<<<blocks_for(n), kThreads, 0, st>>>(iota, n);
+  launch_pdl(k_iota, dim3(blocks_for(n)), dim3(kThreads), 0, st, iota, n);
   PCC_LAUNCHED();
   // radix sort is stable: among equal keys the lowest input row comes first ("first wins")
   PCC_CUDA(cub::DeviceRadixSort::SortPairs(sort_ws, sort_b, keys_in, skeys, iota, srows, (int)n, 0,
                                            64, st));
   g_launches.fetch_add(1);
-  k_run_flags<<<blocks_for(n), kThreads, 0, st>>>(skeys, n, ~0ull, flags);
+  launch_pdl(k_run_flags, dim3(blocks_for(n)), dim3(kThreads), 0, st, skeys, n, ~0ull, flags);
   PCC_LAUNCHED();
   PCC_CUDA(cub::DeviceScan::InclusiveSum(scan_ws, scan_b, flags, flags, (int)n, st));
   g_launches.fetch_add(1);
-  k_scatter_runs<<<blocks_for(n), kThreads, 0, st>>>(skeys, srows, flags, n, ~0ull, keys_out,
+  launch_pdl(k_scatter_runs, dim3(blocks_for(n)), dim3(kThreads), 0, st, skeys, srows, flags, n, ~0ull, keys_out,
                                                      src_row, nullptr, n_out_dev);
   PCC_LAUNCHED();
   return PCC_OK;
@@ -472,11 +518,11 @@ int pcc_coords_downsample(const uint64_t* keys_in, int64_t n, int log2_stride, u
     return PCC_E_WORKSPACE;
   }
   uint64_t mask = ~((1ull << (3 * log2_stride)) - 1ull);
-  k_run_flags<<<blocks_for(n), kThreads, 0, st>>>(keys_in, n, mask, flags);
+  launch_pdl(k_run_flags, dim3(blocks_for(n)), dim3(kThreads), 0, st, keys_in, n, mask, flags);
   PCC_LAUNCHED();
   PCC_CUDA(cub::DeviceScan::InclusiveSum(scan_ws, scan_b, flags, flags, (int)n, st));
   g_launches.fetch_add(1);
-  k_scatter_runs<<<blocks_for(n), kThreads, 0, st>>>(keys_in, nullptr, flags, n, mask, keys_out,
+  launch_pdl(k_scatter_runs, dim3(blocks_for(n)), dim3(kThreads), 0, st, keys_in, nullptr, flags, n, mask, keys_out,
                                                      nullptr, parent_row, n_out_dev);
   PCC_LAUNCHED();
   return PCC_OK;
@@ -509,7 +555,7 @@ int pcc_coords_pyramid(const uint64_t* keys_in, int64_t n, int log2_stride, int 
   }
   const unsigned fo_blocks = blocks_for(num_frames + 1, 64);
   if (num_frames) {
-    k_frame_offsets_dc<<<fo_blocks, 64, 0, st>>>(keys_in, nullptr, n, num_frames, frame_offsets_dev);
+    launch_pdl(k_frame_offsets_dc, dim3(fo_blocks), dim3(64), 0, st, keys_in, nullptr, n, num_frames, frame_offsets_dev);
     PCC_LAUNCHED();
   }
   const uint64_t* cur = keys_in;
@@ -518,14 +564,14 @@ int pcc_coords_pyramid(const uint64_t* keys_in, int64_t n, int log2_stride, int 
     const uint64_t mask = ~((1ull << (3 * (log2_stride + l + 1))) - 1ull);
     uint64_t* out = keys_out + (int64_t)l * n;
     int32_t* par = parent_row + (int64_t)l * n;
-    k_run_flags_dc<<<blocks_for(n), kThreads, 0, st>>>(cur, cur_n, n, mask, flags);
+    launch_pdl(k_run_flags_dc, dim3(blocks_for(n)), dim3(kThreads), 0, st, cur, cur_n, n, mask, flags);
     PCC_LAUNCHED();
     PCC_CUDA(cub::DeviceScan::InclusiveSum(scan_ws, scan_b, flags, flags, (int)n, st));
     g_launches.fetch_add(1);
-    k_scatter_runs_dc<<<blocks_for(n), kThreads, 0, st>>>(cur, flags, cur_n, n, mask, out, par, counts_dev + l);
+    launch_pdl(k_scatter_runs_dc, dim3(blocks_for(n)), dim3(kThreads), 0, st, cur, flags, cur_n, n, mask, out, par, counts_dev + l);
     PCC_LAUNCHED();
     if (num_frames) {
-      k_frame_offsets_dc<<<fo_blocks, 64, 0, st>>>(out, counts_dev + l, n, num_frames,
+      launch_pdl(k_frame_offsets_dc, dim3(fo_blocks), dim3(64), 0, st, out, counts_dev + l, n, num_frames,
                                                    frame_offsets_dev + (int64_t)(l + 1) * (num_frames + 1));
       PCC_LAUNCHED();
     }
@@ -540,7 +586,7 @@ int pcc_coords_children(const uint64_t* keys_in, int64_t n, int log2_stride, uin
   PCC_CHECK_ARG(n >= 0 && 8 * n < (1ll << 31) && log2_stride >= 0 && log2_stride <= 14);
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(keys_in && keys_out);
-  k_children<<<blocks_for(8 * n), kThreads, 0, as_stream(s)>>>(keys_in, n, 3 * log2_stride,
+  launch_pdl(k_children, dim3(blocks_for(8 * n)), dim3(kThreads), 0, as_stream(s), keys_in, n, 3 * log2_stride,
                                                                keys_out);
   PCC_LAUNCHED();
   return PCC_OK;
@@ -550,7 +596,7 @@ int pcc_frame_offsets(const uint64_t* keys, int64_t n, int32_t num_frames, int32
                       pcc_stream_t s) {
   PCC_CHECK_ARG(n >= 0 && num_frames >= 0 && num_frames < 65535 && offsets);
   PCC_CHECK_ARG(n == 0 || keys);
-  k_frame_offsets<<<blocks_for(num_frames + 1, 64), 64, 0, as_stream(s)>>>(keys, n, num_frames,
+  launch_pdl(k_frame_offsets, dim3(blocks_for(num_frames + 1, 64)), dim3(64), 0, as_stream(s), keys, n, num_frames,
                                                                            offsets);
   PCC_LAUNCHED();
   return PCC_OK;
@@ -577,7 +623,7 @@ int pcc_lex_order(const uint64_t* keys, int64_t n, int32_t* perm, void* ws, int6
     set_error("pcc_lex_order: workspace too small");
     return PCC_E_WORKSPACE;
   }
-  k_lex_keys<<<blocks_for(n), kThreads, 0, st>>>(keys, n, lex, row);
+  launch_pdl(k_lex_keys, dim3(blocks_for(n)), dim3(kThreads), 0, st, keys, n, lex, row);
   PCC_LAUNCHED();
   PCC_CUDA(cub::DeviceRadixSort::SortPairs(sort_ws, sort_b, lex, lex_sorted, row, perm, (int)n, 0,
                                            64, st));
@@ -591,8 +637,7 @@ int pcc_rows_f32_to_bf16(const float* src, int c_src, const int32_t* src_row, in
   PCC_CHECK_ARG(n_out >= 0 && c_src > 0 && c_dst > 0);
   if (n_out == 0) return PCC_OK;
   PCC_CHECK_ARG(src && dst_bf16);
-  k_rows_f32_to_bf16<<<blocks_for(n_out * c_dst), kThreads, 0, as_stream(s)>>>(
-      src, c_src, src_row, n_out, (__nv_bfloat16*)dst_bf16, c_dst);
+  launch_pdl(k_rows_f32_to_bf16, dim3(blocks_for(n_out * c_dst)), dim3(kThreads), 0, as_stream(s), src, c_src, src_row, n_out, (__nv_bfloat16*)dst_bf16, c_dst);
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -601,8 +646,7 @@ int pcc_rows_bf16_to_f32(const void* src_bf16, int c_src, int64_t n, float* dst,
   PCC_CHECK_ARG(n >= 0 && c_src > 0 && c_dst > 0 && c_dst <= c_src);
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(src_bf16 && dst);
-  k_rows_bf16_to_f32<<<blocks_for(n * c_dst), kThreads, 0, as_stream(s)>>>(
-      (const __nv_bfloat16*)src_bf16, c_src, n, dst, c_dst);
+  launch_pdl(k_rows_bf16_to_f32, dim3(blocks_for(n * c_dst)), dim3(kThreads), 0, as_stream(s), (const __nv_bfloat16*)src_bf16, c_src, n, dst, c_dst);
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -612,8 +656,7 @@ int pcc_gather_rows_bf16(const void* src_bf16, int c, const int32_t* src_row, in
   if (n_out == 0) return PCC_OK;
   PCC_CHECK_ARG(src_bf16 && dst_bf16 && src_row);
   int chunks = c / 8;
-  k_gather_rows16<<<blocks_for(n_out * chunks), kThreads, 0, as_stream(s)>>>(
-      (const uint4*)src_bf16, chunks, src_row, n_out, (uint4*)dst_bf16);
+  launch_pdl(k_gather_rows16, dim3(blocks_for(n_out * chunks)), dim3(kThreads), 0, as_stream(s), (const uint4*)src_bf16, chunks, src_row, n_out, (uint4*)dst_bf16);
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -622,7 +665,7 @@ int pcc_gather_rows_f32(const float* src, int c, const int32_t* src_row, int64_t
   PCC_CHECK_ARG(n_out >= 0 && c > 0);
   if (n_out == 0) return PCC_OK;
   PCC_CHECK_ARG(src && dst && src_row);
-  k_gather_rows_f32<<<blocks_for(n_out * c), kThreads, 0, as_stream(s)>>>(src, c, src_row, n_out,
+  launch_pdl(k_gather_rows_f32, dim3(blocks_for(n_out * c)), dim3(kThreads), 0, as_stream(s), src, c, src_row, n_out,
                                                                           dst);
   PCC_LAUNCHED();
   return PCC_OK;
@@ -632,7 +675,7 @@ int pcc_gather_keys(const uint64_t* src, const int32_t* src_row, int64_t n_out, 
   PCC_CHECK_ARG(n_out >= 0);
   if (n_out == 0) return PCC_OK;
   PCC_CHECK_ARG(src && dst && src_row);
-  k_gather_keys<<<blocks_for(n_out), kThreads, 0, as_stream(s)>>>(src, src_row, n_out, dst);
+  launch_pdl(k_gather_keys, dim3(blocks_for(n_out)), dim3(kThreads), 0, as_stream(s), src, src_row, n_out, dst);
   PCC_LAUNCHED();
   return PCC_OK;
 }

@@ -46,6 +46,8 @@ __global__ void __launch_bounds__(256)
 k_factorized_quant(const float* __restrict__ z, const int32_t* __restrict__ perm,
                    const float* __restrict__ med, int64_t n, int C, int32_t* __restrict__ sym,
                    __nv_bfloat16* __restrict__ zb, float* __restrict__ zf) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ int32_t tile[kTile][kTile + 1];
   const int tx = threadIdx.x, ty = threadIdx.y;
   const int64_t i0 = (int64_t)blockIdx.x * kTile;
@@ -79,6 +81,8 @@ __global__ void __launch_bounds__(256)
 k_factorized_dequant(const int32_t* __restrict__ sym, const int32_t* __restrict__ perm,
                      const float* __restrict__ med, int64_t n, int C, __nv_bfloat16* __restrict__ zb,
                      float* __restrict__ zf) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ int32_t tile[kTile][kTile + 1];
   const int tx = threadIdx.x, ty = threadIdx.y;
   const int64_t i0 = (int64_t)blockIdx.x * kTile;
@@ -112,6 +116,8 @@ k_gauss_params(const float* __restrict__ y, const float* __restrict__ params,
                const float* __restrict__ scale, const float* __restrict__ table, int table_len,
                float bound, int64_t n, int C, int Q, int32_t* __restrict__ sym,
                uint16_t* __restrict__ idx) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ int32_t tsym[kTile][kTile + 1];
   __shared__ uint16_t tidx[kTile][kTile + 2];
   __shared__ float stable[256];
@@ -165,6 +171,8 @@ k_gauss_dequant(const int32_t* __restrict__ sym, const float* __restrict__ param
                 const int32_t* __restrict__ prow, const int32_t* __restrict__ perm,
                 const float* __restrict__ scale, const float* __restrict__ gain, float bound, int64_t n,
                 int C, __nv_bfloat16* __restrict__ yb, float* __restrict__ yf) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ int32_t tile[kTile][kTile + 1];
   const int tx = threadIdx.x, ty = threadIdx.y;
   const int64_t i0 = (int64_t)blockIdx.x * kTile;
@@ -220,8 +228,7 @@ int pcc_factorized_quant(const float* z, const int32_t* perm, const float* media
   PCC_CHECK_ARG(n >= 0 && c > 0 && c <= 65535 * kTile);
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(z && medians && sym);
-  k_factorized_quant<<<tile_grid(n, c), dim3(32, 8), 0, as_stream(s)>>>(
-      z, perm, medians, n, c, sym, (__nv_bfloat16*)zhat_bf16, zhat_f32);
+  launch_pdl(k_factorized_quant, dim3(tile_grid(n, c)), dim3(dim3(32, 8)), 0, as_stream(s), z, perm, medians, n, c, sym, (__nv_bfloat16*)zhat_bf16, zhat_f32);
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -231,8 +238,7 @@ int pcc_factorized_dequant(const int32_t* sym, const int32_t* perm, const float*
   PCC_CHECK_ARG(n >= 0 && c > 0);
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(sym && medians && (zhat_bf16 || zhat_f32));
-  k_factorized_dequant<<<tile_grid(n, c), dim3(32, 8), 0, as_stream(s)>>>(
-      sym, perm, medians, n, c, (__nv_bfloat16*)zhat_bf16, zhat_f32);
+  launch_pdl(k_factorized_dequant, dim3(tile_grid(n, c)), dim3(dim3(32, 8)), 0, as_stream(s), sym, perm, medians, n, c, (__nv_bfloat16*)zhat_bf16, zhat_f32);
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -243,8 +249,7 @@ int pcc_gauss_encode(const float* y, const float* params, const int32_t* prow, c
   PCC_CHECK_ARG(n >= 0 && c > 0 && q >= 1 && table_len >= 2 && table_len <= 256);
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(y && params && scale && scale_table && sym && idx);
-  k_gauss_params<true><<<tile_grid(n, c), dim3(32, 8), 0, as_stream(s)>>>(
-      y, params, prow, perm, scale, scale_table, table_len, scale_bound, n, c, q, sym, idx);
+  launch_pdl(k_gauss_params<true>, dim3(tile_grid(n, c)), dim3(dim3(32, 8)), 0, as_stream(s), y, params, prow, perm, scale, scale_table, table_len, scale_bound, n, c, q, sym, idx);
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -255,8 +260,7 @@ int pcc_gauss_indexes(const float* params, const int32_t* prow, const int32_t* p
   PCC_CHECK_ARG(n >= 0 && c > 0 && table_len >= 2 && table_len <= 256);
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(params && scale && scale_table && idx);
-  k_gauss_params<false><<<tile_grid(n, c), dim3(32, 8), 0, as_stream(s)>>>(
-      nullptr, params, prow, perm, scale, scale_table, table_len, scale_bound, n, c, 1, nullptr, idx);
+  launch_pdl(k_gauss_params<false>, dim3(tile_grid(n, c)), dim3(dim3(32, 8)), 0, as_stream(s), nullptr, params, prow, perm, scale, scale_table, table_len, scale_bound, n, c, 1, nullptr, idx);
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -268,8 +272,7 @@ int pcc_gauss_dequant(const int32_t* sym, const float* params, const int32_t* pr
   PCC_CHECK_ARG(n >= 0 && c > 0);
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(sym && params && scale && (yhat_bf16 || yhat_f32));
-  k_gauss_dequant<<<tile_grid(n, c), dim3(32, 8), 0, as_stream(s)>>>(
-      sym, params, prow, perm, scale, offset_gain, scale_bound, n, c, (__nv_bfloat16*)yhat_bf16,
+  launch_pdl(k_gauss_dequant, dim3(tile_grid(n, c)), dim3(dim3(32, 8)), 0, as_stream(s), sym, params, prow, perm, scale, offset_gain, scale_bound, n, c, (__nv_bfloat16*)yhat_bf16,
       yhat_f32);
   PCC_LAUNCHED();
   return PCC_OK;

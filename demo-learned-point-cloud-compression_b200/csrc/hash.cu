@@ -12,12 +12,16 @@ namespace pcc {
 constexpr int kWin = 4;
 
 __global__ void k_hash_clear(uint64_t* __restrict__ tk, int64_t cap) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i < cap) tk[i] = kEmptyKey;
 }
 
 __global__ void k_hash_insert(const uint64_t* __restrict__ keys, int64_t n, uint64_t* __restrict__ tk,
                               int32_t* __restrict__ tv, uint64_t cap_mask) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   uint64_t key = keys[i];
@@ -72,6 +76,8 @@ __device__ __forceinline__ int32_t probe4(uint64_t key, bool active, const uint6
 __global__ void k_hash_query(const uint64_t* __restrict__ q, int64_t nq, const uint64_t* __restrict__ tk,
                              const int32_t* __restrict__ tv, uint64_t cap_mask,
                              int32_t* __restrict__ rows) {
+  pdl_trigger();
+  pdl_wait();
   int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   int64_t qi = t >> 2;
   int sub = threadIdx.x & 3;
@@ -87,6 +93,8 @@ __global__ void k_hash_query(const uint64_t* __restrict__ q, int64_t nq, const u
 __global__ void __launch_bounds__(256)
 k_kmap_k3(const uint64_t* __restrict__ keys, int64_t n, int step, const uint64_t* __restrict__ tk,
           const int32_t* __restrict__ tv, uint64_t cap_mask, int32_t* __restrict__ nbr) {
+  pdl_trigger();
+  pdl_wait();
   int64_t o = blockIdx.x * 64ll + (threadIdx.x >> 2);
   int sub = threadIdx.x & 3;
   int gshift = (threadIdx.x & 31) & ~3;
@@ -111,12 +119,16 @@ k_kmap_k3(const uint64_t* __restrict__ keys, int64_t n, int step, const uint64_t
 }
 
 __global__ void k_fill_i32(int32_t* __restrict__ p, int64_t n, int32_t v) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i < n) p[i] = v;
 }
 
 __global__ void k_kmap_down2(const uint64_t* __restrict__ ckeys, const int32_t* __restrict__ parent,
                              int64_t n_child, int shift, int32_t* __restrict__ nbr, int64_t ld) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n_child) return;
   int j = (int)((ckeys[i] >> shift) & 7ull);
@@ -136,6 +148,8 @@ __global__ void k_kmap_down2(const uint64_t* __restrict__ ckeys, const int32_t* 
 __global__ void __launch_bounds__(256)
 k_blockmap_insert(const uint64_t* __restrict__ keys, int64_t n, int shift, uint64_t* __restrict__ tk,
                   ulonglong2* __restrict__ tv, uint64_t cap_mask) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint64_t k = keys[i];
@@ -211,6 +225,8 @@ __global__ void __launch_bounds__(kKmapThreads)
 k_kmap_k3_blocks(const uint64_t* __restrict__ keys, int64_t n, int l, const uint64_t* __restrict__ tk,
                  const ulonglong2* __restrict__ tv, uint64_t cap_mask, int32_t* __restrict__ nbr,
                  int64_t ld) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ uint4 ent[8][kKmapThreads];
   const int tid = threadIdx.x;
   const int64_t o = blockIdx.x * (int64_t)blockDim.x + tid;
@@ -290,11 +306,11 @@ int pcc_hash_build(const uint64_t* keys, int64_t n, uint64_t* table_keys, int32_
   PCC_CHECK_ARG(n >= 0 && capacity >= 8 && (capacity & (capacity - 1)) == 0 && capacity >= 2 * n);
   PCC_CHECK_ARG(table_keys && table_vals);
   cudaStream_t st = as_stream(s);
-  k_hash_clear<<<(unsigned)((capacity + 255) / 256), 256, 0, st>>>(table_keys, capacity);
+  launch_pdl(k_hash_clear, dim3((unsigned)((capacity + 255) / 256)), dim3(256), 0, st, table_keys, capacity);
   PCC_LAUNCHED();
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(keys);
-  k_hash_insert<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(keys, n, table_keys, table_vals,
+  launch_pdl(k_hash_insert, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, st, keys, n, table_keys, table_vals,
                                                             (uint64_t)capacity - 1);
   PCC_LAUNCHED();
   return PCC_OK;
@@ -306,8 +322,7 @@ int pcc_hash_query(const uint64_t* queries, int64_t nq, const uint64_t* table_ke
   if (nq == 0) return PCC_OK;
   PCC_CHECK_ARG(queries && table_keys && table_vals && rows);
   int64_t threads = nq * 4;
-  k_hash_query<<<(unsigned)((threads + 255) / 256), 256, 0, as_stream(s)>>>(
-      queries, nq, table_keys, table_vals, (uint64_t)capacity - 1, rows);
+  launch_pdl(k_hash_query, dim3((unsigned)((threads + 255) / 256)), dim3(256), 0, as_stream(s), queries, nq, table_keys, table_vals, (uint64_t)capacity - 1, rows);
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -318,8 +333,7 @@ int pcc_kmap_k3(const uint64_t* keys, int64_t n, int log2_stride, const uint64_t
   PCC_CHECK_ARG(capacity >= 8 && (capacity & (capacity - 1)) == 0);
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(keys && table_keys && table_vals && nbr);
-  k_kmap_k3<<<(unsigned)((n + 63) / 64), 256, 0, as_stream(s)>>>(
-      keys, n, 1 << log2_stride, table_keys, table_vals, (uint64_t)capacity - 1, nbr);
+  launch_pdl(k_kmap_k3, dim3((unsigned)((n + 63) / 64)), dim3(256), 0, as_stream(s), keys, n, 1 << log2_stride, table_keys, table_vals, (uint64_t)capacity - 1, nbr);
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -333,11 +347,10 @@ int pcc_kmap_down2(const uint64_t* child_keys, const int32_t* parent_row, int64_
   PCC_CHECK_ARG(child_keys && parent_row && nbr);
   cudaStream_t st = as_stream(s);
   int64_t tot = 8 * nbr_ld;
-  k_fill_i32<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(nbr, tot, -1);
+  launch_pdl(k_fill_i32, dim3((unsigned)((tot + 255) / 256)), dim3(256), 0, st, nbr, tot, -1);
   PCC_LAUNCHED();
   if (n_child == 0) return PCC_OK;
-  k_kmap_down2<<<(unsigned)((n_child + 255) / 256), 256, 0, st>>>(
-      child_keys, parent_row, n_child, 3 * log2_child_stride, nbr, nbr_ld);
+  launch_pdl(k_kmap_down2, dim3((unsigned)((n_child + 255) / 256)), dim3(256), 0, st, child_keys, parent_row, n_child, 3 * log2_child_stride, nbr, nbr_ld);
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -349,11 +362,11 @@ int pcc_blockmap_build(const uint64_t* keys, int64_t n, int log2_stride, uint64_
   PCC_CHECK_ARG(table_keys && table_vals16 && ((uintptr_t)table_vals16 % 16) == 0 &&
                 ((uintptr_t)table_keys % 32) == 0);
   cudaStream_t st = as_stream(s);
-  k_hash_clear<<<(unsigned)((capacity + 255) / 256), 256, 0, st>>>(table_keys, capacity);
+  launch_pdl(k_hash_clear, dim3((unsigned)((capacity + 255) / 256)), dim3(256), 0, st, table_keys, capacity);
   PCC_LAUNCHED();
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(keys);
-  k_blockmap_insert<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(keys, n, 3 * log2_stride, table_keys,
+  launch_pdl(k_blockmap_insert, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, st, keys, n, 3 * log2_stride, table_keys,
                                                                 (ulonglong2*)table_vals16,
                                                                 (uint64_t)capacity - 1);
   PCC_LAUNCHED();
@@ -367,8 +380,7 @@ int pcc_kmap_k3_blocks(const uint64_t* keys, int64_t n, int log2_stride, const u
   PCC_CHECK_ARG(capacity >= 8 && (capacity & (capacity - 1)) == 0);
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(keys && table_keys && table_vals16 && nbr);
-  k_kmap_k3_blocks<<<(unsigned)((n + 255) / 256), 256, 0, as_stream(s)>>>(
-      keys, n, log2_stride, table_keys, (const ulonglong2*)table_vals16, (uint64_t)capacity - 1, nbr,
+  launch_pdl(k_kmap_k3_blocks, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, as_stream(s), keys, n, log2_stride, table_keys, (const ulonglong2*)table_vals16, (uint64_t)capacity - 1, nbr,
       nbr_ld);
   PCC_LAUNCHED();
   return PCC_OK;

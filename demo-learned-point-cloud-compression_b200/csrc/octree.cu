@@ -35,6 +35,8 @@ __device__ __forceinline__ int oct_depth(uint64_t first, uint64_t last) {
 __global__ void __launch_bounds__(kOctEncThreads)
 k_octree_levels(const uint64_t* __restrict__ keys, const int32_t* __restrict__ frame_off, int shift0,
                 uint32_t* __restrict__ scratch, int64_t pitch_words, int32_t* __restrict__ counts) {
+  pdl_trigger();
+  pdl_wait();
   using Scan = cub::BlockScan<int, kOctEncThreads>;
   __shared__ typename Scan::TempStorage tmp;
   const int l = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
@@ -76,6 +78,8 @@ __global__ void __launch_bounds__(256)
 k_octree_pack(const uint64_t* __restrict__ keys, const int32_t* __restrict__ frame_off, int shift0,
               const uint32_t* __restrict__ scratch, int64_t pitch_words, const int32_t* __restrict__ counts,
               uint8_t* __restrict__ out, const int64_t* __restrict__ out_off, int32_t* __restrict__ sizes) {
+  pdl_trigger();
+  pdl_wait();
   const int l = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
   const int r0 = frame_off[b], r1 = frame_off[b + 1];
   const int n = r1 - r0 > 0 ? r1 - r0 : 0;
@@ -118,6 +122,8 @@ k_octree_decode(const uint8_t* __restrict__ streams, const int64_t* __restrict__
                 const int32_t* __restrict__ stream_len, const int32_t* __restrict__ row_off, int shift0,
                 uint64_t* __restrict__ nodes_a, uint64_t* __restrict__ nodes_b, uint64_t* __restrict__ keys_out,
                 int32_t* __restrict__ status) {
+  pdl_trigger();
+  pdl_wait();
   using Scan = cub::BlockScan<int, kOctDecThreads>;
   __shared__ typename Scan::TempStorage tmp;
   __shared__ uint32_t hdr_s[5 + kOctMaxDepth];
@@ -233,11 +239,11 @@ int pcc_octree_encode(const uint64_t* keys, int64_t n_total, const int32_t* fram
   PCC_CUDA(cudaMemsetAsync(ws, 0, (size_t)pcc_octree_encode_workspace_bytes(n_total, num_frames) - 64, st));
   dim3 grid(kOctMaxDepth, (unsigned)num_frames);
   if (n_total > 0) {
-    k_octree_levels<<<grid, kOctEncThreads, 0, st>>>(keys, frame_offsets_dev, 3 * log2_stride, scratch, pitch / 4,
+    launch_pdl(k_octree_levels, dim3(grid), dim3(kOctEncThreads), 0, st, keys, frame_offsets_dev, 3 * log2_stride, scratch, pitch / 4,
                                                     counts);
     PCC_LAUNCHED();
   }
-  k_octree_pack<<<grid, 256, 0, st>>>(keys, frame_offsets_dev, 3 * log2_stride, scratch, pitch / 4, counts, out,
+  launch_pdl(k_octree_pack, dim3(grid), dim3(256), 0, st, keys, frame_offsets_dev, 3 * log2_stride, scratch, pitch / 4, counts, out,
                                       out_offsets_dev, sizes_dev);
   PCC_LAUNCHED();
   return PCC_OK;
@@ -261,7 +267,7 @@ int pcc_octree_decode(const uint8_t* streams, const int64_t* stream_offsets_dev,
   }
   uint64_t* a = (uint64_t*)ws;
   uint64_t* b = a + (n_total > 0 ? n_total : 1);
-  k_octree_decode<<<(unsigned)num_frames, kOctDecThreads, 0, st>>>(streams, stream_offsets_dev, stream_bytes_dev,
+  launch_pdl(k_octree_decode, dim3((unsigned)num_frames), dim3(kOctDecThreads), 0, st, streams, stream_offsets_dev, stream_bytes_dev,
                                                                  row_offsets_dev, 3 * log2_stride, a, b, keys_out,
                                                                  status_dev);
   PCC_LAUNCHED();

@@ -20,6 +20,8 @@ __host__ __device__ inline uint32_t align16(uint32_t v) { return (v + 15u) & ~15
 __global__ void __launch_bounds__(256)
 k_pack_strings(PackArgs a, int n, int first, int batch, uint32_t payload0, uint8_t* __restrict__ out, int64_t out_cap,
                int n_total) {
+  pdl_trigger();
+  pdl_wait();
   uint32_t* hdr = reinterpret_cast<uint32_t*>(out);
   const int sidx = blockIdx.y;
   uint32_t off = batch == 0 ? payload0 : hdr[n_total + batch - 1];
@@ -72,7 +74,7 @@ int pcc_pack_strings(const void* const* bufs, const int32_t* const* lens, int32_
       a.buf[i] = nullptr;
       a.len[i] = nullptr;
     }
-    k_pack_strings<<<dim3(8, cnt), 256, 0, as_stream(s)>>>(a, cnt, first, batch, (uint32_t)hdr, out, out_cap, n);
+    launch_pdl(k_pack_strings, dim3(dim3(8, cnt)), dim3(256), 0, as_stream(s), a, cnt, first, batch, (uint32_t)hdr, out, out_cap, n);
     PCC_LAUNCHED();
   }
   return PCC_OK;

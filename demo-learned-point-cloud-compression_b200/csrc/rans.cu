@@ -88,6 +88,8 @@ __device__ __forceinline__ SymOps make_ops(int32_t symbol, int32_t t, const Tabl
 __global__ void __launch_bounds__(256)
 k_rans_prepare(const int32_t* __restrict__ sym, const uint16_t* __restrict__ idx, int64_t chan_len, int64_t n,
                Tables T, uint32_t* __restrict__ packed, uint32_t* __restrict__ raw, uint32_t* __restrict__ escmask) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   uint32_t pk = 0, rw = 0;
   bool esc = false;
@@ -125,6 +127,8 @@ __global__ void __launch_bounds__(32 * kEncWarps)
 k_rans_encode(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ raw,
               const uint32_t* __restrict__ escmask, int64_t n, int32_t seg_size, int32_t nseg,
               uint16_t* __restrict__ scratch, uint32_t* __restrict__ states, int32_t* __restrict__ nwords) {
+  pdl_trigger();
+  pdl_wait();
   const int seg = blockIdx.x * kEncWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (seg >= nseg) return;
   const unsigned lt = (1u << lane) - 1u;
@@ -212,6 +216,8 @@ __global__ void __launch_bounds__(256)
 k_rans_pack(const uint16_t* __restrict__ scratch, const uint32_t* __restrict__ states,
             const int32_t* __restrict__ nwords, int32_t nseg, int32_t seg_size, uint32_t n,
             uint8_t* __restrict__ out, int32_t* __restrict__ out_bytes) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ uint32_t s_off;
   __shared__ uint32_t red[256];
   const int seg = blockIdx.x, tid = threadIdx.x;
@@ -250,6 +256,8 @@ k_rans_pack(const uint16_t* __restrict__ scratch, const uint32_t* __restrict__ s
 // lut[t][b] = largest s in [0, maxv] with cdf_t[s] <= b << kLutShift (b = 0..kLutN-1), lut[t][kLutN] = maxv:
 // the symbol of cumulative frequency cf lies in [lut[t][cf >> kLutShift], lut[t][(cf >> kLutShift) + 1]].
 __global__ void k_rans_build_lut(Tables T, uint16_t* __restrict__ lut) {
+  pdl_trigger();
+  pdl_wait();
   const int t = blockIdx.x;
   const int32_t coff = T.off[t], maxv = T.size[t] - 2;
   for (int b = threadIdx.x; b <= kLutN; b += blockDim.x) {
@@ -279,6 +287,8 @@ __global__ void __launch_bounds__(32 * kDecWarps)
 k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, int32_t seg_size_arg,
               const uint16_t* __restrict__ idx, int64_t chan_len, int64_t n, int32_t nseg_arg, Tables T,
               int32_t* __restrict__ sym, int32_t* __restrict__ status) {
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ __align__(16) uint8_t dec_smem[];
   int4* s_meta = reinterpret_cast<int4*>(dec_smem);                                  // [T]
   uint16_t* s_lut = reinterpret_cast<uint16_t*>(dec_smem + (size_t)T.T * 16);        // [T][kLutN+1]
@@ -503,12 +513,12 @@ int pcc_rans_encode(const int32_t* sym, const uint16_t* idx, int64_t chan_len, i
   Tables T{tables->cdf, tables->cdf_off, tables->cdf_size, tables->offset, tables->lut, tables->num_tables, tables->cdf_total};
   cudaStream_t st = as_stream(s);
   const int64_t cl = chan_len > 0 ? chan_len : 1;
-  k_rans_prepare<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(sym, idx, cl, n, T, packed, raw, escmask);
+  launch_pdl(k_rans_prepare, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, st, sym, idx, cl, n, T, packed, raw, escmask);
   PCC_LAUNCHED();
-  k_rans_encode<<<(ns + kEncWarps - 1) / kEncWarps, 32 * kEncWarps, 0, st>>>(packed, raw, escmask, n, seg_size, ns,
+  launch_pdl(k_rans_encode, dim3((ns + kEncWarps - 1) / kEncWarps), dim3(32 * kEncWarps), 0, st, packed, raw, escmask, n, seg_size, ns,
                                                                           scratch, states, nwords);
   PCC_LAUNCHED();
-  k_rans_pack<<<ns, 256, 0, st>>>(scratch, states, nwords, ns, seg_size, (uint32_t)n, out, out_bytes_dev);
+  launch_pdl(k_rans_pack, dim3(ns), dim3(256), 0, st, scratch, states, nwords, ns, seg_size, (uint32_t)n, out, out_bytes_dev);
   PCC_LAUNCHED();
   return PCC_OK;
 }
@@ -537,10 +547,10 @@ int pcc_rans_decode(const uint8_t* container, int64_t container_bytes, int32_t s
     configured = true;
   }
   if (T.lut && T.total > 0 && smem <= 224 * 1024) {
-    k_rans_decode<true><<<grid, 32 * kDecWarps, smem, st>>>(container, container_bytes, seg_size, idx,
+    launch_pdl(k_rans_decode<true>, dim3(grid), dim3(32 * kDecWarps), smem, st, container, container_bytes, seg_size, idx,
                                                           chan_len > 0 ? chan_len : 1, n, ns, T, sym, status_dev);
   } else {
-    k_rans_decode<false><<<grid, 32 * kDecWarps, wsm, st>>>(container, container_bytes, seg_size, idx,
+    launch_pdl(k_rans_decode<false>, dim3(grid), dim3(32 * kDecWarps), wsm, st, container, container_bytes, seg_size, idx,
                                                         chan_len > 0 ? chan_len : 1, n, ns, T, sym, status_dev);
   }
   PCC_LAUNCHED();
@@ -553,7 +563,7 @@ int pcc_rans_build_lut(const pcc_cdf_tables_t* tables, uint16_t* lut, pcc_stream
   PCC_CHECK_ARG(tables && lut && tables->num_tables > 0);
   PCC_CHECK_ARG(tables->cdf && tables->cdf_off && tables->cdf_size && tables->offset);
   Tables T{tables->cdf, tables->cdf_off, tables->cdf_size, tables->offset, nullptr, tables->num_tables, 0};
-  k_rans_build_lut<<<tables->num_tables, 128, 0, as_stream(s)>>>(T, lut);
+  launch_pdl(k_rans_build_lut, dim3(tables->num_tables), dim3(128), 0, as_stream(s), T, lut);
   PCC_LAUNCHED();
   return PCC_OK;
 }

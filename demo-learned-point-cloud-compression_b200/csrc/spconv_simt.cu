@@ -15,6 +15,8 @@ k_spconv_narrow(const __nv_bfloat16* __restrict__ in, int cin, const int32_t* __
                 const float* __restrict__ bias, const __nv_bfloat16* __restrict__ residual,
                 int64_t ldr, int relu, __nv_bfloat16* __restrict__ out_bf16,
                 float* __restrict__ out_f32, int64_t ldo) {
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ float ws[];  // [kvol][cin][COUT]
   int total = kvol * cin * COUT;
   for (int i = threadIdx.x; i < total; i += blockDim.x) ws[i] = __bfloat162float(w[i]);
@@ -68,6 +70,8 @@ __global__ void k_spconv_wide_ref(const __nv_bfloat16* __restrict__ in, int cin,
                                   int cout, const __nv_bfloat16* __restrict__ residual, int64_t ldr,
                                   int relu, __nv_bfloat16* __restrict__ out_bf16,
                                   float* __restrict__ out_f32, int64_t ldo) {
+  pdl_trigger();
+  pdl_wait();
   int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (t >= n_out * cout) return;
   int64_t o = t / cout;
@@ -96,7 +100,7 @@ using namespace pcc;
   case C:                                                                                       \
     PCC_CUDA(cudaFuncSetAttribute(k_spconv_narrow<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                   (int)smem));                                                  \
-    k_spconv_narrow<C><<<grid, 256, smem, st>>>(in, cin, nbr, n_out, kvol, w, bias, res, ldr,   \
+    launch_pdl(k_spconv_narrow<C>, dim3(grid), dim3(256), smem, st, in, cin, nbr, n_out, kvol, w, bias, res, ldr,   \
                                                 relu, ob, out_f32, ldo);                        \
     break;
 
@@ -139,8 +143,7 @@ extern "C" int pcc_spconv_simt(const void* in_bf16, int64_t n_in, int cin, const
     return PCC_OK;
   }
   int64_t tot = n_out * cout;
-  k_spconv_wide_ref<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(
-      in, cin, nbr, n_out, kvol, w, bias, cout, res, ldr, relu, ob, out_f32, ldo);
+  launch_pdl(k_spconv_wide_ref, dim3((unsigned)((tot + 255) / 256)), dim3(256), 0, st, in, cin, nbr, n_out, kvol, w, bias, cout, res, ldr, relu, ob, out_f32, ldo);
   PCC_LAUNCHED();
   return PCC_OK;
 }

@@ -218,6 +218,7 @@ k_spconv_umma(const UmmaParams p) {
   const int warp = tid >> 5;
   const int lane = tid & 31;
   const int cout = p.cout, kvol = p.kvol;
+  pdl_trigger();      // the next convolution of the stream may set itself up on SMs this grid leaves
   constexpr int lt = LT, T = 1 << LT;   // compile time: the tile loops unroll, dirty bits become immediates
   const uint32_t b_bytes = (uint32_t)CIN * cout * 2u;
   const uint32_t a_bytes = a_tile << lt;    // one stage: T tiles
@@ -256,6 +257,10 @@ k_spconv_umma(const UmmaParams p) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = ld_shared_u32(tmem_slot);
+  // Everything above (barriers, TMEM) is this CTA's own; from here on the kernel reads what its predecessors in
+  // the stream wrote (feature rows, kernel map, residual).  The launch is a programmatic dependent one, so this CTA
+  // may have become resident while the previous kernel's last CTAs were still running.
+  pdl_wait();
 
   if (warp >= kProdWarp0) {
     // ---------------- gather groups ----------------
@@ -570,8 +575,8 @@ static int launch_umma_glt(const UmmaParams& p, size_t smem, unsigned grid, cuda
     PCC_CUDA(cudaFuncSetAttribute(k_spconv_umma<CIN, G, LT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
     configured = true;
   }
-  k_spconv_umma<CIN, G, LT><<<grid, 32 * (kProdWarp0 + 4 * G), smem, st>>>(p);
-  PCC_LAUNCHED();
+  pcc::g_launches.fetch_add(1);
+  PCC_CUDA(launch_pdl(k_spconv_umma<CIN, G, LT>, dim3(grid), dim3(32 * (kProdWarp0 + 4 * G)), smem, st, p));
   return PCC_OK;
 }
 template <int CIN, int G>

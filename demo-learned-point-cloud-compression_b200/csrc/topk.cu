@@ -30,6 +30,8 @@ struct SelState {
 };
 
 __global__ void k_sel_init(const int32_t* __restrict__ k, int nf, SelState* __restrict__ st, uint32_t* __restrict__ hist) {
+  pdl_trigger();
+  pdl_wait();
   const int b = blockIdx.x;
   if (threadIdx.x == 0) {
     st[b].prefix = 0;
@@ -45,6 +47,8 @@ __global__ void k_sel_init(const int32_t* __restrict__ k, int nf, SelState* __re
 __global__ void __launch_bounds__(kSelThreads)
 k_sel_pass(const float* __restrict__ logits, const int32_t* __restrict__ frame_off, int shift,
            SelState* __restrict__ st, uint32_t* __restrict__ hist) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ uint32_t sh[256];
   __shared__ bool last;
   const int b = blockIdx.y;
@@ -98,6 +102,8 @@ k_sel_pass(const float* __restrict__ logits, const int32_t* __restrict__ frame_o
 __global__ void __launch_bounds__(kSelThreads)
 k_sel_ties(const float* __restrict__ logits, const int32_t* __restrict__ frame_off, const SelState* __restrict__ st,
            int32_t* __restrict__ tie) {
+  pdl_trigger();
+  pdl_wait();
   const int b = blockIdx.y;
   const int r0 = frame_off[b], r1 = frame_off[b + 1];
   const uint32_t T = st[b].prefix;
@@ -113,6 +119,8 @@ k_sel_ties(const float* __restrict__ logits, const int32_t* __restrict__ frame_o
 __global__ void __launch_bounds__(kSelThreads)
 k_sel_flags(const float* __restrict__ logits, const int32_t* __restrict__ frame_off, const SelState* __restrict__ st,
             const int32_t* __restrict__ tie_scan, uint8_t* __restrict__ flags) {
+  pdl_trigger();
+  pdl_wait();
   const int b = blockIdx.y;
   const int r0 = frame_off[b], r1 = frame_off[b + 1];
   const int base = r0 + blockIdx.x * kSelChunk;
@@ -193,17 +201,17 @@ int pcc_topk_select(const float* logits, const uint64_t* keys, int64_t n,
   PCC_CUDA(cudaMemsetAsync(flags, 0, (size_t)n, st));
   PCC_CUDA(cudaMemsetAsync(tie, 0, (size_t)n * 4, st));
   const dim3 grid((unsigned)((n + kSelChunk - 1) / kSelChunk), (unsigned)num_frames);
-  k_sel_init<<<(unsigned)num_frames, 256, 0, st>>>(k, num_frames, state, hist);
+  launch_pdl(k_sel_init, dim3((unsigned)num_frames), dim3(256), 0, st, k, num_frames, state, hist);
   PCC_LAUNCHED();
   for (int shift = 24; shift >= 0; shift -= 8) {
-    k_sel_pass<<<grid, kSelThreads, 0, st>>>(logits, frame_offsets, shift, state, hist);
+    launch_pdl(k_sel_pass, dim3(grid), dim3(kSelThreads), 0, st, logits, frame_offsets, shift, state, hist);
     PCC_LAUNCHED();
   }
-  k_sel_ties<<<grid, kSelThreads, 0, st>>>(logits, frame_offsets, state, tie);
+  launch_pdl(k_sel_ties, dim3(grid), dim3(kSelThreads), 0, st, logits, frame_offsets, state, tie);
   PCC_LAUNCHED();
   PCC_CUDA(cub::DeviceScan::ExclusiveSum(sws, sb, tie, tie_scan, (int)n, st));
   g_launches.fetch_add(1);
-  k_sel_flags<<<grid, kSelThreads, 0, st>>>(logits, frame_offsets, state, tie_scan, flags);
+  launch_pdl(k_sel_flags, dim3(grid), dim3(kSelThreads), 0, st, logits, frame_offsets, state, tie_scan, flags);
   PCC_LAUNCHED();
   PCC_CUDA(cub::DeviceSelect::Flagged(fws, fb, cub::CountingInputIterator<int32_t>(0), flags, keep_row,
                                       n_keep_dev, (int)n, st));
