@@ -260,6 +260,11 @@ k_spconv_umma(const UmmaParams p) {
   // Everything above (barriers, TMEM) is this CTA's own; from here on the kernel reads what its predecessors in
   // the stream wrote (feature rows, kernel map, residual).  The launch is a programmatic dependent one, so this CTA
   // may have become resident while the previous kernel's last CTAs were still running.
+  // The resident weight panels are constants of the model: their copy goes out before the wait.
+  if (warp == kLoaderWarp && lane == 0 && p.wres) {
+    mbar_arrive_expect_tx(wfull, w_total);
+    for (int j = 0; j < kvol; ++j) bulk_g2s(w0 + (uint32_t)j * b_bytes, p.w + (size_t)j * b_bytes, b_bytes, wfull);
+  }
   pdl_wait();
 
   if (warp >= kProdWarp0) {
@@ -358,11 +363,7 @@ k_spconv_umma(const UmmaParams p) {
       while (j >= (uint32_t)kvol) { j -= kvol; ++r; rg += gridDim.x; }
     }
   } else if (warp == kLoaderWarp) {
-    // ---------------- kernel-map loader + resident weights ----------------
-    if (lane == 0 && p.wres) {
-      mbar_arrive_expect_tx(wfull, w_total);
-      for (int j = 0; j < kvol; ++j) bulk_g2s(w0 + (uint32_t)j * b_bytes, p.w + (size_t)j * b_bytes, b_bytes, wfull);
-    }
+    // ---------------- kernel-map loader (the resident weights were requested before the wait) ----------------
     if (p.nbr) {
       uint32_t unit = 0;
       const int jc = p.jc;
