@@ -150,16 +150,27 @@ k_blockmap_insert(const uint64_t* __restrict__ keys, int64_t n, int shift, uint6
                   ulonglong2* __restrict__ tv, uint64_t cap_mask) {
   pdl_trigger();
   pdl_wait();
-  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const uint64_t k = keys[i];
-  const uint64_t bkey = k >> (shift + 6);
-  if (i > 0 && (keys[i - 1] >> (shift + 6)) == bkey) return;  // not the first row of its block
-  uint64_t mask = 1ull << ((k >> shift) & 63ull);
-  for (int64_t j = i + 1; j < n && j < i + 64; ++j) {
-    const uint64_t kj = keys[j];
-    if ((kj >> (shift + 6)) != bkey) break;
-    mask |= 1ull << ((kj >> shift) & 63ull);
+  // The rows of a block are consecutive, so the lanes of a warp that hold rows of one block find each other with a
+  // match and OR their occupancy bits with one warp reduction; only a block that runs past the end of its warp is
+  // finished row by row by the thread of its first row.
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const bool in = i < n;
+  const uint64_t k = in ? keys[i] : 0ull;
+  const uint64_t bkey = in ? k >> (shift + 6) : kEmptyKey;     // rows past the end form a group of their own
+  const unsigned peers = __match_any_sync(0xffffffffu, bkey);
+  const uint32_t idx = (uint32_t)((k >> shift) & 63ull);
+  const uint32_t lo = __reduce_or_sync(peers, idx < 32u ? 1u << idx : 0u);
+  const uint32_t hi = __reduce_or_sync(peers, idx >= 32u ? 1u << (idx - 32u) : 0u);
+  if (!in || lane != __ffs(peers) - 1) return;                 // one lane per group goes on
+  if (lane == 0 && i > 0 && (keys[i - 1] >> (shift + 6)) == bkey) return;   // the block started in the previous warp
+  uint64_t mask = (uint64_t)lo | ((uint64_t)hi << 32);
+  if (peers >> 31) {                                           // the group reaches the end of the warp: walk on
+    for (int64_t j = i + __popc(peers); j < n && j < i + 64; ++j) {
+      const uint64_t kj = keys[j];
+      if ((kj >> (shift + 6)) != bkey) break;
+      mask |= 1ull << ((kj >> shift) & 63ull);
+    }
   }
   uint64_t base = hash_key(bkey) & cap_mask & ~(uint64_t)(kWin - 1);
   for (uint64_t probes = 0; probes <= cap_mask; probes += kWin) {
