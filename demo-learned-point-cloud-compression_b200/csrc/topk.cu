@@ -83,18 +83,44 @@ k_sel_pass(const float* __restrict__ logits, const int32_t* __restrict__ frame_o
   sh[threadIdx.x] = __ldcg(&hist[b * 256 + threadIdx.x]);
   hist[b * 256 + threadIdx.x] = 0;
   __syncthreads();
-  if (threadIdx.x == 0) {
-    int32_t kleft = st[b].kleft;
-    uint32_t cum = 0;
-    int d = 255;
-    for (; d > 0; --d) {
-      if ((int64_t)cum + sh[d] >= (int64_t)kleft) break;
-      cum += sh[d];
+  // Pick the digit: walking down from 255, the first d > 0 with (rows in digits above d) + sh[d] >= kleft, else 0.
+  // Warp 0 does the walk in parallel: lane L owns digits 255 - 8 L ... 248 - 8 L, a shuffle scan gives the rows above
+  // its range, the lowest lane that finds a hit wins.
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+    const int32_t kleft = st[b].kleft;
+    const int top = 255 - 8 * lane;
+    uint32_t loc[8];
+    uint32_t sum = 0;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      loc[e] = sh[top - e];
+      sum += loc[e];
     }
-    // d == 0 also catches k larger than the frame: everything down to the smallest digit is taken
-    st[b].prefix = prefix | ((uint32_t)d << shift);
-    st[b].kleft = kleft - (int32_t)cum;
-    st[b].done = 0;
+    uint32_t incl = sum;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, incl, off);
+      if (lane >= off) incl += v;
+    }
+    uint32_t cum = incl - sum;      // rows in the digits above this lane's range
+    int d = -1;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      if (d < 0) {
+        if (top - e > 0 && (int64_t)cum + loc[e] >= (int64_t)kleft) d = top - e;
+        else if (top - e > 0) cum += loc[e];
+      }
+    }
+    const unsigned hit = __ballot_sync(0xffffffffu, d >= 0);
+    // no hit: d = 0 (also catches k larger than the frame: everything down to the smallest digit is taken) and
+    // cum = rows in digits 255 ... 1, which is what lane 31 has accumulated
+    const int win = hit ? __ffs(hit) - 1 : 31;
+    if (lane == win) {
+      st[b].prefix = prefix | ((uint32_t)(d >= 0 ? d : 0) << shift);
+      st[b].kleft = kleft - (int32_t)cum;
+      st[b].done = 0;
+    }
   }
 }
 
