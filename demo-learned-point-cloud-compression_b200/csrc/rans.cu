@@ -299,7 +299,14 @@ k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, in
   if (SMEM) {
     for (int t = threadIdx.x; t < T.T; t += blockDim.x)
       s_meta[t] = make_int4(T.off[t], T.size[t] - 2, T.offset[t], 0);
-    for (int i = threadIdx.x; i < T.T * (kLutN + 1); i += blockDim.x) s_lut[i] = T.lut[i];
+    {   // search windows: 16-byte copies (the 2-byte loop was 8 % of the kernel's time)
+      const int nl = T.T * (kLutN + 1);
+      const int nv = (reinterpret_cast<uintptr_t>(T.lut) & 15) == 0 ? nl >> 3 : 0;
+      const uint4* l4 = reinterpret_cast<const uint4*>(T.lut);
+      uint4* sl4 = reinterpret_cast<uint4*>(s_lut);
+      for (int i = threadIdx.x; i < nv; i += blockDim.x) sl4[i] = __ldg(l4 + i);
+      for (int i = (nv << 3) + threadIdx.x; i < nl; i += blockDim.x) s_lut[i] = T.lut[i];
+    }
     // four entries per 16-byte load, batches of four independent loads in flight per thread
     const uint4* c4 = reinterpret_cast<const uint4*>(T.cdf);
     uint2* s4 = reinterpret_cast<uint2*>(s_cdf);
@@ -359,6 +366,14 @@ k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, in
   bool bad = false;
   // table index of each round, prefetched kChunk rounds ahead (double buffered in registers)
   int32_t cur[kChunk], nxt[kChunk];
+  // Without an index array the table of symbol i is its channel i / chan_len: the quotient is carried from round
+  // to round (a 64-bit division per round would sit in the one instruction stream the warp's time consists of).
+  // load_chunk is called for consecutive chunks, so the pair always belongs to the next round to be loaded.
+  int64_t ch_q = 0, ch_r = 0;
+  if (!idx) {
+    ch_q = (start + lane) / chan_len;
+    ch_r = (start + lane) - ch_q * chan_len;
+  }
   auto load_chunk = [&](int32_t r0, int32_t (&buf)[kChunk]) {   // rounds r0 ... r0+kChunk-1
 #pragma unroll
     for (int k = 0; k < kChunk; ++k) {
@@ -367,7 +382,14 @@ k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, in
       int32_t t = -1;
       if (r0 + k < rounds && li < cnt) {
         const int64_t i = start + li;
-        t = idx ? (int32_t)__ldg(idx + i) : (int32_t)(i / chan_len);
+        t = idx ? (int32_t)__ldg(idx + i) : (int32_t)ch_q;
+      }
+      if (!idx) {
+        ch_r += 32;
+        while (ch_r >= chan_len) {
+          ch_r -= chan_len;
+          ++ch_q;
+        }
       }
       buf[k] = t;
     }
