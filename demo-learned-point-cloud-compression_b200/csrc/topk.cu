@@ -3,8 +3,9 @@
 // Radix select instead of a sort: four 8-bit passes over the order-preserving integer image of the
 // logits find, per frame, the value T of the k-th largest logit and the number r of rows equal to T
 // that still belong to the top k; a row is kept iff logit > T, or logit == T and fewer than r equal
-// rows precede it in its frame (exclusive scan of the tie indicator).  The kept rows leave through an
-// order-preserving compaction.  Every pass reads 4 bytes per candidate; nothing is sorted.
+// rows precede it in its frame.  One 64-bit inclusive scan of (above | tied << 32) marks counts both kinds of
+// rows, so every kept row knows its output position and is written in order without a separate compaction.
+// Every pass reads 4 bytes per candidate; nothing is sorted.
 #include "common.cuh"
 #include <cub/cub.cuh>
 
@@ -124,10 +125,11 @@ k_sel_pass(const float* __restrict__ logits, const int32_t* __restrict__ frame_o
   }
 }
 
-// tie[i] = logit image equals the frame's threshold
+// mark[i] = (logit above the frame's threshold) | (logit equal to it) << 32: one 64-bit inclusive scan then ranks
+// both kinds of rows at once
 __global__ void __launch_bounds__(kSelThreads)
-k_sel_ties(const float* __restrict__ logits, const int32_t* __restrict__ frame_off, const SelState* __restrict__ st,
-           int32_t* __restrict__ tie) {
+k_sel_mark(const float* __restrict__ logits, const int32_t* __restrict__ frame_off, const SelState* __restrict__ st,
+           uint64_t* __restrict__ mark) {
   pdl_trigger();
   pdl_wait();
   const int b = blockIdx.y;
@@ -135,31 +137,62 @@ k_sel_ties(const float* __restrict__ logits, const int32_t* __restrict__ frame_o
   const uint32_t T = st[b].prefix;
   const int base = r0 + blockIdx.x * kSelChunk;
   if (base >= r1) return;
-#pragma unroll
-  for (int e = 0; e < kSelPerThread; ++e) {
-    const int i = base + e * kSelThreads + threadIdx.x;
-    if (i < r1) tie[i] = orderable(__ldg(logits + i)) == T;
-  }
-}
-
-__global__ void __launch_bounds__(kSelThreads)
-k_sel_flags(const float* __restrict__ logits, const int32_t* __restrict__ frame_off, const SelState* __restrict__ st,
-            const int32_t* __restrict__ tie_scan, uint8_t* __restrict__ flags) {
-  pdl_trigger();
-  pdl_wait();
-  const int b = blockIdx.y;
-  const int r0 = frame_off[b], r1 = frame_off[b + 1];
-  const int base = r0 + blockIdx.x * kSelChunk;
-  if (base >= r1) return;
-  const uint32_t T = st[b].prefix;
-  const int32_t r = st[b].kleft;
-  const int32_t t0 = tie_scan[r0];
 #pragma unroll
   for (int e = 0; e < kSelPerThread; ++e) {
     const int i = base + e * kSelThreads + threadIdx.x;
     if (i < r1) {
       const uint32_t u = orderable(__ldg(logits + i));
-      flags[i] = (uint8_t)(u > T || (u == T && tie_scan[i] - t0 < r));
+      mark[i] = u > T ? 1ull : (u == T ? (1ull << 32) : 0ull);
+    }
+  }
+}
+
+// Kept rows of frame b: every row above the threshold and the first kleft rows equal to it.  A kept row lands
+// behind the kept rows of the earlier frames, the rows above the threshold that precede it in its frame and the
+// (at most kleft) tied rows that precede it.  Block (0, last frame) also writes the total.
+__global__ void __launch_bounds__(kSelThreads)
+k_sel_emit(const int32_t* __restrict__ frame_off, const SelState* __restrict__ st, const uint64_t* __restrict__ scan,
+           int nf, int32_t* __restrict__ keep_row, int32_t* __restrict__ n_keep) {
+  pdl_trigger();
+  pdl_wait();
+  __shared__ int64_t s_before;     // kept rows of the frames before b
+  const int b = blockIdx.y;
+  const int r0 = frame_off[b], r1 = frame_off[b + 1];
+  const int base = r0 + blockIdx.x * kSelChunk;
+  const bool totals = blockIdx.x == 0 && b == nf - 1;
+  if (base >= r1 && !totals) return;
+  if (threadIdx.x == 0) {
+    int64_t before = 0, total = 0;
+    const int upto = totals ? nf : b;
+    for (int f = 0; f < upto; ++f) {
+      const int f0 = frame_off[f], f1 = frame_off[f + 1];
+      if (f1 <= f0) continue;
+      const uint64_t lo = f0 ? scan[f0 - 1] : 0ull, hi = scan[f1 - 1];
+      const int64_t above = (int64_t)((hi & 0xffffffffu) - (lo & 0xffffffffu));
+      const int64_t eq = (int64_t)((hi >> 32) - (lo >> 32));
+      const int64_t r = st[f].kleft;
+      const int64_t kept = above + (eq < r ? eq : r);
+      if (f < b) before += kept;
+      total += kept;
+    }
+    if (totals) *n_keep = (int32_t)total;
+    s_before = before;
+  }
+  __syncthreads();
+  if (base >= r1) return;
+  const int64_t before = s_before;
+  const uint64_t s0 = r0 ? scan[r0 - 1] : 0ull;
+  const int64_t a0 = (int64_t)(s0 & 0xffffffffu), e0 = (int64_t)(s0 >> 32);
+  const int64_t r = st[b].kleft;
+#pragma unroll
+  for (int e = 0; e < kSelPerThread; ++e) {
+    const int i = base + e * kSelThreads + threadIdx.x;
+    if (i < r1) {
+      const uint64_t incl = scan[i], prev = i ? scan[i - 1] : 0ull;
+      const int64_t a_prev = (int64_t)(prev & 0xffffffffu) - a0, e_prev = (int64_t)(prev >> 32) - e0;
+      const bool is_above = (incl & 0xffffffffu) != (prev & 0xffffffffu);
+      const bool is_eq = (incl >> 32) != (prev >> 32);
+      if (is_above || (is_eq && e_prev < r)) keep_row[before + a_prev + (e_prev < r ? e_prev : r)] = i;
     }
   }
 }
@@ -172,13 +205,7 @@ constexpr int64_t kMaxFrames = 4096;   // frames per call (a GOP holds a handful
 
 static size_t scan_bytes(int64_t n) {
   size_t b = 0;
-  cub::DeviceScan::ExclusiveSum(nullptr, b, (const int32_t*)nullptr, (int32_t*)nullptr, (int)n);
-  return b;
-}
-static size_t select_bytes(int64_t n) {
-  size_t b = 0;
-  cub::DeviceSelect::Flagged(nullptr, b, cub::CountingInputIterator<int32_t>(0), (const uint8_t*)nullptr,
-                             (int32_t*)nullptr, (int32_t*)nullptr, (int)n);
+  cub::DeviceScan::InclusiveSum(nullptr, b, (const uint64_t*)nullptr, (uint64_t*)nullptr, (int)n);
   return b;
 }
 
@@ -186,8 +213,7 @@ extern "C" {
 
 int64_t pcc_topk_workspace_bytes(int64_t n) {
   if (n <= 0) return 256;
-  return 2 * align_up(n * 4, 256) + align_up(n, 256) + align_up((int64_t)scan_bytes(n), 256) +
-         align_up((int64_t)select_bytes(n), 256) + align_up(kMaxFrames * (16 + 1024), 256) + 2 * 256;
+  return align_up(n * 8, 256) + align_up((int64_t)scan_bytes(n), 256) + align_up(kMaxFrames * (16 + 1024), 256) + 2 * 256;
 }
 
 int pcc_topk_select(const float* logits, const uint64_t* keys, int64_t n,
@@ -211,21 +237,17 @@ int pcc_topk_select(const float* logits, const uint64_t* keys, int64_t n,
     left -= b;
     return r;
   };
-  int32_t* tie = (int32_t*)take(n * 4);
-  int32_t* tie_scan = (int32_t*)take(n * 4);
-  uint8_t* flags = (uint8_t*)take(n);
-  size_t sb = scan_bytes(n), fb = select_bytes(n);
+  uint64_t* mark = (uint64_t*)take(n * 8);
+  size_t sb = scan_bytes(n);
   void* sws = take((int64_t)sb);
-  void* fws = take((int64_t)fb);
   SelState* state = (SelState*)take((int64_t)num_frames * sizeof(SelState));
   uint32_t* hist = (uint32_t*)take((int64_t)num_frames * 1024);
-  if (!tie || !tie_scan || !flags || !sws || !fws || !state || !hist) {
+  if (!mark || !sws || !state || !hist) {
     set_error("pcc_topk_select: workspace too small");
     return PCC_E_WORKSPACE;
   }
   // rows of frames >= num_frames (none in a well-formed batch) are dropped
-  PCC_CUDA(cudaMemsetAsync(flags, 0, (size_t)n, st));
-  PCC_CUDA(cudaMemsetAsync(tie, 0, (size_t)n * 4, st));
+  PCC_CUDA(cudaMemsetAsync(mark, 0, (size_t)n * 8, st));
   const dim3 grid((unsigned)((n + kSelChunk - 1) / kSelChunk), (unsigned)num_frames);
   launch_pdl(k_sel_init, dim3((unsigned)num_frames), dim3(256), 0, st, k, num_frames, state, hist);
   PCC_LAUNCHED();
@@ -233,15 +255,12 @@ int pcc_topk_select(const float* logits, const uint64_t* keys, int64_t n,
     launch_pdl(k_sel_pass, dim3(grid), dim3(kSelThreads), 0, st, logits, frame_offsets, shift, state, hist);
     PCC_LAUNCHED();
   }
-  launch_pdl(k_sel_ties, dim3(grid), dim3(kSelThreads), 0, st, logits, frame_offsets, state, tie);
+  launch_pdl(k_sel_mark, dim3(grid), dim3(kSelThreads), 0, st, logits, frame_offsets, state, mark);
   PCC_LAUNCHED();
-  PCC_CUDA(cub::DeviceScan::ExclusiveSum(sws, sb, tie, tie_scan, (int)n, st));
+  PCC_CUDA(cub::DeviceScan::InclusiveSum(sws, sb, mark, mark, (int)n, st));
   g_launches.fetch_add(1);
-  launch_pdl(k_sel_flags, dim3(grid), dim3(kSelThreads), 0, st, logits, frame_offsets, state, tie_scan, flags);
+  launch_pdl(k_sel_emit, dim3(grid), dim3(kSelThreads), 0, st, frame_offsets, state, mark, num_frames, keep_row, n_keep_dev);
   PCC_LAUNCHED();
-  PCC_CUDA(cub::DeviceSelect::Flagged(fws, fb, cub::CountingInputIterator<int32_t>(0), flags, keep_row,
-                                      n_keep_dev, (int)n, st));
-  g_launches.fetch_add(1);
   return PCC_OK;
 }
 

@@ -229,8 +229,9 @@ int pcc_gather_keys(const uint64_t* src, const int32_t* src_row, int64_t n_out, 
 /* Per-frame top-k occupancy selection + pruning (torch.topk + MinkowskiPruning inside
  * g_s(y_hat, k=ks), codec_parallel.py:469).  Keeps, in frame b, the k[b] rows with the largest
  * logits; ties -> lower row (= lower key); NaN ranks last.  keep_row = kept rows ascending,
- * n_keep_dev = count.  Radix select (four 8-bit histogram passes per frame) + tie scan +
- * order-preserving compaction; num_frames <= 4096.  `keys` is only used to document the row order. */
+ * n_keep_dev = count.  Radix select (four 8-bit histogram passes per frame), then one 64-bit scan of
+ * (above threshold | tied << 32) marks gives every kept row its output position; num_frames <= 4096.
+ * `keys` is only used to document the row order. */
 int64_t pcc_topk_workspace_bytes(int64_t n);
 int pcc_topk_select(const float* logits, const uint64_t* keys, int64_t n,
                     const int32_t* frame_offsets, const int32_t* k, int32_t num_frames,
