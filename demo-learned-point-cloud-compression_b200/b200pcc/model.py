@@ -603,42 +603,45 @@ class EntropyBottleneck(_CodedModel):
         self.factors = [np.asarray(sd[f"{prefix}factors.{i}"], np.float32) for i in range(n - 1)]
         self.quantiles = np.asarray(sd[f"{prefix}quantiles"], np.float32)
 
-    @staticmethod
-    def _softplus(x):
-        return np.maximum(x, 0) + np.log1p(np.exp(-np.abs(x)))
-
-    def _logits_cumulative(self, x):
+    def _logits_cumulative(self, x: torch.Tensor) -> torch.Tensor:
+        """CompressAI 1.2.4 EntropyBottleneck._logits_cumulative on float32 CPU tensors, op for op
+        (softplus(matrix) @ logits, += bias, += tanh(factor) * tanh(logits)); SURVEY App. A.3."""
         logits = x
         for i in range(len(self.matrices)):
-            logits = np.matmul(self._softplus(self.matrices[i].astype(np.float64)), logits) + \
-                self.biases[i].astype(np.float64)
+            m = torch.from_numpy(self.matrices[i])
+            logits = torch.matmul(torch.nn.functional.softplus(m), logits)
+            logits = logits + torch.from_numpy(self.biases[i])
             if i < len(self.factors):
-                logits = logits + np.tanh(self.factors[i].astype(np.float64)) * np.tanh(logits)
+                logits = logits + torch.tanh(torch.from_numpy(self.factors[i])) * torch.tanh(logits)
         return logits
 
-    def update(self, device, force=True):
-        q = self.quantiles.astype(np.float64)
+    def factorized_pmf_f32(self):
+        """The pmf rows EntropyBottleneck.update(force=True) hands to pmf_to_quantized_cdf: float32 torch
+        arithmetic in CompressAI's order -> (list of float32 rows incl. the tail entry, minima, medians)."""
+        q = torch.from_numpy(self.quantiles)
         medians = q[:, 0, 1]
-        minima = np.maximum(np.ceil(medians - q[:, 0, 0]), 0).astype(np.int64)
-        maxima = np.maximum(np.ceil(q[:, 0, 2] - medians), 0).astype(np.int64)
+        minima = torch.clamp(torch.ceil(medians - q[:, 0, 0]).int(), min=0)
+        maxima = torch.clamp(torch.ceil(q[:, 0, 2] - medians).int(), min=0)
         pmf_start = medians - minima
         pmf_length = maxima + minima + 1
         max_length = int(pmf_length.max())
-        samples = np.arange(max_length, dtype=np.float64)[None, None, :] + pmf_start[:, None, None]
+        samples = torch.arange(max_length)[None, :] + pmf_start[:, None, None]
         lower = self._logits_cumulative(samples - 0.5)
         upper = self._logits_cumulative(samples + 0.5)
-        sign = -np.sign(lower + upper)
-        sig = lambda v: 1.0 / (1.0 + np.exp(-v))
-        pmf = np.abs(sig(sign * upper) - sig(sign * lower))[:, 0, :]
-        tail = sig(lower[:, 0, :1]) + sig(-upper[:, 0, -1:])
-        rows = []
-        for c in range(self.channels):
-            L = int(pmf_length[c])
-            rows.append(ops.pmf_to_quantized_cdf(np.concatenate([pmf[c, :L], tail[c]]).astype(np.float32)))
+        sign = -torch.sign(lower + upper)
+        pmf = torch.abs(torch.sigmoid(sign * upper) - torch.sigmoid(sign * lower))[:, 0, :]
+        tail = torch.sigmoid(lower[:, 0, :1]) + torch.sigmoid(-upper[:, 0, -1:])
+        rows = [torch.cat((pmf[c, :int(pmf_length[c])], tail[c])).numpy().astype(np.float32)
+                for c in range(self.channels)]
+        return rows, minima.numpy().astype(np.int64), pmf_length.numpy().astype(np.int64), medians.numpy()
+
+    def update(self, device, force=True):
+        prows, minima, pmf_length, medians = self.factorized_pmf_f32()
+        rows = [ops.pmf_to_quantized_cdf(r) for r in prows]
         self._quantized_cdf = rows
         self._cdf_length = (pmf_length + 2).astype(np.int32)
         self._offset = (-minima).astype(np.int32)
-        self.medians = medians.astype(np.float32)
+        self.medians = np.asarray(medians, np.float32)
         self.device = device
         self.tables = ops.DeviceCdfTables(rows, self._offset, device)
         self.medians_d = torch.from_numpy(self.medians).to(device)
@@ -687,21 +690,34 @@ class GaussianConditional(_CodedModel):
             np.float32)
         self.device = None
 
-    def update(self, device):
-        from scipy.special import erfc, ndtri
-        t64 = self.scale_table.astype(np.float64)
-        multiplier = -ndtri(TAIL_MASS / 2)
-        pmf_center = np.ceil(t64 * multiplier).astype(np.int64)
+    def gaussian_pmf_f32(self):
+        """The pmf rows GaussianConditional.update() hands to pmf_to_quantized_cdf, computed as CompressAI 1.2.4
+        does: float32 torch tensors throughout (scale table, |arange - centre|, (0.5 - s) / sigma, erfc), only the
+        tail-mass quantile is a Python double (scipy.stats.norm.ppf there, ndtri here: the same function).
+        -> (list of float32 rows incl. the tail entry, pmf_center int64)."""
+        from scipy.special import ndtri
+        t = torch.from_numpy(self.scale_table)
+        multiplier = -float(ndtri(TAIL_MASS / 2))
+        pmf_center = torch.ceil(t * multiplier).int()
         pmf_length = 2 * pmf_center + 1
-        phi = lambda x: 0.5 * erfc(-x / math.sqrt(2.0))
-        rows = []
-        for i, s in enumerate(t64):
-            samples = np.abs(np.arange(pmf_length[i]) - pmf_center[i]).astype(np.float64)
-            upper = phi((0.5 - samples) / s)
-            lower = phi((-0.5 - samples) / s)
-            pmf = upper - lower
-            tail = 2.0 * lower[:1]
-            rows.append(ops.pmf_to_quantized_cdf(np.concatenate([pmf, tail]).astype(np.float32)))
+        max_length = int(pmf_length.max())
+        samples = torch.abs(torch.arange(max_length).int() - pmf_center[:, None]).float()
+        scale = t.unsqueeze(1).float()
+
+        def cumulative(x):      # _standardized_cumulative: 0.5 * erfc(-(2 ** -0.5) * x)
+            return 0.5 * torch.erfc(float(-(2 ** -0.5)) * x)
+        upper = cumulative((0.5 - samples) / scale)
+        lower = cumulative((-0.5 - samples) / scale)
+        pmf = upper - lower
+        tail = 2 * lower[:, :1]
+        rows = [torch.cat((pmf[i, :int(pmf_length[i])], tail[i])).numpy().astype(np.float32)
+                for i in range(t.shape[0])]
+        return rows, pmf_center.numpy().astype(np.int64)
+
+    def update(self, device):
+        prows, pmf_center = self.gaussian_pmf_f32()
+        pmf_length = 2 * pmf_center + 1
+        rows = [ops.pmf_to_quantized_cdf(r) for r in prows]
         self._quantized_cdf = rows
         self._cdf_length = (pmf_length + 2).astype(np.int32)
         self._offset = (-pmf_center).astype(np.int32)

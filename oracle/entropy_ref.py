@@ -57,22 +57,37 @@ def scale_table():
     return t.astype(np.float32)
 
 
-def gaussian_tables(table=None):
-    """GaussianConditional.update(): list of cdf rows (ragged), cdf_length, offset."""
+def gaussian_pmf(table=None, dtype=np.float32):
+    """The pmf rows (tail entry last) GaussianConditional.update() quantises, and pmf_center.
+
+    CompressAI 1.2.4 evaluates this on float32 tensors (the scale table is a float32 tensor; `samples.float()`,
+    `samples_scale.float()`, torch.erfc in float32); only the quantile multiplier is a Python double.  dtype =
+    np.float32 restates exactly that with numpy float32 arithmetic and scipy's erfc (an independent erfc: the
+    product uses torch's); dtype = np.float64 is the "mathematically exact" variant, kept to MEASURE what the
+    float32 convention changes (tests/test_cpu_oracle.py::test_gaussian_tables_float32_vs_float64)."""
     table = scale_table() if table is None else np.asarray(table, dtype=np.float32)
-    t64 = table.astype(np.float64)
-    multiplier = -ndtri(TAIL_MASS / 2)
-    pmf_center = np.ceil(t64 * multiplier).astype(np.int64)
+    t = table.astype(dtype)
+    multiplier = dtype(-ndtri(TAIL_MASS / 2))
+    pmf_center = np.ceil(t * multiplier).astype(np.int64)
     pmf_length = 2 * pmf_center + 1
+    half, const = dtype(0.5), dtype(-(2 ** -0.5))
     rows = []
-    for i, s in enumerate(t64):
-        samples = np.abs(np.arange(pmf_length[i]) - pmf_center[i]).astype(np.float64)
-        upper = _phi((0.5 - samples) / s)
-        lower = _phi((-0.5 - samples) / s)
+    for i, s in enumerate(t):
+        samples = np.abs(np.arange(pmf_length[i]) - pmf_center[i]).astype(dtype)
+        upper = half * erfc(const * ((half - samples) / s))
+        lower = half * erfc(const * ((-half - samples) / s))
+        assert upper.dtype == dtype
         pmf = upper - lower
-        tail = 2.0 * lower[:1]
-        rows.append(pmf_to_quantized_cdf(np.concatenate([pmf, tail])))
-    return rows, (pmf_length + 2).astype(np.int32), (-pmf_center).astype(np.int32)
+        tail = dtype(2) * lower[:1]
+        rows.append(np.concatenate([pmf, tail]).astype(np.float32))
+    return rows, pmf_center
+
+
+def gaussian_tables(table=None, dtype=np.float32):
+    """GaussianConditional.update(): list of cdf rows (ragged), cdf_length, offset."""
+    prows, pmf_center = gaussian_pmf(table, dtype)
+    rows = [pmf_to_quantized_cdf(r) for r in prows]
+    return rows, (2 * pmf_center + 3).astype(np.int32), (-pmf_center).astype(np.int32)
 
 
 def lower_bound_scale(s):
@@ -152,37 +167,47 @@ def _softplus(x):
     return np.maximum(x, 0) + np.log1p(np.exp(-np.abs(x)))
 
 
-def eb_logits_cumulative(x, matrices, biases, factors):
-    """x [C,1,N] float64."""
-    logits = x
+def _sigmoid(v):
+    with np.errstate(over="ignore"):
+        return (1 / (1 + np.exp(-v))).astype(v.dtype)
+
+
+def eb_logits_cumulative(x, matrices, biases, factors, dtype=np.float32):
+    """x [C,1,N]; EntropyBottleneck._logits_cumulative in `dtype` arithmetic (CompressAI: float32)."""
+    logits = x.astype(dtype)
     for i in range(len(matrices)):
-        logits = np.matmul(_softplus(matrices[i].astype(np.float64)), logits) + biases[i].astype(np.float64)
+        logits = np.matmul(_softplus(matrices[i].astype(dtype)), logits) + biases[i].astype(dtype)
         if i < len(factors):
-            logits = logits + np.tanh(factors[i].astype(np.float64)) * np.tanh(logits)
+            logits = logits + np.tanh(factors[i].astype(dtype)) * np.tanh(logits)
     return logits
 
 
-def eb_tables(matrices, biases, factors, quantiles):
-    """EntropyBottleneck.update(force=True) -> (cdf rows, cdf_length, offset, medians)."""
-    q = np.asarray(quantiles, dtype=np.float64)
+def eb_pmf(matrices, biases, factors, quantiles, dtype=np.float32):
+    """The pmf rows (tail entry last) EntropyBottleneck.update(force=True) quantises.  float32 like CompressAI
+    (parameters and samples are float32 tensors); float64 kept as the measuring stick."""
+    q = np.asarray(quantiles, dtype=np.float32).astype(dtype)
     medians = q[:, 0, 1]
     minima = np.maximum(np.ceil(medians - q[:, 0, 0]), 0).astype(np.int64)
     maxima = np.maximum(np.ceil(q[:, 0, 2] - medians), 0).astype(np.int64)
-    pmf_start = medians - minima
+    pmf_start = medians - minima.astype(dtype)
     pmf_length = maxima + minima + 1
     max_length = int(pmf_length.max())
-    samples = np.arange(max_length, dtype=np.float64)[None, None, :] + pmf_start[:, None, None]
-    lower = eb_logits_cumulative(samples - 0.5, matrices, biases, factors)
-    upper = eb_logits_cumulative(samples + 0.5, matrices, biases, factors)
+    samples = np.arange(max_length).astype(dtype)[None, None, :] + pmf_start[:, None, None]
+    half = dtype(0.5)
+    lower = eb_logits_cumulative(samples - half, matrices, biases, factors, dtype)
+    upper = eb_logits_cumulative(samples + half, matrices, biases, factors, dtype)
     sign = -np.sign(lower + upper)
-    sig = lambda v: 1.0 / (1.0 + np.exp(-v))
-    pmf = np.abs(sig(sign * upper) - sig(sign * lower))[:, 0, :]
-    tail = (sig(lower[:, 0, :1]) + sig(-upper[:, 0, -1:]))
-    rows = []
-    for c in range(pmf.shape[0]):
-        L = int(pmf_length[c])
-        rows.append(pmf_to_quantized_cdf(np.concatenate([pmf[c, :L], tail[c]])))
-    return rows, (pmf_length + 2).astype(np.int32), (-minima).astype(np.int32), medians.astype(np.float32)
+    pmf = np.abs(_sigmoid(sign * upper) - _sigmoid(sign * lower))[:, 0, :]
+    tail = _sigmoid(lower[:, 0, :1]) + _sigmoid(-upper[:, 0, -1:])
+    rows = [np.concatenate([pmf[c, :int(pmf_length[c])], tail[c]]).astype(np.float32) for c in range(pmf.shape[0])]
+    return rows, minima, pmf_length, medians.astype(np.float32)
+
+
+def eb_tables(matrices, biases, factors, quantiles, dtype=np.float32):
+    """EntropyBottleneck.update(force=True) -> (cdf rows, cdf_length, offset, medians)."""
+    prows, minima, pmf_length, medians = eb_pmf(matrices, biases, factors, quantiles, dtype)
+    rows = [pmf_to_quantized_cdf(r) for r in prows]
+    return rows, (pmf_length + 2).astype(np.int32), (-minima).astype(np.int32), medians
 
 
 def factorized_quantize(z, medians):

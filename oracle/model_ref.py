@@ -91,23 +91,38 @@ class RefModel:
         params = self._conv("entropy_model.h_s.head", F, None, store=False)
         return C, params
 
+    def g_s_pre(self, y_hat):
+        """g_s's 1x1 input convolution on y_hat [Ny, Cy] (rows in any order: no neighbours involved)."""
+        return self._conv("g_s.pre", self._store(np.asarray(y_hat, np.float32)), None, relu=True)
+
+    def g_s_stage(self, i, C, F, stride):
+        """Up-stage i of g_s on GIVEN inputs (coordinates at tensor stride `stride`, their features):
+        generative up-convolution, residual blocks, occupancy logits on the un-pruned candidates.
+        -> (C_children at stride/2, F [n, c], logits [n, 1]).  Stage-wise parity tests feed the product's
+        kept rows of stage i-1 here (codec_parallel.py:469 runs all three inside g_s)."""
+        C, F = self._up(f"g_s.up{i}", C, F, stride, relu=True)
+        stride //= 2
+        for b in range(self.cfg["blocks"]):
+            F = self._block(f"g_s.block{i}_{b}", C, F, stride)
+        logits = self._conv(f"g_s.occ{i}", F, self._k3(C, stride), store=False)
+        return C, F, logits
+
+    def g_s_color(self, C, F):
+        """Colour head on the final (stride-1) coordinates: fp32 [n, 3], before pack_batches' clip."""
+        return self._conv("g_s.color", F, self._k3(C, 1), store=False)
+
     def g_s(self, C, y_hat, ks, return_intermediates=False):
-        cfg = self.cfg
-        F = self._store(np.asarray(y_hat, np.float32))
-        F = self._conv("g_s.pre", F, None, relu=True)
+        F = self.g_s_pre(y_hat)
         stride = 8
         inter = []
         for i in range(3):
-            C, F = self._up(f"g_s.up{i}", C, F, stride, relu=True)
+            C, F, logits = self.g_s_stage(i, C, F, stride)
             stride //= 2
-            for b in range(cfg["blocks"]):
-                F = self._block(f"g_s.block{i}_{b}", C, F, stride)
-            logits = self._conv(f"g_s.occ{i}", F, self._k3(C, stride), store=False)
             keep = S.topk_mask(logits[:, 0], C, ks[i])
             if return_intermediates:
                 inter.append({"C": C, "F": F, "logits": logits, "keep": keep})
             C, F = C[keep], F[keep]
-        colors = self._conv("g_s.color", F, self._k3(C, 1), store=False)
+        colors = self.g_s_color(C, F)
         if return_intermediates:
             return C, colors, inter
         return C, colors

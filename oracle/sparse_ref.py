@@ -5,7 +5,43 @@ SURVEY.md Appendix A.2, each isolated in one named function so it can be re-poin
 every coordinate set is the reference's canonical order (shared/utils.py:116-141 `sort_tensor`):
 ascending (b, x, y, z).
 """
+import ctypes as _C
+import os as _os
+
 import numpy as np
+
+# ---- optional C core (sparse_ref.c): same definitions, OpenMP; selected with use_fast(True) ---------------
+_FAST = False
+_fastlib = None
+
+
+def _fast():
+    global _fastlib
+    if _fastlib is None:
+        here = _os.path.dirname(_os.path.abspath(__file__))
+        so = _os.path.join(here, "_build", "libsparse_ref.so")
+        if not _os.path.exists(so):
+            import subprocess
+            subprocess.check_call(["make", "-C", here], stdout=subprocess.DEVNULL)
+        _fastlib = _C.CDLL(so)
+        _fastlib.ref_count_pairs.restype = _C.c_int64
+    return _fastlib
+
+
+def use_fast(on=True):
+    """Route kernel_map / conv_forward through the C core (full-size frames); returns the previous setting."""
+    global _FAST
+    prev, _FAST = _FAST, bool(on)
+    return prev
+
+
+def fast_threads():
+    import multiprocessing
+    return int(_os.environ.get("OMP_NUM_THREADS", 0) or multiprocessing.cpu_count())
+
+
+def _p(a):
+    return a.ctypes.data_as(_C.c_void_p)
 
 
 # ---- canonical order ----------------------------------------------------------------------------
@@ -92,6 +128,15 @@ def lookup_rows(C_src, C_query):
 def kernel_map(C_in, C_out, offsets, transposed=False):
     """nbr[j, o] = row i of C_in with  C_in[i] = C_out[o] + d_j  (forward conv)  or
     C_in[i] = C_out[o] - d_j  (transposed conv: out[f] += in[c] W[j] where f = c + d_j)."""
+    if _FAST and len(C_out):
+        ks = lex_key(C_in)
+        if len(ks) < 2 or bool(np.all(ks[1:] > ks[:-1])):      # canonical order (every caller's case)
+            co = np.ascontiguousarray(C_out, dtype=np.int32)
+            offs = np.ascontiguousarray(offsets, dtype=np.int64)
+            nbr = np.empty((len(offs), len(co)), dtype=np.int64)
+            _fast().ref_kernel_map(_p(ks), _C.c_int64(len(ks)), _p(co), _C.c_int64(len(co)), _p(offs),
+                                   _C.c_int32(len(offs)), _C.c_int32(-1 if transposed else 1), _p(nbr))
+            return nbr
     C_out = np.asarray(C_out, dtype=np.int64)
     nbr = np.full((len(offsets), len(C_out)), -1, dtype=np.int64)
     for j, d in enumerate(offsets):
@@ -124,11 +169,14 @@ def generative_coords(C, out_stride):
 def bf16_round(a):
     """Round float32 values to the nearest bfloat16 (ties to even); result stays float32."""
     a = np.ascontiguousarray(a, dtype=np.float32)
-    u = a.view(np.uint32).astype(np.uint64)
-    lsb = (u >> np.uint64(16)) & np.uint64(1)
-    u = (u + np.uint64(0x7FFF) + lsb) & np.uint64(0xFFFF0000)
-    out = u.astype(np.uint32).view(np.float32).reshape(a.shape)
-    return np.where(np.isfinite(a), out, a)
+    if _FAST and a.size:
+        out = np.empty_like(a)
+        _fast().ref_bf16_round(_p(a), _C.c_int64(a.size), _p(out))
+        return out
+    u = a.view(np.uint32)
+    r = (u + np.uint32(0x7FFF) + ((u >> np.uint32(16)) & np.uint32(1))) & np.uint32(0xFFFF0000)   # wraps never: finite max -> inf
+    finite = (u & np.uint32(0x7F800000)) != np.uint32(0x7F800000)
+    return np.where(finite, r, u).view(np.float32).reshape(a.shape)
 
 
 def conv_forward(F_in, nbr, W, bias=None, residual=None, relu=False, bf16=False):
@@ -141,6 +189,19 @@ def conv_forward(F_in, nbr, W, bias=None, residual=None, relu=False, bf16=False)
         F_in = bf16_round(F_in)
         W = bf16_round(W)
     n_out = F_in.shape[0] if nbr is None else nbr.shape[1]
+    if _FAST and n_out and W.shape[2] <= 1024:
+        F_c, W_c = np.ascontiguousarray(F_in), np.ascontiguousarray(W)
+        out = np.empty((n_out, W.shape[2]), dtype=np.float32)
+        nb = None if nbr is None else np.ascontiguousarray(nbr, dtype=np.int64)
+        b = None if bias is None else np.ascontiguousarray(bias, dtype=np.float32).reshape(-1)
+        r = None if residual is None else np.ascontiguousarray(residual, dtype=np.float32)
+        rc = _fast().ref_conv_forward(_p(F_c), _C.c_int64(F_c.shape[0]), _C.c_int32(F_c.shape[1]),
+                                      None if nb is None else _p(nb), _C.c_int64(n_out), _C.c_int32(W_c.shape[0]),
+                                      _p(W_c), _C.c_int32(W_c.shape[2]), None if b is None else _p(b),
+                                      None if r is None else _p(r), _C.c_int32(int(relu)), _p(out))
+        if rc != 0:
+            raise ValueError("ref_conv_forward: unsupported shape")
+        return out
     out = np.zeros((n_out, W.shape[2]), dtype=np.float32)
     if nbr is None:
         out += F_in @ W[0]
@@ -157,6 +218,11 @@ def conv_forward(F_in, nbr, W, bias=None, residual=None, relu=False, bf16=False)
     if relu:
         out = np.maximum(out, 0.0)
     return out
+
+
+def count_pairs(nbr):
+    """P of SURVEY 8d: (offset, output row) pairs that have a neighbour."""
+    return int((np.asarray(nbr) >= 0).sum())
 
 
 # ---- pruning ------------------------------------------------------------------------------------------

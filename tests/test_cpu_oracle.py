@@ -218,10 +218,109 @@ def test_scale_nn_host_matches_oracle():
     sd = cfgmod.make_state_dict()
     nn = ScaleNN(64, 64)
     nn.load(sd)
+    w1, b1 = sd["entropy_model.scale_nn.w1"].astype(np.float64), sd["entropy_model.scale_nn.b1"].astype(np.float64)
+    w2, b2 = sd["entropy_model.scale_nn.w2"].astype(np.float64), sd["entropy_model.scale_nn.b2"].astype(np.float64)
     for q in ([1.0, 0.0], [0.0, 1.0], [1, 1], [0.3, 0.7]):
         ref = E.scale_nn(q, sd["entropy_model.scale_nn.w1"], sd["entropy_model.scale_nn.b1"],
                          sd["entropy_model.scale_nn.w2"], sd["entropy_model.scale_nn.b2"])
         assert np.array_equal(nn.numpy([q])[0], ref) and np.all(ref > 0)
+        # independent statement (float64 matrix form): softplus(relu(q W1 + b1) W2 + b2)
+        o = np.maximum(np.asarray(q, np.float64) @ w1 + b1, 0) @ w2 + b2
+        np.testing.assert_allclose(ref, np.log1p(np.exp(o)), rtol=2e-6)
+
+
+def test_bin_offset_is_the_laplacian_bin_centroid():
+    """E.bin_offset (and its twin EntropyModel.get_offsets) against an independent statement: for a Laplacian of
+    standard deviation sd the mean of x over the unit bin [k - 1/2, k + 1/2], k >= 1, is k - offset(sd), by
+    numerical quadrature in float64."""
+    for sd in (0.11, 0.3, 0.8, 1.5, 3.0, 5.0, 5.7, 9.0, 40.0, 256.0):
+        b = sd / np.sqrt(2.0)
+        k = 3.0
+        x = np.linspace(k - 0.5, k + 0.5, 200001)
+        w = np.exp(-(x - k) / b)                 # density up to a constant factor (x > 0)
+        centroid = np.trapezoid(x * w, x) / np.trapezoid(w, x)
+        want = min(max(k - centroid, 0.0), 0.5)
+        got = float(E.bin_offset(np.array([sd], np.float32))[0])
+        assert abs(got - want) <= 2e-5 + 2e-4 * want, (sd, got, want)
+
+
+def test_fast_oracle_core_equals_numpy_statement():
+    """oracle/sparse_ref.c (OpenMP core used for the full-size frames) vs the numpy statements: kernel maps
+    (k3 stride 1 and 2, k2 strided, k2 generative/transposed) identical, convolutions equal to fp32 summation
+    order, bf16 rounding identical."""
+    rng = np.random.default_rng(3)
+    raw = np.concatenate([rng.integers(0, 2, (6000, 1)), rng.integers(-24, 24, (6000, 3))], axis=1)
+    C, _ = S.sparse_tensor(raw.astype(np.float64))
+    C2 = S.stride_coords(C, 2)
+    Cc = S.generative_coords(C2, 1)
+    cases = [(C, C, S.region_offsets(3, 1), False), (C2, C2, S.region_offsets(3, 2), False),
+             (C, C2, S.region_offsets(2, 1), False), (C2, Cc, S.region_offsets(2, 1), True)]
+    F = rng.standard_normal((len(C), 32)).astype(np.float32) * 3
+    W = (rng.standard_normal((27, 32, 48)) * 0.1).astype(np.float32)
+    b = rng.standard_normal(48).astype(np.float32)
+    R_ = rng.standard_normal((len(C), 48)).astype(np.float32)
+    a = rng.standard_normal(10000).astype(np.float32) * np.float32(10.0) ** rng.integers(-30, 30, 10000)
+    a[:4] = [np.inf, -np.inf, 0.0, 3.4e38]
+    slow_maps = [S.kernel_map(ci, co, offs, transposed=t) for ci, co, offs, t in cases]
+    slow_conv = S.conv_forward(F, slow_maps[0], W, b, R_, relu=True, bf16=True)
+    slow_id = S.conv_forward(F, None, W[:1], b)
+    slow_r = S.bf16_round(a)
+    prev = S.use_fast(True)
+    try:
+        for (ci, co, offs, t), want in zip(cases, slow_maps):
+            assert np.array_equal(S.kernel_map(ci, co, offs, transposed=t), want)
+        np.testing.assert_allclose(S.conv_forward(F, slow_maps[0], W, b, R_, relu=True, bf16=True), slow_conv,
+                                   rtol=1e-5, atol=1e-5)
+        np.testing.assert_allclose(S.conv_forward(F, None, W[:1], b), slow_id, rtol=1e-5, atol=1e-5)
+        assert np.array_equal(S.bf16_round(a).view(np.uint32), slow_r.view(np.uint32))
+    finally:
+        S.use_fast(prev)
+    assert S.count_pairs(slow_maps[0]) == int((slow_maps[0] >= 0).sum()) > len(C)
+
+
+def _cdf_diff(A, B):
+    total = sum(len(a) for a in A)
+    differ = sum(int((np.asarray(a) != np.asarray(b)).sum()) for a, b in zip(A, B))
+    worst = max(int(np.abs(np.asarray(a, np.int64) - np.asarray(b, np.int64)).max()) for a, b in zip(A, B))
+    return total, differ, worst
+
+
+def test_gaussian_tables_independent_builders_and_float32_convention():
+    """GaussianConditional.update(): the product builds the pmf with torch float32 ops in CompressAI 1.2.4's order,
+    the oracle with numpy float32 + scipy's erfc -- two independent routes (their pmfs differ in the last bit of
+    ~6 % of the entries) that must give IDENTICAL quantised tables.  The float64 evaluation is a different
+    convention (what round 1 used): it changes ~1 % of the table entries, which is why App. A says to name it."""
+    from b200pcc.model import GaussianConditional
+    from b200pcc import ops
+    gc = GaussianConditional()
+    prows, center = gc.gaussian_pmf_f32()
+    r32, c32 = E.gaussian_pmf(dtype=np.float32)
+    assert np.array_equal(center, c32) and all(a.dtype == np.float32 for a in prows)
+    ulp = max(float(np.abs(a.astype(np.float64) - b).max()) for a, b in zip(prows, r32))
+    assert ulp <= 2.0 ** -23           # values are < 1: one unit in the last place at most
+    product = [ops.pmf_to_quantized_cdf(r) for r in prows]      # C++ quantiser of the library (host function)
+    oracle = E.gaussian_tables()[0]                               # Python quantiser on the oracle's own pmf
+    assert _cdf_diff(product, oracle)[1] == 0
+    total, differ, worst = _cdf_diff(oracle, E.gaussian_tables(dtype=np.float64)[0])
+    assert total == 27256 and 0 < differ < 0.03 * total and worst <= 3, (differ, worst)
+
+
+def test_factorized_tables_independent_builders():
+    """EntropyBottleneck.update(force=True): torch float32 (product, CompressAI's ops) vs numpy float32 (oracle).
+    softplus / matmul / tanh / sigmoid come from different libraries, so a pmf value may differ in its last bits
+    and a table entry by one count: lengths, offsets and medians exact, <= 2 % of the entries off by one."""
+    from b200pcc import config as cfgmod, ops
+    from b200pcc.model import EntropyBottleneck
+    sd = cfgmod.make_state_dict()
+    eb = EntropyBottleneck(64)
+    eb.load(sd)
+    prows, minima, pmf_length, medians = eb.factorized_pmf_f32()
+    rows, lens, offs, med = E.eb_tables(eb.matrices, eb.biases, eb.factors, eb.quantiles)
+    assert np.array_equal(lens, pmf_length + 2) and np.array_equal(offs, -minima) and np.array_equal(med, medians)
+    total, differ, worst = _cdf_diff([ops.pmf_to_quantized_cdf(r) for r in prows], rows)
+    assert differ <= 0.02 * total and worst <= 1, (total, differ, worst)
+    for r in rows:
+        assert r[0] == 0 and r[-1] == 65536 and np.all(np.diff(r) > 0)
 
 
 def test_golden_vectors():

@@ -29,8 +29,12 @@ def test_tables_match_oracle(model):
     assert np.array_equal(lens, em.gaussian_conditional._cdf_length)
     assert np.array_equal(offs, em.gaussian_conditional._offset)
     eb = em.entropy_bottleneck
+    # the factorized pmf goes through softplus / matmul / tanh / sigmoid of two different libraries (torch float32
+    # in the product like CompressAI, numpy float32 in the oracle): an entry may differ by one count
+    # (tests/test_cpu_oracle.py::test_factorized_tables_independent_builders states the bar)
     rz, lz, oz, med = E.eb_tables(eb.matrices, eb.biases, eb.factors, eb.quantiles)
-    assert all(np.array_equal(a, b) for a, b in zip(rz, eb._quantized_cdf))
+    diff = [np.abs(np.asarray(a, np.int64) - np.asarray(b, np.int64)) for a, b in zip(rz, eb._quantized_cdf)]
+    assert max(int(d.max()) for d in diff) <= 1 and sum(int((d > 0).sum()) for d in diff) <= 0.02 * sum(map(len, rz))
     assert np.array_equal(lz, eb._cdf_length) and np.array_equal(oz, eb._offset)
     assert np.array_equal(med, eb.medians)
 

@@ -1,0 +1,307 @@
+"""GPU parity, transform level: h_s and every level of g_s against the oracle on identical inputs, the
+reconstructed colours with a stated tolerance, pack_batches' NaN / clip handling, and the end-to-end
+decision mismatch counts SURVEY.md 7.4.7 asks for (oracle in bf16 mode and in fp32 mode).
+
+Reference call sites: receiver/decoder/codec_parallel.py:376 (h_s), :469 (g_s(y_hat, k=ks)), :474-502
+(pack_batches); sender/encoder/codec_pipeline.py:354 (h_s on the encoder), :397-437 (symbols).
+
+Stated tolerances (the product multiplies bf16 operands, accumulates in fp32 and stores bf16 between layers;
+the oracle's bf16 mode does the same with another fp32 summation order, so a value may land on the
+neighbouring bf16 — 2^-8 relative — after a layer, and such flips propagate through the following layers):
+
+    T_FEAT  bf16 feature rows after a chain of <= 6 layers on identical inputs:
+            mean |d| <= 4e-3 * mean|ref|   and   max |d| <= 0.08 * max(1, max|ref|)
+    T_F32   fp32 outputs (occupancy logits, Gaussian parameters) of such a chain: the same two bounds
+    T_HEAD  one fp32-output convolution on IDENTICAL bf16 inputs (colour head stage-wise): |d| <= 2e-3 + 2e-3 |ref|
+    T_COL   reconstructed colours end to end (after the [0,1] clip), on the points both sides keep:
+            mean |d| <= 4e-3, max |d| <= 0.06
+"""
+import copy
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+from oracle import sparse_ref as S  # noqa: E402
+from oracle import entropy_ref as E  # noqa: E402
+from oracle.model_ref import RefModel  # noqa: E402
+from oracle.codec_ref import RefCodec  # noqa: E402
+from helpers import to_canonical, stack_frames, report  # noqa: E402
+
+T_FEAT_MEAN, T_FEAT_MAX = 4e-3, 0.08
+T_COL_MEAN, T_COL_MAX = 4e-3, 0.06
+
+
+@pytest.fixture(scope="module")
+def dev():
+    return torch.device("cuda:0")
+
+
+@pytest.fixture(scope="module")
+def model(dev):
+    from b200pcc.pipeline import load_model
+    return load_model(dev)
+
+
+@pytest.fixture(scope="module")
+def frames():
+    from b200pcc import synth
+    return [synth.small_frame(seed=31, n_target=18000), synth.small_frame(seed=32, n_target=8000, offset=(-2, 5, 1))]
+
+
+@pytest.fixture(scope="module")
+def fast_oracle():
+    prev = S.use_fast(True)
+    yield
+    S.use_fast(prev)
+
+
+def _chain_bounds(got, ref, what):
+    err = np.abs(got - ref)
+    scale_mean, scale_max = np.abs(ref).mean(), max(1.0, float(np.abs(ref).max()))
+    assert err.mean() <= T_FEAT_MEAN * scale_mean, (what, "mean", err.mean(), scale_mean)
+    assert err.max() <= T_FEAT_MAX * scale_max, (what, "max", err.max(), scale_max)
+    return {"mean_err": float(err.mean()), "max_err": float(err.max()), "mean_ref": float(scale_mean),
+            "max_ref": float(np.abs(ref).max())}
+
+
+def _coded(model, dev, frames, settings=((1.0, 1.0),)):
+    from b200pcc.pipeline import CompressionPipeline, DecompressionPipeline
+    from b200pcc import container
+    enc = CompressionPipeline([list(s) for s in settings], device=dev, model=model)
+    dec = DecompressionPipeline(device=dev, model=model)
+    enc.keep_debug = dec.keep_debug = True
+    comp, _ = enc.compress({"frames": copy.deepcopy(frames), "timestamps": {}})
+    out, _ = dec.decompress(comp[1])
+    ks = container.read_bitstream_batched(comp[1])[5]
+    return enc, dec, comp, out, ks
+
+
+def test_h_s_vs_oracle(model, dev, frames):
+    """Row a6: the product's z_hat through RefModel.h_s -- generated coordinates exact, the 2*Cy Gaussian
+    parameters within T_F32 (two bf16 generative up-convolutions + the fp32 1x1 head)."""
+    enc, dec, _, _, _ = _coded(model, dev, frames)
+    z_hat, gp = enc.debug["z_hat"], enc.debug["gaussian_params"]
+    Cz, zh = to_canonical(z_hat.C.cpu().numpy(), z_hat.F.cpu().numpy())
+    ref = RefModel(model.config, model.state_dict(), bf16=True)
+    Cp_ref, p_ref = ref.h_s(Cz, zh)
+    Cp, pg = to_canonical(gp.C.cpu().numpy(), gp.F.cpu().numpy())
+    assert np.array_equal(Cp, Cp_ref)
+    assert gp.tensor_stride == [8, 8, 8]
+    r = _chain_bounds(pg, p_ref, "gaussian params")
+    # the decoder rebuilds the same tensor from the decoded z (SURVEY 3 invariant 3), so the comparison holds for it too
+    assert torch.equal(dec.debug["gaussian_params"]._feats, gp._feats)
+    report("h_s_vs_oracle", rows=int(len(Cp)), **r)
+
+
+def _stagewise(model, dev, frames, tag):
+    """Every up-stage of g_s on identical inputs (the product's kept rows of stage i-1 go to the oracle's stage i)."""
+    from b200pcc import ops
+    enc, dec, comp, out, ks = _coded(model, dev, frames)
+    y_hat = dec.debug["y_hat"]
+    x_hat, inter = model.g_s(y_hat, k=ks, return_intermediates=True)
+    ref = RefModel(model.config, model.state_dict(), bf16=True)
+    C_in, yh = to_canonical(y_hat.C.cpu().numpy(), y_hat.F.cpu().numpy())
+    F_in = ref.g_s_pre(yh)
+    stride = 8
+    for i in range(3):
+        Cc, Fc, lg = ref.g_s_stage(i, C_in, F_in, stride)
+        stride //= 2
+        lv = inter[i]
+        Cg = ops.coords_from_keys(lv["keys"]).cpu().numpy()
+        Fg_m = lv["F"].float().cpu().numpy()
+        lg_m = lv["logits"].cpu().numpy()
+        Cg_c, Fg, lgg = to_canonical(Cg, Fg_m, lg_m)
+        assert np.array_equal(Cg_c, Cc), f"candidate coordinates of level {i}"
+        rf = _chain_bounds(Fg, Fc, f"level {i} features")
+        rl = _chain_bounds(lgg, lg, f"level {i} logits")
+        # top-k: exact on equal logits (the product's own logits through the oracle's rule) ...
+        keep_rule = S.topk_mask(lg_m[:, 0], Cg, ks[i])
+        keep_got = lv["keep"].cpu().numpy()
+        assert np.array_equal(np.nonzero(keep_rule)[0], keep_got), f"top-k rule at level {i}"
+        # ... and against the oracle's own logits: count the flipped decisions and show they are near-ties
+        keep_ref = S.topk_mask(lg[:, 0], Cc, ks[i])
+        got_mask_m = np.zeros(len(Cg), bool)
+        got_mask_m[keep_got] = True
+        _, got_mask = to_canonical(Cg, got_mask_m)
+        flips = np.nonzero(keep_ref != got_mask)[0]
+        margin = 0.0
+        if len(flips):
+            # a flipped row's oracle logit lies within the logit tolerance of the frame's oracle threshold
+            for b in range(len(ks[i])):
+                rows = np.nonzero(Cc[:, 0] == b)[0]
+                fr = flips[np.isin(flips, rows)]
+                if len(fr) == 0:
+                    continue
+                kept = lg[rows, 0][keep_ref[rows]]
+                thr = kept.min() if len(kept) else np.inf
+                margin = max(margin, float(np.abs(lg[fr, 0] - thr).max()))
+            assert margin <= 2 * rl["max_err"] + 1e-6, (i, margin, rl)
+        report(f"g_s_stagewise_{tag}", level=i, rows=int(len(Cc)), kept=int(keep_ref.sum()), topk_flips=int(len(flips)),
+               flip_margin=margin, feat=rf, logits=rl)
+        # next stage runs on the PRODUCT's kept rows
+        C_in, F_in = to_canonical(Cg[keep_got], Fg_m[keep_got])
+    # colour head on identical inputs (T_HEAD), before the clip
+    col_ref = ref.g_s_color(C_in, F_in)
+    Cx, colg = to_canonical(x_hat.C.cpu().numpy(), x_hat.F.cpu().numpy())
+    assert np.array_equal(Cx, C_in)
+    np.testing.assert_allclose(colg, col_ref, rtol=2e-3, atol=2e-3)
+    report(f"g_s_colour_head_{tag}", rows=int(len(Cx)), max_err=float(np.abs(colg - col_ref).max()))
+    return enc, dec, comp, out, ks, ref
+
+
+def test_g_s_all_levels_stagewise_and_colours(model, dev, frames):
+    """Row a14: stage-wise parity of all three levels and the colour head; then the whole synthesis end to end:
+    geometry disagreement == rows whose top-k decision flipped at a near-tie, colours within T_COL on the
+    points both sides keep, after pack_batches' clip."""
+    enc, dec, comp, out, ks, ref = _stagewise(model, dev, frames, "small")
+    y_hat = dec.debug["y_hat"]
+    Cy, yh = to_canonical(y_hat.C.cpu().numpy(), y_hat.F.cpu().numpy())
+    C_ref, col_ref = ref.g_s(Cy, yh, ks)
+    for b, f_out in enumerate(out):
+        m = C_ref[:, 0] == b
+        P_ref = C_ref[m][:, 1:]
+        c_ref = np.clip(np.nan_to_num(col_ref[m], nan=0.0) * 255.0, 0, 255) / 255          # codec_parallel.py:489-491
+        assert f_out["points"].shape == P_ref.shape
+        key = lambda P: (P[:, 0].astype(np.int64) + 32768 << 32) | (P[:, 1].astype(np.int64) + 32768 << 16) | (P[:, 2].astype(np.int64) + 32768)
+        kg, kr = key(f_out["points"]), key(P_ref)
+        common, ig, ir = np.intersect1d(kg, kr, return_indices=True)
+        agree = len(common) / len(kr)
+        d = np.abs(f_out["colors"][ig] - c_ref[ir])
+        assert d.mean() <= T_COL_MEAN and d.max() <= T_COL_MAX, (d.mean(), d.max())
+        assert agree >= 0.985, agree
+        report("g_s_end_to_end_small", frame=b, points=int(len(kr)), geometry_agreement=agree,
+               differing_points=int(len(kr) - len(common)), colour_mean_err=float(d.mean()), colour_max_err=float(d.max()))
+
+
+def test_pack_batches_nan_and_clip_bit_exact(dev):
+    """Row a16: pcc_unpack_output == np.clip(np.nan_to_num(c, nan=0.0) * 255.0, 0, 255) / 255
+    (codec_parallel.py:489-491) and pcc_pack_visualizer == the client's packing (receiver/client/client.py:139-146),
+    bit for bit, on NaN, infinities, negative, > 1, exactly 1, -0, denormal and just-off-grid colours."""
+    from b200pcc import ops
+    rng = np.random.default_rng(5)
+    special = np.array([np.nan, -np.nan, np.inf, -np.inf, -0.2, 1.7, 1.0, 0.0, -0.0, 1e-45, -1e-45, 1.17e-38,
+                        0.5, 1.0 - 2 ** -24, 1.0 + 2 ** -23, 254.5 / 255, 255.5 / 255, 0.00390625, 3.4e38, -3.4e38,
+                        1 / 255, 2 / 255, 127.5 / 255, 128 / 255], dtype=np.float32)
+    rand = np.concatenate([rng.uniform(-0.5, 1.5, 5000), rng.integers(0, 256, 2000) / 255.0]).astype(np.float32)
+    c = np.concatenate([special, rand])
+    c = np.concatenate([c, np.zeros((-len(c)) % 3, np.float32)]).reshape(-1, 3)
+    n = len(c)
+    pts = np.concatenate([np.zeros((n, 1)), rng.integers(-3000, 3000, (n, 3))], axis=1).astype(np.int32)
+    keys = ops.keys_from_coords(torch.from_numpy(pts).to(dev))
+    feats = torch.from_numpy(c).to(dev)
+    p_d, c_d = ops.unpack_output(keys, feats)
+    with np.errstate(over="ignore", invalid="ignore"):
+        want = np.clip(np.nan_to_num(c, nan=0.0) * 255.0, 0, 255) / 255
+    got = c_d.cpu().numpy()
+    assert want.dtype == np.float32 and got.dtype == np.float32
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    assert np.array_equal(p_d.cpu().numpy(), pts[:, 1:])
+    vp, vc = ops.pack_visualizer(keys, feats, 100.0)
+    points = pts[:, 1:] + 100
+    colors = 255 * want
+    assert vp.cpu().numpy().tobytes() == np.array(points, dtype=np.float32).tobytes()
+    assert vc.cpu().numpy().tobytes() == np.array(colors, dtype=np.uint8).tobytes()
+
+
+def _end_to_end_counts(model, dev, frame, tag, modes=(True, False)):
+    """the whole codec on the product vs the oracle running on its own (no stage-wise feeding):
+    latent coordinates / k / counts exact; symbol and top-k decision mismatch counts per oracle mode."""
+    enc, dec, comp, out, ks = _coded(model, dev, [frame])
+    y = enc.debug["y"]
+    Cy_g = y.C.cpu().numpy()
+    order = np.argsort(S.lex_key(Cy_g), kind="stable")
+    sym_g = enc.debug["y_sym"][0].cpu().numpy()
+    pts_g = out[0]["points"]
+    key = lambda P: (P[:, 0].astype(np.int64) + 32768 << 32) | (P[:, 1].astype(np.int64) + 32768 << 16) | (P[:, 2].astype(np.int64) + 32768)
+    res = {}
+    for bf16 in modes:
+        codec = RefCodec(model.config, model.state_dict(), bf16=bf16)
+        blob = codec.compress([frame], [[1.0, 1.0]])
+        assert np.array_equal(Cy_g[order], blob["y_coords"]), "latent coordinates"
+        assert blob["k"] == ks, "k"
+        sym_r = blob["debug"]["y_sym"][0]
+        assert sym_r.shape == sym_g.shape
+        mism = int((sym_r != sym_g).sum())
+        off_by_more = int((np.abs(sym_r.astype(np.int64) - sym_g) > 1).sum())
+        yerr = np.abs(y.F.cpu().numpy()[order] - blob["debug"]["y"])
+        frames_r, _ = codec.decompress(blob, 0)
+        P_ref = frames_r[0]["points"]
+        assert P_ref.shape == pts_g.shape
+        common, ig, ir = np.intersect1d(key(pts_g), key(P_ref), return_indices=True)
+        d = np.abs(out[0]["colors"][ig] - frames_r[0]["colors"][ir])
+        res["bf16" if bf16 else "fp32"] = r = {
+            "symbols": int(sym_r.size), "symbol_mismatches": mism, "symbol_mismatch_rate": mism / sym_r.size,
+            "symbols_off_by_more_than_one": off_by_more,
+            "y_mean_rel_err": float(yerr.mean() / np.abs(blob["debug"]["y"]).mean()),
+            "points": int(len(P_ref)), "points_differing": int(len(P_ref) - len(common)),
+            "geometry_agreement": len(common) / len(P_ref),
+            "colour_mean_err": float(d.mean()), "colour_max_err": float(d.max())}
+        report(f"end_to_end_{tag}", oracle_mode="bf16" if bf16 else "fp32", **r)
+    return res
+
+
+def test_end_to_end_mismatch_counts_bf16_and_fp32(model, dev, fast_oracle):
+    """Both oracle modes on a 40 k-point frame.  In bf16 mode the oracle rounds exactly where the product rounds,
+    so the few symbol flips come from fp32 summation order only; fp32 mode adds the bf16 rounding itself."""
+    from b200pcc import synth
+    frame = synth.small_frame(seed=33, n_target=40_000)
+    res = _end_to_end_counts(model, dev, frame, "40k")
+    b, f = res["bf16"], res["fp32"]
+    assert b["symbol_mismatch_rate"] <= 0.02 and b["symbols_off_by_more_than_one"] == 0, b
+    assert b["geometry_agreement"] >= 0.97 and b["colour_mean_err"] <= 2 * T_COL_MEAN, b
+    assert f["symbol_mismatch_rate"] <= 0.10, f
+    assert f["geometry_agreement"] >= 0.90, f
+
+
+def test_cfg2_full_frame_vs_oracle(model, dev, fast_oracle):
+    """BASELINE.json cfg-2 at full size (798 223 points) against the oracle (C core, seconds): latent coordinates,
+    k and counts exact; y within the chain bound; h_a, h_s, symbols and indexes stage-wise; all three g_s levels
+    stage-wise with flip counts; then the end-to-end counts in bf16 mode."""
+    from b200pcc import synth, ops
+    frame = synth.frame_8ivfb(seed=1)
+    _full_frame_vs_oracle(model, dev, frame, "cfg2_800k")
+
+
+def test_cfg3_zed_frame_vs_oracle(model, dev, fast_oracle):
+    """One cfg-3 frame (ZED-shaped sheet, ~300 k points, negative coordinates), same checks."""
+    from b200pcc import synth
+    frame = synth.frame_zed(seed=2)
+    _full_frame_vs_oracle(model, dev, frame, "cfg3_300k")
+
+
+def _full_frame_vs_oracle(model, dev, frame, tag):
+    from b200pcc import ops
+    enc, dec, comp, out, ks, ref = _stagewise(model, dev, [frame], tag)
+    # ---- encoder side, stage-wise
+    C, F = stack_frames([frame])
+    Co, Fo = S.sparse_tensor(C.astype(np.float64), F)
+    Cy, y_ref, k_ref = ref.g_a(Co, Fo, 1)
+    y = enc.debug["y"]
+    Cg, yg = to_canonical(y.C.cpu().numpy(), y.F.cpu().numpy())
+    assert np.array_equal(Cg, Cy) and ks == k_ref
+    ry = _chain_bounds(yg, y_ref, "y")
+    z = enc.debug["z"]
+    Cz, z_ref = ref.h_a(Cy, yg)
+    Czg, zg = to_canonical(z.C.cpu().numpy(), z.F.cpu().numpy())
+    assert np.array_equal(Czg, Cz)
+    rz = _chain_bounds(zg, z_ref, "z")
+    z_hat, gp = enc.debug["z_hat"], enc.debug["gaussian_params"]
+    Czh, zh = to_canonical(z_hat.C.cpu().numpy(), z_hat.F.cpu().numpy())
+    Cp_ref, p_ref = ref.h_s(Czh, zh)
+    Cp, pg = to_canonical(gp.C.cpu().numpy(), gp.F.cpu().numpy())
+    assert np.array_equal(Cp, Cp_ref)
+    rp = _chain_bounds(pg, p_ref, "gaussian params")
+    # symbols / indexes on the product's own y and parameters: bit-exact
+    rows = S.lookup_rows(Cp, Cg)
+    P = np.where(rows[:, None] >= 0, pg[np.maximum(rows, 0)], 0.0).astype(np.float32)
+    cy = model.config["c_y"]
+    s_ref, i_ref = E.gaussian_encode_symbols(yg.T, P[:, :cy].T, P[:, cy:].T, enc.debug["scale"][0].cpu().numpy())
+    assert np.array_equal(enc.debug["y_sym"][0].cpu().numpy(), s_ref)
+    assert np.array_equal(enc.debug["y_idx"][0].cpu().numpy().astype(np.int32), i_ref)
+    report(f"full_frame_{tag}", points=int(len(frame["points"])), latent_points=int(len(Cy)), y=ry, z=rz, params=rp,
+           symbols=int(s_ref.size))
+    _end_to_end_counts(model, dev, frame, tag, modes=(True,))
