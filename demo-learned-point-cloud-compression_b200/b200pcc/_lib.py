@@ -43,6 +43,9 @@ SIGNATURES = {
     "pcc_version": (INT, []),
     "pcc_last_error": (C.c_char_p, []),
     "pcc_launch_count": (I64, []),
+    "pcc_fault_fetch": (INT, [P, P]),
+    "pcc_fault_string": (C.c_char_p, [I32]),
+    "pcc_debug_inject": (INT, [I32]),
     "pcc_keys_from_coords_i32": (INT, [P, I64, P, P]),
     "pcc_keys_from_coords_f32": (INT, [P, I64, P, P]),
     "pcc_ingest_frame": (INT, [P, P, I64, I32, P, P, P]),

@@ -565,7 +565,11 @@ def fetch_strings(pending, as_bytes: bool = True):
     torch.cuda.current_stream().synchronize()
     h32 = host[:hdr].numpy().view(np.uint32)
     sizes = h32[:n].tolist()
-    end = int(h32[n + (n + 63) // 64 - 1])
+    nb = (n + 63) // 64
+    end = int(h32[n + nb - 1])
+    fault = int(h32[n + nb])           # device fault word, delivered (and cleared) with the strings
+    if fault:
+        raise PccError(ops.fault_message(fault))
     if end > cap:
         raise PccError(f"fetch_strings: the strings need {end} bytes, their buffers hold {cap}")
     if end > guess:            # first call, or a GOP much larger than the last one

@@ -206,14 +206,31 @@ def _defer(cnt: torch.Tensor, expect: int, what: str):
     _deferred_list().append((cnt, int(expect), what))
 
 
-def verify_deferred(extra_status=()):
-    """One device->host copy for every deferred count and status word; raises PccError on mismatch."""
+def fault_fetch(device) -> torch.Tensor:
+    """Device int32 [1] holding the device fault word (cleared by the fetch, stream ordered): non-zero when a
+    kernel since the last fetch gave up instead of trapping (pcc_b200.h: PCC_FAULT_*)."""
+    dst = torch.empty(1, dtype=torch.int32, device=device)
+    check(lib.pcc_fault_fetch(_ptr(dst), _stream()))
+    return dst
+
+
+def fault_message(code: int) -> str:
+    return f"device fault {int(code)}: {lib.pcc_fault_string(int(code)).decode()}"
+
+
+def verify_deferred(extra_status=(), device=None):
+    """One device->host copy for every deferred count and status word -- and, when `device` is given, the device
+    fault word; raises PccError on mismatch."""
     items = list(_deferred_list())
     _TLS.deferred = []
     tensors = [c.reshape(1).to(torch.int32) for c, _, _ in items] + [t.reshape(1).to(torch.int32) for t, _ in extra_status]
+    if device is not None:
+        tensors.append(fault_fetch(device))
     if not tensors:
         return
     host = torch.cat(tensors).cpu().numpy()
+    if device is not None and int(host[-1]) != 0:
+        raise _lib.PccError(fault_message(int(host[-1])))
     for (c, e, what), v in zip(items, host[:len(items)]):
         if int(v) != e:
             raise _lib.PccError(f"{what}: device count {int(v)} != expected {e}")

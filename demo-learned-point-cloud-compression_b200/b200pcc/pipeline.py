@@ -86,10 +86,23 @@ class _Stager:
 
     def __init__(self):
         self.buf = None
+        self.busy = None        # event recorded after the last DMA that reads self.buf
+
+    def wait_free(self):
+        """The pinned buffer is written by the host and read by an asynchronous DMA: before the host writes it
+        again, the previous copy out of it must have finished (stage_frames() may be called back to back)."""
+        if self.busy is not None:
+            self.busy.synchronize()
+            self.busy = None
+
+    def mark_busy(self, stream=None):
+        self.busy = torch.cuda.Event()
+        self.busy.record(stream if stream is not None else torch.cuda.current_stream())
 
     def to_device(self, arrays: List[np.ndarray], device, pad4: bool = False) -> List[torch.Tensor]:
         """pad4: uint8 arrays come back with their length rounded up to 4 (zero filled)."""
         total = sum((a.nbytes + 255) // 256 * 256 for a in arrays)
+        self.wait_free()
         if self.buf is None or self.buf.numel() < total:
             self.buf = torch.empty(max(total, 1 << 20), dtype=torch.uint8, pin_memory=True)
         dev = torch.empty(max(total, 1), dtype=torch.uint8, device=device)
@@ -102,6 +115,7 @@ class _Stager:
             offs.append(pos)
             pos += (b.size + 255) // 256 * 256
         dev[:pos].copy_(self.buf[:pos], non_blocking=True)
+        self.mark_busy()
         outs = []
         for a, o in zip(arrays, offs):
             if pad4 and a.dtype == np.uint8 and a.ndim == 1:
@@ -139,6 +153,7 @@ def _stage_concat(stager: "_Stager", arrays: List[np.ndarray], torch_dtype, widt
     import ctypes as C
     from ._lib import lib, check
     total = sum(a.nbytes for a in arrays) // (4 if to_bf16 else 1)
+    stager.wait_free()
     if stager.buf is None or stager.buf.numel() < total:
         stager.buf = torch.empty(max(total, 1 << 20), dtype=torch.uint8, pin_memory=True)
     st = stream if stream is not None else torch.cuda.current_stream()
@@ -152,6 +167,7 @@ def _stage_concat(stager: "_Stager", arrays: List[np.ndarray], torch_dtype, widt
     def job():
         with torch.cuda.device(device):      # a helper thread starts on device 0
             check(lib.pcc_stage_h2d(srcs, sizes, n, pinned_ptr, dev_ptr, _STAGE_PIECE, _STAGE_THREADS, int(to_bf16), st_ptr))
+            stager.mark_busy(st)
         return arrays       # the sources stay alive until their copies are enqueued
     view = dev_buf[:total].view(torch_dtype).view(-1, width)
     if background and total > _STAGE_PIECE:
@@ -627,7 +643,7 @@ class DecompressionPipeline:
             packed = self.pack_batches(x_hat, nf) if to_host else None
             # the call's single blocking point: every deferred size check and both decoder status words
             ops.verify_deferred([(st_geo, "coordinate stream decode failed"), (st_z, "entropy decode of z failed"),
-                                 (st_y, "entropy decode of y failed")])
+                                 (st_y, "entropy decode of y failed")], device=self.device)
             if to_host and getattr(self, "_pts_done", None) is not None:
                 self._pts_done.synchronize()          # the side-stream copy of the points
                 self._pts_done = None

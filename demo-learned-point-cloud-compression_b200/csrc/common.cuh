@@ -62,6 +62,31 @@ static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 b
   return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 
+// Device fault word.  A kernel that meets a condition the host has to hear about (a block table that turns out too
+// small, a pipeline barrier that never completes) records a PCC_FAULT_* code here and returns early; nothing in this
+// library executes `trap`, which would poison the CUDA context of the whole (long-lived) encoder / decoder process.
+// The word lives in device memory of each device (fault.cu); kernels receive its address as an argument.  Hosts read
+// and clear it with pcc_fault_fetch (decompress: with the deferred checks; compress: in the header of the packed
+// strings).  Returns nullptr after setting the error text when the CUDA runtime fails.
+int* fault_word();
+
+constexpr int kMaxDevices = 64;
+// current device index (0 when the runtime cannot say; callers only use it to index small per-device caches)
+static inline int current_device() {
+  int d = 0;
+  if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= kMaxDevices) d = 0;
+  return d;
+}
+// "done once per device" marker for function attributes (cudaFuncSetAttribute is per device / context, not per
+// process): test-and-set is racy only in the harmless direction (the attribute may be set twice).
+struct PerDeviceOnce {
+  std::atomic<uint8_t> done[kMaxDevices];
+  bool needed(int dev) const { return !done[dev].load(std::memory_order_acquire); }
+  void mark(int dev) { done[dev].store(1, std::memory_order_release); }
+};
+// SM count of the current device (cached per device)
+int sm_count();
+
 static inline cudaStream_t as_stream(pcc_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 
 static inline int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }

@@ -147,7 +147,7 @@ __global__ void k_kmap_down2(const uint64_t* __restrict__ ckeys, const int32_t* 
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 k_blockmap_insert(const uint64_t* __restrict__ keys, int64_t n, int shift, uint64_t* __restrict__ tk,
-                  ulonglong2* __restrict__ tv, uint64_t cap_mask) {
+                  ulonglong2* __restrict__ tv, uint64_t cap_mask, int* __restrict__ fault) {
   pdl_trigger();
   pdl_wait();
   // The rows of a block are consecutive, so the lanes of a warp that hold rows of one block find each other with a
@@ -186,7 +186,9 @@ k_blockmap_insert(const uint64_t* __restrict__ keys, int64_t n, int shift, uint6
     }
     base = (base + kWin) & cap_mask;
   }
-  __trap();   // table full: the caller's capacity was below the number of occupied blocks
+  // table full: the caller's capacity was below the number of occupied blocks.  The block stays out of the table
+  // (its rows will look absent to the map kernel) and the host is told through the fault word.
+  atomicMax(fault, PCC_FAULT_BLOCKMAP_FULL);
 }
 
 struct BlockEntry {
@@ -377,9 +379,11 @@ int pcc_blockmap_build(const uint64_t* keys, int64_t n, int log2_stride, uint64_
   PCC_LAUNCHED();
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(keys);
+  int* fault = fault_word();
+  if (!fault) return PCC_E_CUDA;
   launch_pdl(k_blockmap_insert, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, st, keys, n, 3 * log2_stride, table_keys,
                                                                 (ulonglong2*)table_vals16,
-                                                                (uint64_t)capacity - 1);
+                                                                (uint64_t)capacity - 1, fault);
   PCC_LAUNCHED();
   return PCC_OK;
 }

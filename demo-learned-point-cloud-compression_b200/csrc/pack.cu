@@ -19,7 +19,7 @@ __host__ __device__ inline uint32_t align16(uint32_t v) { return (v + 15u) & ~15
 // starts where batch b - 1 ended (end[b - 1], written by the previous launch on the same stream).
 __global__ void __launch_bounds__(256)
 k_pack_strings(PackArgs a, int n, int first, int batch, uint32_t payload0, uint8_t* __restrict__ out, int64_t out_cap,
-               int n_total) {
+               int n_total, int n_batches, int* __restrict__ fault) {
   pdl_trigger();
   pdl_wait();
   uint32_t* hdr = reinterpret_cast<uint32_t*>(out);
@@ -29,7 +29,11 @@ k_pack_strings(PackArgs a, int n, int first, int batch, uint32_t payload0, uint8
   const uint32_t len = (uint32_t)max(*a.len[sidx], 0);
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     hdr[first + sidx] = len;
-    if (sidx == n - 1) hdr[n_total + batch] = off + align16(len);
+    if (sidx == n - 1) {
+      hdr[n_total + batch] = off + align16(len);
+      // last batch: hand the device fault word (common.cuh) to the host with the strings, and clear it
+      if (batch == n_batches - 1) hdr[n_total + n_batches] = (uint32_t)atomicExch(fault, 0);
+    }
   }
   if ((int64_t)off + len > out_cap) return;      // the host sees end > capacity and reports it
   const uint8_t* src = a.buf[sidx];
@@ -53,7 +57,7 @@ extern "C" {
 int64_t pcc_pack_strings_header_bytes(int32_t n) {
   if (n < 0) return -1;
   const int64_t nb = (n + kPackBatch - 1) / kPackBatch;
-  return (int64_t)align16((uint32_t)(4 * (n + nb)));
+  return (int64_t)align16((uint32_t)(4 * (n + nb + 1)));      // lengths, batch ends, fault word
 }
 
 int pcc_pack_strings(const void* const* bufs, const int32_t* const* lens, int32_t n, uint8_t* out, int64_t out_cap,
@@ -62,6 +66,9 @@ int pcc_pack_strings(const void* const* bufs, const int32_t* const* lens, int32_
   PCC_CHECK_ARG(n == 0 || (bufs && lens));
   const int64_t hdr = pcc_pack_strings_header_bytes(n);
   PCC_CHECK_ARG(out_cap >= hdr && out_cap < (1ll << 32));
+  int* fault = fault_word();
+  if (!fault) return PCC_E_CUDA;
+  const int n_batches = (n + kPackBatch - 1) / kPackBatch;
   for (int first = 0, batch = 0; first < n; first += kPackBatch, ++batch) {
     PackArgs a;
     const int cnt = n - first < kPackBatch ? n - first : kPackBatch;
@@ -74,7 +81,7 @@ int pcc_pack_strings(const void* const* bufs, const int32_t* const* lens, int32_
       a.buf[i] = nullptr;
       a.len[i] = nullptr;
     }
-    launch_pdl(k_pack_strings, dim3(dim3(8, cnt)), dim3(256), 0, as_stream(s), a, cnt, first, batch, (uint32_t)hdr, out, out_cap, n);
+    launch_pdl(k_pack_strings, dim3(dim3(8, cnt)), dim3(256), 0, as_stream(s), a, cnt, first, batch, (uint32_t)hdr, out, out_cap, n, n_batches, fault);
     PCC_LAUNCHED();
   }
   return PCC_OK;

@@ -340,7 +340,9 @@ k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, in
   for (int i = lane; i < seg; i += 32) acc += h32[4 + i];
   acc = __reduce_add_sync(0xffffffffu, acc);
   const uint64_t seg_off = 16ull + 4ull * nseg + acc;
-  if (seg_off + 132 > (uint64_t)container_bytes) {
+  // the segment sizes come from the (untrusted) stream: a segment that does not start on a 4-byte boundary or
+  // past the end is a damaged stream, never an address to dereference
+  if ((seg_off & 3ull) != 0 || seg_off + 132 > (uint64_t)container_bytes) {
     if (lane == 0) atomicExch(status, 1);
     return;
   }
@@ -562,11 +564,12 @@ int pcc_rans_decode(const uint8_t* container, int64_t container_bytes, int32_t s
   const size_t smem = (size_t)T.T * 16 +
                       ((((size_t)T.T * (kLutN + 1) + 7) & ~(size_t)7) + (((size_t)T.total + 7) & ~(size_t)7)) * 2 + wsm;
   const unsigned grid = (unsigned)((ns + kDecWarps - 1) / kDecWarps);
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceOnce configured;      // the opt-in is per device, not per process
+  const int dev = current_device();
+  if (configured.needed(dev)) {
     PCC_CUDA(cudaFuncSetAttribute(k_rans_decode<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
     PCC_CUDA(cudaFuncSetAttribute(k_rans_decode<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsm));
-    configured = true;
+    configured.mark(dev);
   }
   if (T.lut && T.total > 0 && smem <= 224 * 1024) {
     launch_pdl(k_rans_decode<true>, dim3(grid), dim3(32 * kDecWarps), smem, st, container, container_bytes, seg_size, idx,

@@ -30,28 +30,24 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  uint32_t ok = 0;
-  // Bounded spin: a protocol bug traps (CUDA error) instead of hanging the GPU.
-  for (uint32_t spin = 0; spin < (1u << 22); ++spin) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
-        "selp.u32 %0, 1, 0, p;\n"
-        "}\n"
-        : "=r"(ok)
-        : "r"(bar), "r"(parity)
-        : "memory");
-    if (ok) return;
-  }
-  __trap();
+// Waiting on a pipeline barrier never hangs and never traps: the spin is bounded, and a waiter that runs out of
+// patience raises the CTA's abort flag (shared memory) and records PCC_FAULT_PIPELINE_TIMEOUT in the device fault
+// word (common.cuh).  Every waiter polls the flag, so all roles of the CTA leave their loops within microseconds and
+// the kernel ends normally -- its tiles stay unwritten and the host learns about it from the fault word.  A timeout
+// means a protocol bug (or a profiler / time-slicing pause of several seconds), not a data-dependent condition.
+struct WaitCtx {
+  uint32_t abort_flag;   // shared-memory address of the CTA's abort word
+  uint32_t spin_limit;
+  int* fault;
+};
+__device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
 }
-// Same, for waiters that are not on the critical path: the suspend-time hint keeps the polling
-// (one shared-memory wavefront per try) off the L1/shared data pipe the gather is bound by.
-__device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity) {
-  uint32_t ok = 0;
-  for (uint32_t spin = 0; spin < (1u << 22); ++spin) {
+__device__ __noinline__ bool mbar_wait_slow(uint32_t bar, uint32_t parity, uint32_t hint, const WaitCtx& w) {
+  for (uint32_t spin = 0; spin < w.spin_limit; ++spin) {
+    uint32_t ok = 0;
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
@@ -59,11 +55,34 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity)
         "selp.u32 %0, 1, 0, p;\n"
         "}\n"
         : "=r"(ok)
-        : "r"(bar), "r"(parity), "r"(2000u)
+        : "r"(bar), "r"(parity), "r"(hint)
         : "memory");
-    if (ok) return;
+    if (ok) return true;
+    if ((spin & 15u) == 15u && ld_shared_u32(w.abort_flag) != 0u) return false;
   }
-  __trap();
+  asm volatile("st.shared.b32 [%0], %1;" ::"r"(w.abort_flag), "r"(1u) : "memory");
+  atomicMax(w.fault, PCC_FAULT_PIPELINE_TIMEOUT);
+  return false;
+}
+// Fast path inline (one try), the bounded loop out of line.
+__device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity, const WaitCtx& w) {
+  uint32_t ok = 0;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  if (ok) return true;
+  return mbar_wait_slow(bar, parity, 0u, w);
+}
+// Same, for waiters that are not on the critical path: the suspend-time hint keeps the polling
+// (one shared-memory wavefront per try) off the L1/shared data pipe the gather is bound by.
+__device__ __forceinline__ bool mbar_wait_relaxed(uint32_t bar, uint32_t parity, const WaitCtx& w) {
+  return mbar_wait_slow(bar, parity, 2000u, w);
 }
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes)
@@ -149,6 +168,9 @@ struct UmmaParams {
   int nrounds_total;   // ceil(ntiles / T)
   int jc;              // kernel offsets per kernel-map unit (divides kvol)
   uint32_t tmem_cols, acc_cols;
+  int* fault;          // device fault word (common.cuh)
+  uint32_t spin_limit; // barrier patience (tries)
+  int inject;          // test hook: drop one hand-off so that the timeout path runs
 };
 
 // warps 4..7 issue MMAs: one elected thread each, every warp owning the tiles t = w (mod 4) of a
@@ -178,12 +200,6 @@ __device__ __forceinline__ void gather_chunk(uint32_t dst, uint64_t base, uint32
       "l"(base), "r"(r), "r"(n_in), "r"(dirty_bit), "n"(ROW_BYTES)
       : "memory");
 }
-__device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr) {
-  uint32_t v;
-  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
-  return v;
-}
-
 // Persistent (one CTA per SM), warp specialised.  A CTA works in rounds: round r of CTA b covers the
 // super-tile of T = 2^lt consecutive 128-row tiles starting at tile T*(b + r*gridDim.x).  One pipeline
 // stage = (round, kernel offset j): the gathered rows of all T tiles for that offset.  The T tiles
@@ -232,7 +248,8 @@ k_spconv_umma(const UmmaParams p) {
   const uint32_t bar0 = (nbr0 + kNbrBufs * unit_bytes + 7u) & ~7u;
   const uint32_t full0 = bar0, empty0 = bar0 + 8u * G, tfull0 = bar0 + 16u * G, tempty0 = tfull0 + 16u,
                  wfull = tempty0 + 16u, nfull0 = wfull + 8u, nempty0 = nfull0 + 8u * kNbrBufs,
-                 tmem_slot = nempty0 + 8u * kNbrBufs;
+                 tmem_slot = nempty0 + 8u * kNbrBufs, abort_slot = tmem_slot + 4u;
+  const WaitCtx wc{abort_slot, p.spin_limit, p.fault};
   const uint32_t nunits = (uint32_t)(kvol / p.jc);   // kernel-map units per round
 
   if (tid == 0) {
@@ -250,6 +267,7 @@ k_spconv_umma(const UmmaParams p) {
       mbar_init(nempty0 + 8u * i, 4 * p.jc);   // every stage of the unit releases it once per warp
     }
     mbar_init(wfull, 1);
+    asm volatile("st.shared.b32 [%0], %1;" ::"r"(abort_slot), "r"(0u) : "memory");
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == kMmaWarp) tmem_alloc(tmem_slot, p.tmem_cols);
@@ -302,11 +320,11 @@ k_spconv_umma(const UmmaParams p) {
         const uint32_t c = j / (uint32_t)p.jc;
         const uint32_t unit = r * nunits + c;
         const uint32_t nbuf = unit % kNbrBufs;
-        mbar_wait(nfull0 + 8u * nbuf, (unit / kNbrBufs) & 1u);
+        if (!mbar_wait(nfull0 + 8u * nbuf, (unit / kNbrBufs) & 1u, wc)) goto role_done;
         nb_addr = nbr0 + nbuf * unit_bytes + (((j - c * p.jc) << lt) * kTileM) * 4u;
         nb_bar = nempty0 + 8u * nbuf;
       }
-      if (use > 0) mbar_wait(emptyb, (use - 1) & 1u);
+      if (use > 0 && !mbar_wait(emptyb, (use - 1) & 1u, wc)) goto role_done;
       if (!p.wres && pw == 0 && lane == 0) {
         mbar_expect_tx(fullb, b_bytes);
         bulk_g2s(w0 + (uint32_t)gi * b_bytes, p.w + (size_t)j * b_bytes, b_bytes, fullb);
@@ -372,7 +390,7 @@ k_spconv_umma(const UmmaParams p) {
         if (tv > T) tv = T;
         for (uint32_t c = 0; c < nunits; ++c, ++unit) {
           const uint32_t nb = unit % kNbrBufs;
-          if (unit >= kNbrBufs) mbar_wait_relaxed(nempty0 + 8u * nb, ((unit / kNbrBufs) - 1u) & 1u);
+          if (unit >= kNbrBufs && !mbar_wait_relaxed(nempty0 + 8u * nb, ((unit / kNbrBufs) - 1u) & 1u, wc)) goto role_done;
           const uint32_t dst = nbr0 + nb * unit_bytes;
           if (p.nbr_bulk) {
             if (tv < T) {      // last round: tiles past the end of the map gather nothing
@@ -419,16 +437,16 @@ k_spconv_umma(const UmmaParams p) {
       const uint64_t bdesc0 = make_desc(w0, lbo_b, 128u);
       const uint32_t a_slot = a_bytes >> 4, a_ks = (2u * lbo_a) >> 4, a_t = (kMmaWarps * a_tile) >> 4;
       const uint32_t b_step = b_bytes >> 4, b_ks = (2u * lbo_b) >> 4;
-      if (p.wres) mbar_wait(wfull, 0);
+      if (p.wres && !mbar_wait(wfull, 0, wc)) goto role_done;
       uint32_t s = 0, ph = 0;
       int r = 0;
       for (int64_t rg = blockIdx.x; rg < p.nrounds_total; rg += gridDim.x, ++r) {
         const uint32_t par = (uint32_t)(r & 1);
-        if (r >= 2) mbar_wait(tempty0 + 8u * par, (uint32_t)(((r >> 1) - 1) & 1));
+        if (r >= 2 && !mbar_wait(tempty0 + 8u * par, (uint32_t)(((r >> 1) - 1) & 1), wc)) goto role_done;
         tc_fence_after();
         const uint32_t tmem_d0 = tmem_base + ((par << lt) + (uint32_t)mw) * p.acc_cols;
         for (int j = 0; j < kvol; ++j) {
-          mbar_wait(full0 + 8u * s, ph & 1u);
+          if (!mbar_wait(full0 + 8u * s, ph & 1u, wc)) goto role_done;
           tc_fence_after();
           const uint64_t ad = adesc0 + (uint64_t)(s * a_slot);
           const uint64_t bd = bdesc0 + (uint64_t)((p.wres ? (uint32_t)j : s) * b_step);
@@ -438,7 +456,7 @@ k_spconv_umma(const UmmaParams p) {
               umma_bf16(tmem_d0 + (uint32_t)(ti * kMmaWarps) * p.acc_cols, ad + (uint64_t)(ti * a_t + ks * a_ks),
                         bd + (uint64_t)(ks * b_ks), idesc, (j == 0 && ks == 0) ? 0u : 1u);
           }
-          umma_commit(empty0 + 8u * s);
+          if (!(p.inject && mw == 0 && r == 0 && j == 1)) umma_commit(empty0 + 8u * s);
           if (j == kvol - 1) umma_commit(tfull0 + 8u * par);
           if (++s == (uint32_t)G) { s = 0; ++ph; }
         }
@@ -450,7 +468,7 @@ k_spconv_umma(const UmmaParams p) {
     const int cstore = p.cstore > 0 ? p.cstore : cout;
     for (int64_t rg = blockIdx.x; rg < p.nrounds_total; rg += gridDim.x, ++r) {
       const uint32_t par = (uint32_t)(r & 1);
-      mbar_wait_relaxed(tfull0 + 8u * par, (uint32_t)((r >> 1) & 1));
+      if (!mbar_wait_relaxed(tfull0 + 8u * par, (uint32_t)((r >> 1) & 1), wc)) goto role_done;
       tc_fence_after();
       for (int t = 0; t < T; ++t) {
         const int64_t tile = (rg << lt) + t;
@@ -525,6 +543,7 @@ k_spconv_umma(const UmmaParams p) {
       if (lane == 0) mbar_arrive(tempty0 + 8u * par);
     }
   }
+role_done:
   tc_fence_before();
   __syncthreads();
   if (warp == kMmaWarp) tmem_dealloc(tmem_base, p.tmem_cols);
@@ -568,13 +587,15 @@ int pcc_spconv_pack_weights(const float* w, int kvol, int cin, int cout, int cin
 
 extern "C++" {
 static int g_groups = 0, g_max_t = 4;  // g_groups 0 = by channel count
+static std::atomic<int> g_inject{0};   // pcc_debug_inject
 
 template <int CIN, int G, int LT>
 static int launch_umma_glt(const UmmaParams& p, size_t smem, unsigned grid, cudaStream_t st) {
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceOnce configured;      // the shared-memory opt-in is per device, not per process
+  const int dev = current_device();
+  if (configured.needed(dev)) {
     PCC_CUDA(cudaFuncSetAttribute(k_spconv_umma<CIN, G, LT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
-    configured = true;
+    configured.mark(dev);
   }
   pcc::g_launches.fetch_add(1);
   PCC_CUDA(launch_pdl(k_spconv_umma<CIN, G, LT>, dim3(grid), dim3(32 * (kProdWarp0 + 4 * G)), smem, st, p));
@@ -598,6 +619,12 @@ static int launch_umma(const UmmaParams& p, int groups, size_t smem, unsigned gr
   }
 }
 }  // extern "C++"
+
+int pcc_debug_inject(int32_t what) {
+  PCC_CHECK_ARG(what == 0 || what == 1);
+  g_inject.store(what);
+  return PCC_OK;
+}
 
 int pcc_spconv_set_tuning(int groups, int max_tiles, int use_cg) {
   PCC_CHECK_ARG(max_tiles == 1 || max_tiles == 2 || max_tiles == 4);
@@ -650,12 +677,11 @@ int pcc_spconv_umma(const void* in_bf16, int64_t n_in, int cin, const int32_t* n
   const int64_t ntiles = (n_out + kTileM - 1) / kTileM;
   p.ntiles = (int)ntiles;
   p.nbr_bulk = (nbr && nbr_ld % 4 == 0 && nbr_ld >= ntiles * kTileM && ((uintptr_t)nbr % 16) == 0) ? 1 : 0;
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    PCC_CUDA(cudaGetDevice(&dev));
-    PCC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  }
+  const int sms = sm_count();
+  p.fault = fault_word();
+  if (!p.fault) return PCC_E_CUDA;
+  p.inject = g_inject.exchange(0);
+  p.spin_limit = p.inject ? (1u << 10) : (1u << 22);
   // gather groups (= ring slots) and T tiles per stage.  T is bounded by TMEM (2 x T accumulators of
   // acc_cols columns in 512), by shared memory (G slots of T tiles), by the tuning cap and by the
   // tile count (keep >= 2 rounds per SM so the persistent grid stays balanced).

@@ -41,6 +41,20 @@ const char* pcc_last_error(void);
 /* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
 int64_t pcc_launch_count(void);
 
+/* Device fault word.  Kernels never trap (a trap is a sticky error that ends the CUDA context of the whole
+ * encoder / decoder service, sender/encoder/encoder.py:50-75, receiver/decoder/decoder.py:41-62 keep one process
+ * alive for the session): a kernel that cannot go on records a PCC_FAULT_* code in a per-device word and returns
+ * early, leaving its outputs unwritten.  pcc_fault_fetch copies the word of the current device into dst_dev (device
+ * int32) and clears it, stream ordered; pcc_pack_strings also delivers and clears it in its header.  A non-zero
+ * value means the results of the calls since the last fetch must be discarded. */
+#define PCC_FAULT_BLOCKMAP_FULL 1
+#define PCC_FAULT_PIPELINE_TIMEOUT 2
+int pcc_fault_fetch(int32_t* dst_dev, pcc_stream_t s);
+const char* pcc_fault_string(int32_t code);
+/* Test hook: what = 1 makes the next pcc_spconv_umma launch of this process drop one pipeline hand-off (and spin
+ * briefly instead of for seconds), so that the timeout path can be exercised; 0 disarms. */
+int pcc_debug_inject(int32_t what);
+
 /* ------------------------------------------------------------------------------------------
  * (1) coordinates, hash, kernel maps
  * ------------------------------------------------------------------------------------------ */

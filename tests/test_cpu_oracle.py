@@ -341,3 +341,20 @@ def test_golden_vectors():
     out, _ = codec.decompress(blob, 0)
     assert np.array_equal(out[0]["points"], g["dec_points"])
     np.testing.assert_allclose(out[0]["colors"], g["dec_colors"], atol=1e-6)
+
+
+def test_recorded_frame_coordinate_sizes():
+    """The reference's recorded frame 0 (tests/golden/recorded_frames.npz) through the oracle's coordinate
+    conventions reproduces the sizes SURVEY 7.3 measured: 19 679 -> 8 874 -> 2 831 -> 815 -> 229 -> 63 and 7.2
+    kernel-map pairs per point at stride 1."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "recorded_frames.npz"))
+    p = g["points_0"]
+    assert p.dtype == np.int16 and g["colors_0"].dtype == np.float64 and p.min() < 0
+    C = np.concatenate([np.zeros((len(p), 1), np.int32), p.astype(np.int32)], axis=1)
+    Cl = S.sparse_tensor(C.astype(np.float64))[0]
+    assert abs(S.count_pairs(S.kernel_map(Cl, Cl, S.region_offsets(3, 1))) / len(Cl) - 7.2) < 0.1
+    sizes = [len(Cl)]
+    for l in range(5):
+        Cl = S.stride_coords(Cl, 2 << l)
+        sizes.append(len(Cl))
+    assert sizes == [19679, 8874, 2831, 815, 229, 63]

@@ -207,20 +207,21 @@ def test_pack_batches_nan_and_clip_bit_exact(dev):
     assert vc.cpu().numpy().tobytes() == np.array(colors, dtype=np.uint8).tobytes()
 
 
-def _end_to_end_counts(model, dev, frame, tag, modes=(True, False)):
+def _end_to_end_counts(model, dev, frames, tag, modes=(True, False)):
     """the whole codec on the product vs the oracle running on its own (no stage-wise feeding):
     latent coordinates / k / counts exact; symbol and top-k decision mismatch counts per oracle mode."""
-    enc, dec, comp, out, ks = _coded(model, dev, [frame])
+    if isinstance(frames, dict):
+        frames = [frames]
+    enc, dec, comp, out, ks = _coded(model, dev, frames)
     y = enc.debug["y"]
     Cy_g = y.C.cpu().numpy()
     order = np.argsort(S.lex_key(Cy_g), kind="stable")
     sym_g = enc.debug["y_sym"][0].cpu().numpy()
-    pts_g = out[0]["points"]
     key = lambda P: (P[:, 0].astype(np.int64) + 32768 << 32) | (P[:, 1].astype(np.int64) + 32768 << 16) | (P[:, 2].astype(np.int64) + 32768)
     res = {}
     for bf16 in modes:
         codec = RefCodec(model.config, model.state_dict(), bf16=bf16)
-        blob = codec.compress([frame], [[1.0, 1.0]])
+        blob = codec.compress(frames, [[1.0, 1.0]])
         assert np.array_equal(Cy_g[order], blob["y_coords"]), "latent coordinates"
         assert blob["k"] == ks, "k"
         sym_r = blob["debug"]["y_sym"][0]
@@ -229,16 +230,20 @@ def _end_to_end_counts(model, dev, frame, tag, modes=(True, False)):
         off_by_more = int((np.abs(sym_r.astype(np.int64) - sym_g) > 1).sum())
         yerr = np.abs(y.F.cpu().numpy()[order] - blob["debug"]["y"])
         frames_r, _ = codec.decompress(blob, 0)
-        P_ref = frames_r[0]["points"]
-        assert P_ref.shape == pts_g.shape
-        common, ig, ir = np.intersect1d(key(pts_g), key(P_ref), return_indices=True)
-        d = np.abs(out[0]["colors"][ig] - frames_r[0]["colors"][ir])
+        n_pts = n_common = 0
+        d = []
+        for f_g, f_r in zip(out, frames_r):
+            assert f_r["points"].shape == f_g["points"].shape
+            common, ig, ir = np.intersect1d(key(f_g["points"]), key(f_r["points"]), return_indices=True)
+            d.append(np.abs(f_g["colors"][ig] - f_r["colors"][ir]).reshape(-1))
+            n_pts, n_common = n_pts + len(f_r["points"]), n_common + len(common)
+        d = np.concatenate(d)
         res["bf16" if bf16 else "fp32"] = r = {
             "symbols": int(sym_r.size), "symbol_mismatches": mism, "symbol_mismatch_rate": mism / sym_r.size,
             "symbols_off_by_more_than_one": off_by_more,
             "y_mean_rel_err": float(yerr.mean() / np.abs(blob["debug"]["y"]).mean()),
-            "points": int(len(P_ref)), "points_differing": int(len(P_ref) - len(common)),
-            "geometry_agreement": len(common) / len(P_ref),
+            "points": int(n_pts), "points_differing": int(n_pts - n_common),
+            "geometry_agreement": n_common / n_pts,
             "colour_mean_err": float(d.mean()), "colour_max_err": float(d.max())}
         report(f"end_to_end_{tag}", oracle_mode="bf16" if bf16 else "fp32", **r)
     return res
@@ -273,13 +278,14 @@ def test_cfg3_zed_frame_vs_oracle(model, dev, fast_oracle):
     _full_frame_vs_oracle(model, dev, frame, "cfg3_300k")
 
 
-def _full_frame_vs_oracle(model, dev, frame, tag):
-    from b200pcc import ops
-    enc, dec, comp, out, ks, ref = _stagewise(model, dev, [frame], tag)
+def _full_frame_vs_oracle(model, dev, frames, tag):
+    if isinstance(frames, dict):
+        frames = [frames]
+    enc, dec, comp, out, ks, ref = _stagewise(model, dev, frames, tag)
     # ---- encoder side, stage-wise
-    C, F = stack_frames([frame])
+    C, F = stack_frames(frames)
     Co, Fo = S.sparse_tensor(C.astype(np.float64), F)
-    Cy, y_ref, k_ref = ref.g_a(Co, Fo, 1)
+    Cy, y_ref, k_ref = ref.g_a(Co, Fo, len(frames))
     y = enc.debug["y"]
     Cg, yg = to_canonical(y.C.cpu().numpy(), y.F.cpu().numpy())
     assert np.array_equal(Cg, Cy) and ks == k_ref
@@ -302,6 +308,52 @@ def _full_frame_vs_oracle(model, dev, frame, tag):
     s_ref, i_ref = E.gaussian_encode_symbols(yg.T, P[:, :cy].T, P[:, cy:].T, enc.debug["scale"][0].cpu().numpy())
     assert np.array_equal(enc.debug["y_sym"][0].cpu().numpy(), s_ref)
     assert np.array_equal(enc.debug["y_idx"][0].cpu().numpy().astype(np.int32), i_ref)
-    report(f"full_frame_{tag}", points=int(len(frame["points"])), latent_points=int(len(Cy)), y=ry, z=rz, params=rp,
-           symbols=int(s_ref.size))
-    _end_to_end_counts(model, dev, frame, tag, modes=(True,))
+    report(f"full_frame_{tag}", points=int(sum(len(f["points"]) for f in frames)), latent_points=int(len(Cy)), y=ry, z=rz,
+           params=rp, symbols=int(s_ref.size))
+    return _end_to_end_counts(model, dev, frames, tag, modes=(True,))
+
+
+def recorded_frames():
+    """The reference's recorded capturer frames (tests/golden/recorded_frames.npz, made by make_recorded.py from
+    evaluation/data/test_sequence/frame_0000{0,1,2}.pkl)."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "recorded_frames.npz"))
+    return [{"points": g[f"points_{i}"], "colors": g[f"colors_{i}"]} for i in g["frames"]]
+
+
+def test_recorded_frames_coordinates_and_kernel_maps(dev):
+    """on a real recorded ZED frame (19 679 points, negative coordinates) the output coordinates at
+    strides 2 / 4 / 8 / 16 / 32 and the k3 kernel maps equal the oracle's exactly (sizes 19 679 -> 8 874 -> 2 831 ->
+    815 -> 229 -> 63), as do the k2/s2 maps and the generative children."""
+    from b200pcc import ops
+    frame = recorded_frames()[0]
+    C, _ = stack_frames([frame])
+    keys = ops.sort_unique(ops.keys_from_coords(torch.from_numpy(C).to(dev)))[0]
+    sizes, Cl = [len(C)], S.sparse_tensor(C.astype(np.float64))[0]
+    for l in range(6):
+        t = 1 << l
+        Cg = ops.coords_from_keys(keys).cpu().numpy()
+        assert np.array_equal(to_canonical(Cg)[0], Cl)
+        if l <= 3:
+            ref = S.kernel_map(Cg, Cg, S.region_offsets(3, t))
+            got = ops.kmap_k3_blocks(keys, l, ops.blockmap_build(keys, l)).cpu().numpy()
+            assert np.array_equal(got, ref), l
+            if l == 0:
+                assert abs((ref >= 0).sum() / len(Cg) - 7.2) < 0.1          # pairs per point measured in SURVEY 7.3
+        if l == 5:
+            break
+        pk, parent = ops.coords_downsample(keys, l + 1)
+        Cp = ops.coords_from_keys(pk).cpu().numpy()
+        refd = S.kernel_map(Cg, Cp, S.region_offsets(2, t))          # oracle on the product's row orders
+        assert np.array_equal(ops.kmap_down2(keys, parent, l, pk.shape[0]).cpu().numpy(), refd), l
+        ch = ops.coords_from_keys(ops.coords_children(pk, l)).cpu().numpy()
+        assert np.array_equal(to_canonical(ch)[0], S.generative_coords(Cp, t))
+        keys, Cl = pk, S.stride_coords(Cl, 2 * t)
+        sizes.append(len(Cl))
+    assert sizes == [19679, 8874, 2831, 815, 229, 63], sizes
+
+
+def test_recorded_gop_vs_oracle(model, dev, fast_oracle):
+    """A GOP of three recorded frames through every stage-wise and end-to-end check of the synthetic configurations."""
+    res = _full_frame_vs_oracle(model, dev, recorded_frames(), "recorded_3x19k")
+    assert res["bf16"]["geometry_agreement"] >= 0.97
