@@ -119,7 +119,8 @@ __global__ void k_unpack_output(const uint64_t* __restrict__ keys, const float* 
     float v = feats[3 * i + c];
     if (v != v) v = 0.0f;
     float t = __fmul_rn(v, 255.0f);
-    t = fminf(fmaxf(t, 0.0f), 255.0f);
+    t = t < 0.0f ? 0.0f : t;          // np.clip's comparisons, not fmax/fmin: -0.0 stays -0.0 as in numpy
+    t = t > 255.0f ? 255.0f : t;
     col[3 * i + c] = __fdiv_rn(t, 255.0f);
   }
 }
@@ -142,7 +143,9 @@ __global__ void k_pack_visualizer(const uint64_t* __restrict__ keys, const float
   for (int c = 0; c < 3; ++c) {
     float v = feats[3 * i + c];
     if (v != v) v = 0.0f;
-    float t = fminf(fmaxf(__fmul_rn(v, 255.0f), 0.0f), 255.0f);
+    float t = __fmul_rn(v, 255.0f);
+    t = t < 0.0f ? 0.0f : t;
+    t = t > 255.0f ? 255.0f : t;
     t = __fmul_rn(255.0f, __fdiv_rn(t, 255.0f));
     col[3 * i + c] = (uint8_t)(int)t;      // 0 <= t <= 255: truncation like ndarray.astype(uint8)
   }

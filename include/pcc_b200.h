@@ -51,7 +51,7 @@ int64_t pcc_launch_count(void);
 #define PCC_FAULT_PIPELINE_TIMEOUT 2
 int pcc_fault_fetch(int32_t* dst_dev, pcc_stream_t s);
 const char* pcc_fault_string(int32_t code);
-/* Test hook: what = 1 makes the next pcc_spconv_umma launch of this process drop one pipeline hand-off (and spin
+/* Test hook: what = 1 makes the next k = 3 pcc_spconv_umma launch of this process drop one pipeline hand-off (and spin
  * briefly instead of for seconds), so that the timeout path can be exercised; 0 disarms. */
 int pcc_debug_inject(int32_t what);
 

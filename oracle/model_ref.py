@@ -111,14 +111,17 @@ class RefModel:
         """Colour head on the final (stride-1) coordinates: fp32 [n, 3], before pack_batches' clip."""
         return self._conv("g_s.color", F, self._k3(C, 1), store=False)
 
-    def g_s(self, C, y_hat, ks, return_intermediates=False):
+    def g_s(self, C, y_hat, ks, return_intermediates=False, keeps=None):
+        """keeps: optional list of three boolean masks (canonical row order of each level's candidates) that REPLACE
+        the oracle's own top-k decisions -- parity tests pass the product's decisions so that both sides reconstruct
+        the same geometry and the attributes can be compared point by point."""
         F = self.g_s_pre(y_hat)
         stride = 8
         inter = []
         for i in range(3):
             C, F, logits = self.g_s_stage(i, C, F, stride)
             stride //= 2
-            keep = S.topk_mask(logits[:, 0], C, ks[i])
+            keep = S.topk_mask(logits[:, 0], C, ks[i]) if keeps is None else np.asarray(keeps[i], bool)
             if return_intermediates:
                 inter.append({"C": C, "F": F, "logits": logits, "keep": keep})
             C, F = C[keep], F[keep]
