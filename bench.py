@@ -85,6 +85,23 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
+def _load_plain(name):
+    """b200pcc/<name>.py as a stand-alone module (synth, config: numpy only).  The CPU arm must not import the
+    b200pcc package -- its __init__ loads libpcc_b200.so, and the reference process is meant to hold no GPU code."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location(f"_plain_{name}", os.path.join(PKG_DIR, "b200pcc", f"{name}.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def _config(points_per_frame, world):
+    """The `config` object of the JSON line: the same for the GPU arm and the reference arm."""
+    return {"workload": WORKLOAD, "points_per_frame": int(points_per_frame), "frames_per_step": 1,
+            "model": "synth_small (seeded weights; the demo_small weights are not in the reference tree)",
+            "l2": "256 MiB flush write between timed iterations", "parallelism": f"frame-parallel x{world}"}
+
+
 def _crop_sample(frame, n_target):
     """Bounded CPU sample of the same workload: a horizontal slab of the frame with ~n_target points."""
     p = frame["points"]
@@ -94,58 +111,143 @@ def _crop_sample(frame, n_target):
     return {"points": p[sel], "colors": frame["colors"][sel]}
 
 
-def _blas_threads():
-    """Threads the numpy BLAS pool of this process actually uses (what the CPU port runs on)."""
-    try:
-        from threadpoolctl import threadpool_info
-        n = [int(p.get("num_threads", 1)) for p in threadpool_info() if p.get("user_api") == "blas"]
-        return max(n) if n else 1
-    except Exception:
-        return 1
-
-
-def cpu_port_run(frame, sample_points, reps=1):
-    """Oracle port (numpy + C rANS) timed on the host cores: encode + decode of the sample."""
-    from b200pcc import config as cfgmod
+def cpu_port_run(frame, sample_points, reps=1, settings=((1.0, 1.0),)):
+    """Oracle port timed on the host cores: encode + decode.  numpy for the bookkeeping, the C/OpenMP core of
+    oracle/sparse_ref.c for kernel maps, convolutions and bf16 rounding, scalar C rans64 for the entropy coder.
+    sample_points = 0: the whole frame.  -> (points, [seconds per rep], [stage seconds per rep])"""
+    cfgmod = _load_plain("config")
     from oracle.codec_ref import RefCodec
-    sample = _crop_sample(frame, sample_points)
+    from oracle import sparse_ref as S
+    S.use_fast(True)
+    sample = _crop_sample(frame, sample_points) if sample_points else frame
     codec = RefCodec(cfgmod.SYNTH_SMALL, cfgmod.make_state_dict(), bf16=True)
     n = len(sample["points"])
-    times = []
+    times, stages = [], []
+    q = [list(x) for x in settings]
     for _ in range(reps):
         t0 = time.time()
-        blob = codec.compress([sample], [[1.0, 1.0]])
-        codec.decompress(blob, 0)
+        blob = codec.compress([sample], q)
+        _, dside = codec.decompress(blob, len(q) - 1)
         times.append(time.time() - t0)
-    return n, times
+        st = {"enc_" + k: v for k, v in blob["times"].items()}
+        st.update({"dec_" + k: v for k, v in dside["times"].items()})
+        stages.append(st)
+    return n, times, stages
+
+
+def _cpu_threads():
+    """Threads the port runs on: the OpenMP team of the C core (= host cores unless OMP_NUM_THREADS says otherwise)."""
+    from oracle import sparse_ref as S
+    return S.fast_threads()
+
+
+def cpu_cfg1_baseline(warmup=3, reps=10):
+    """cfg-1 (one synthetic 100 100-point frame, seed 0), encode + decode, Q = 1 and Q = 3,
+    3 warm-ups / 10 repetitions, p50, per-stage split with the reference's stage names
+    (sender/encoder/codec_pipeline.py:218-225, receiver/decoder/codec_parallel.py:160-167)."""
+    synth = _load_plain("synth")
+    frame = synth.frame_cpu100k(seed=0)
+    out = {"config": "cfg-1 cpu-100k", "points": int(len(frame["points"])), "warmup": warmup, "reps": reps,
+           "cores": _cpu_threads(), "kind": "port"}
+    for name, settings in (("Q1", ((1.0, 1.0),)), ("Q3", ((1.0, 0.0), (0.0, 1.0), (1.0, 1.0)))):
+        n, times, stages = cpu_port_run(frame, 0, reps=warmup + reps, settings=settings)
+        t = np.asarray(times[warmup:])
+        p50 = float(np.median(t))
+        out[name] = {"seconds_p50": p50, "mpoints_s": n / p50 / 1e6,
+                     "stage_seconds_p50": {k: float(np.median([s[k] for s in stages[warmup:]])) for k in stages[0]}}
+    return out
 
 
 def run_reference(args):
-    """--impl reference: the reference's own CPU path cannot be installed here (MinkowskiEngine,
-    CompressAI and the model submodule are unvendored), so this arm times the oracle port."""
+    """--impl reference: the reference's own CPU path (MinkowskiEngine CPU backend + CompressAI) cannot be installed
+    here (unvendored dependencies, no network), so this arm times the oracle port -- on the SAME cfg-2 frame as the
+    GPU arm (--cpu-sample N > 0 restricts it to an N-point slab and says so).  Nothing of b200pcc is imported."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from b200pcc import synth
-    frame = synth.frame_8ivfb(seed=1)
-    sample_points = args.cpu_sample
+    synth = _load_plain("synth")
+    frame = synth.frame_8ivfb(seed=1, n_target=args.points)
     steps, warmup = args.steps, args.warmup
-    n, times = cpu_port_run(frame, sample_points, reps=warmup + steps)
+    n, times, stages = cpu_port_run(frame, args.cpu_sample, reps=warmup + steps)
     t = times[warmup:]
     total = sum(t)
     value = n * len(t) / total / 1e6
-    cores = _blas_threads()
+    cores = _cpu_threads()
+    sample = (f"the whole cfg-2 frame ({n} points)" if not args.cpu_sample else f"{n}-point slab of the cfg-2 frame") + \
+        f", encode+decode, {len(t)} timed reps after {warmup} warm-ups"
+    cfg = _config(len(frame["points"]), args.gpus)
+    if args.cpu_sample:
+        cfg["workload"] += f" -- REFERENCE ARM SAMPLE: {n}-point slab"
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
         "warmup": warmup, "ms_per_step": 1e3 * total / len(t), "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "model": "synth_small (seeded weights)",
-                   "note": "CPU port of the path (numpy sparse conv + C rans64); reference deps not installable"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"{n}-point slab of the cfg-2 frame, encode+decode, {len(t)} reps"},
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": cfg,
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                         "what": "oracle port: numpy + C/OpenMP sparse ops (oracle/sparse_ref.c) + scalar C rans64; "
+                                 "MinkowskiEngine / CompressAI / the model submodule are not installable here",
+                         "stage_seconds_p50": {k: float(np.median([s[k] for s in stages[warmup:]])) for k in stages[0]}},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
+
+
+def run_cfg4(enc, dec, dev, rank, world, nframes, barrier, pool=4):
+    """cfg-4 as BASELINE.json states it: a sequence of `nframes` cfg-2-shaped frames, frame i -> rank i mod G
+    (b200pcc.shard), every rank coding its frames through the public compress() / decompress() calls with host
+    buffers; then the sequence's bitstreams are gathered on every rank (NCCL all_gather of lengths and of padded
+    payloads) OUTSIDE the timed region, its time reported.  Frame i of the sequence is pool frame i mod `pool`
+    (seeds 1000 + i mod pool): generating 300 distinct 800 k-point frames would take the host several minutes.
+    The digest of the gathered sequence must be the same for every G."""
+    import hashlib
+    import torch
+    import torch.distributed as dist
+    from b200pcc import shard
+    synth = _load_plain("synth")
+    mine = shard.frames_for_rank(nframes, rank, world)
+    frames = {j: synth.frame_8ivfb(seed=1000 + j) for j in sorted({i % pool for i in mine})}
+    for i in mine[:3]:
+        c, _ = enc.compress({"frames": [frames[i % pool]], "timestamps": {}})
+        dec.decompress(c[1])
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    local, pts = {}, 0
+    t0 = time.time()
+    e0.record()
+    for i in mine:
+        c, _ = enc.compress({"frames": [frames[i % pool]], "timestamps": {}})
+        dec.decompress(c[1])
+        local[i] = c[1]
+        pts += len(frames[i % pool]["points"])
+    e1.record()
+    e1.synchronize()
+    own_s = e0.elapsed_time(e1) * 1e-3
+    barrier()
+    wall_s = time.time() - t0
+    tg = time.time()
+    seq = shard.gather_bitstreams(local, nframes, None, dev)
+    torch.cuda.synchronize()
+    gather_s = time.time() - tg
+    stats = torch.tensor([own_s, wall_s, gather_s, float(pts)], dtype=torch.float64, device=dev)
+    if world > 1:
+        mx = stats.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = stats.clone()
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        own_s, wall_s, gather_s, pts = float(mx[0]), float(mx[1]), float(mx[2]), float(sm[3])
+    return {"config": "cfg-4 seq-300", "frames": nframes, "ranks": world, "sharding": "frame i -> rank i mod G (b200pcc.shard)",
+            "distinct_frames": pool, "points_total": int(pts), "seconds_max_over_ranks": own_s,
+            "mpoints_s": pts / own_s / 1e6, "frames_per_s": nframes / own_s, "wall_seconds_incl_barrier": wall_s,
+            "gather_seconds": gather_s, "gather": "all_gather (NCCL) of lengths + padded payloads, outside the timed region"
+            if world > 1 else "single rank: no collective", "sequence_bytes": sum(len(b) for b in seq),
+            "sequence_sha256": hashlib.sha256(b"".join(seq)).hexdigest(), "buffers": "host numpy in, host numpy out"}
+
+
+def run_configs(model, dev):
+    """cfg-1 / cfg-3 / cfg-5 of BASELINE.json on one GPU (tools/bench_configs.py holds the procedures): cfg-1 end to
+    end, cfg-3 frames arriving at 30 fps (p50 / p95 / p99 latency), cfg-5 encode time vs Q (1, 3, 25)."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import bench_configs as bc
+    return {"cfg1": bc.cfg1(model, dev, 10), "cfg3": bc.cfg3(model, dev, 120, 30.0), "cfg5": bc.cfg5(model, dev, 6)}
 
 
 def main():
@@ -154,7 +256,9 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--cpu-sample", type=int, default=150_000, help="points in the bounded CPU sample")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="CPU arm: points of a slab sample (0 = the whole frame)")
+    ap.add_argument("--no-configs", action="store_true", help="skip the cfg-1 / cfg-3 / cfg-4 / cfg-5 legs")
+    ap.add_argument("--seq-frames", type=int, default=300, help="frames of the cfg-4 sequence")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--points", type=int, default=800_000)
     ap.add_argument("--breakdown", action="store_true", help="print per-kernel-family table to stderr")
@@ -275,7 +379,25 @@ def main():
     e2e_total = sum(e2e_ms) * 1e-3
     e2e_pts = sum(n_points[i % n_frames] for i in range(e2e_steps))
 
+    e2e_h2d, e2e_d2h = enc2.h2d_bytes + dec2.h2d_bytes, enc2.d2h_bytes + dec2.d2h_bytes
+
+    # ---------------- the other BASELINE.json configurations ----------------
+    configs = None
+    if not args.no_configs:
+        configs = {"cfg4": run_cfg4(enc2, dec2, dev, rank, world, args.seq_frames, barrier)}
+        if world == 1:
+            configs.update(run_configs(model, dev))
+
     # ---------------- reduce over ranks ----------------
+    mine = torch.tensor([float(np.median(step_ms)), float(np.median(e2e_ms)) if e2e_ms else 0.0], dtype=torch.float64, device=dev)
+    if world > 1:
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        allr = torch.stack(allr).cpu().numpy()
+    else:
+        allr = mine.cpu().numpy()[None]
+    rank_stats = {"resident_p50": {"min": float(allr[:, 0].min()), "median": float(np.median(allr[:, 0])), "max": float(allr[:, 0].max())},
+                  "e2e_p50": {"min": float(allr[:, 1].min()), "median": float(np.median(allr[:, 1])), "max": float(allr[:, 1].max())}}
     if world > 1:
         t = torch.tensor([total_s, e2e_total], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -292,17 +414,19 @@ def main():
         top_name, _ = fams[0]
         # the dominant kernel = the largest launch shape of the family with the largest time share
         shapes = {}
-        for fam, nbytes, flops, e0, e1 in prof.records:
+        for fam, nbytes, flops, e0, e1, dense in prof.records:
             if fam == top_name:
-                d = shapes.setdefault(nbytes, {"launches": 0, "ms": 0.0, "bytes": 0, "flops": 0})
+                d = shapes.setdefault(nbytes, {"launches": 0, "ms": 0.0, "bytes": 0, "flops": 0, "dense": 0})
                 d["launches"] += 1
                 d["ms"] += e0.elapsed_time(e1)
                 d["bytes"] += nbytes
                 d["flops"] += flops
+                d["dense"] += dense
         top_bytes = max(shapes)
         top = shapes[top_bytes]
         gbs = top["bytes"] / (top["ms"] * 1e-3) / 1e9
-        tfs = top["flops"] / (top["ms"] * 1e-3) / 1e12
+        tfs = top["flops"] / (top["ms"] * 1e-3) / 1e12            # 2 P Cin Cout, P counted from the kernel map
+        tfs_dense = top["dense"] / (top["ms"] * 1e-3) / 1e12      # every (offset, row) incl. absent neighbours
         traffic = None
         tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
         if os.path.exists(tpath):
@@ -318,7 +442,8 @@ def main():
                 "launches_per_step": top["launches"] / prof_steps, "avg_launch_ms": top["ms"] / top["launches"],
                 "share_of_kernel_time": top["ms"] / kernel_ms,
                 "family_share_of_kernel_time": fams[0][1]["ms"] / kernel_ms, "tensor_tflops": tfs,
-                "tensor_frac": tfs / tf_peak,
+                "tensor_frac": tfs / tf_peak, "tensor_tflops_dense_equivalent": tfs_dense,
+                "pairs_per_output_row": top["flops"] / max(top["dense"], 1) * 27.0 if "_k27_" in top_name else None,
                 "note": "largest launch shape of the top family; traffic = dram read+write bytes of the same "
                         "shape from the ncu --set full capture summarised under profiles/"}
         if args.breakdown:
@@ -334,26 +459,32 @@ def main():
             "metric": METRIC, "value": pts_done / total_s / 1e6, "unit": UNIT, "n_gpus": world, "steps": steps,
             "warmup": warmup, "ms_per_step": 1e3 * total_s / steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "points_per_frame": int(n_points[0]), "frames_per_step": 1,
-                       "model": "synth_small (seeded weights; the demo_small weights are not in the reference tree)",
-                       "l2": "256 MiB flush write between timed iterations", "parallelism": f"frame-parallel x{world}"},
+            "config": _config(n_points[0], world),
             "latency_ms": {"encode_p50": float(np.median(enc_ms)), "decode_p50": float(np.median(dec_ms)),
                            "step_p50": float(np.median(step_ms))},
             "fps": steps / total_s,
             "e2e": None if not e2e_steps else {
                 "value": e2e_pts / e2e_total / 1e6, "unit": UNIT,
-                "h2d_bytes_per_step": int((enc2.h2d_bytes + dec2.h2d_bytes) / e2e_steps),
-                "d2h_bytes_per_step": int((enc2.d2h_bytes + dec2.d2h_bytes) / e2e_steps),
+                "h2d_bytes_per_step": int(e2e_h2d / e2e_steps),
+                "d2h_bytes_per_step": int(e2e_d2h / e2e_steps),
                 "ms_per_step": 1e3 * e2e_total / e2e_steps},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": roof,
         }
+        line["rank_step_ms"] = rank_stats
+        if configs is not None:
+            line["configs"] = configs
         if not args.no_cpu_baseline and world == 1:
-            n, times = cpu_port_run(frames[0], args.cpu_sample, reps=1)
-            line["cpu_baseline"] = {"value": n / times[0] / 1e6, "unit": UNIT, "cores": _blas_threads(), "kind": "port",
-                                    "sample": f"{n}-point slab of the cfg-2 frame, encode+decode once "
-                                              f"({times[0]:.1f} s; numpy BLAS threads + scalar C rANS)"}
+            # the same workload on the host cores: ONE encode + decode of the whole cfg-2 frame (about 10 s of CPU
+            # work), then BASELINE.md section 3's procedure on cfg-1 (3 warm-ups, 10 repetitions, p50, stage split)
+            n, times, stages = cpu_port_run(frames[0], args.cpu_sample, reps=1)
+            line["cpu_baseline"] = {"value": n / times[0] / 1e6, "unit": UNIT, "cores": _cpu_threads(), "kind": "port",
+                                    "sample": (f"the whole cfg-2 frame ({n} points)" if not args.cpu_sample else
+                                               f"{n}-point slab of the cfg-2 frame") +
+                                              f", encode+decode once ({times[0]:.1f} s; numpy + C/OpenMP sparse ops + scalar C rans64)",
+                                    "stage_seconds": stages[0],
+                                    "cfg1": cpu_cfg1_baseline()}
         else:
             line["cpu_baseline"] = None
         os.write(json_fd, (json.dumps(line) + "\n").encode())

@@ -43,6 +43,7 @@ SIGNATURES = {
     "pcc_version": (INT, []),
     "pcc_last_error": (C.c_char_p, []),
     "pcc_launch_count": (I64, []),
+    "pcc_kmap_count_pairs": (INT, [P, I64, I64, INT, P, P]),
     "pcc_fault_fetch": (INT, [P, P]),
     "pcc_fault_string": (C.c_char_p, [I32]),
     "pcc_debug_inject": (INT, [I32]),

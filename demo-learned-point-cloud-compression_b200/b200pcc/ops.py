@@ -22,19 +22,22 @@ _TLS = threading.local()
 
 class KernelProfiler:
     """Optional per-family CUDA-event timing on the launching stream (bench.py's roofline leg).
-    A record is (family, algorithmic bytes, flops, start event, stop event)."""
+    A record is (family, algorithmic bytes, flops, start event, stop event, dense-equivalent flops): `flops` is
+    2 P Cin Cout with P the pairs counted from the kernel map, the dense equivalent counts every
+    (offset, output row) whether a neighbour exists or not -- what the tensor pipe actually executes."""
 
     def __init__(self):
         self.records = []
 
     def summary(self):
         out = {}
-        for fam, nbytes, flops, e0, e1 in self.records:
-            d = out.setdefault(fam, {"launches": 0, "ms": 0.0, "bytes": 0, "flops": 0})
+        for fam, nbytes, flops, e0, e1, dense in self.records:
+            d = out.setdefault(fam, {"launches": 0, "ms": 0.0, "bytes": 0, "flops": 0, "dense_flops": 0})
             d["launches"] += 1
             d["ms"] += e0.elapsed_time(e1)
             d["bytes"] += nbytes
             d["flops"] += flops
+            d["dense_flops"] += dense
         return out
 
 
@@ -42,8 +45,9 @@ PROFILER = None
 
 
 class _prof:
-    def __init__(self, family, nbytes=0, flops=0):
+    def __init__(self, family, nbytes=0, flops=0, dense_flops=None):
         self.family, self.nbytes, self.flops = family, int(nbytes), int(flops)
+        self.dense = int(flops if dense_flops is None else dense_flops)
 
     def __enter__(self):
         if PROFILER is not None:
@@ -55,8 +59,15 @@ class _prof:
         if PROFILER is not None:
             e1 = torch.cuda.Event(enable_timing=True)
             e1.record()
-            PROFILER.records.append((self.family, self.nbytes, self.flops, self.e0, e1))
+            PROFILER.records.append((self.family, self.nbytes, self.flops, self.e0, e1, self.dense))
         return False
+
+
+def kmap_pairs(nbr_ptr: int, nbr_ld: int, n_out: int, kvol: int, device) -> int:
+    """Pairs of a kernel map given by raw address (measurement only: synchronises)."""
+    cnt = torch.empty(1, dtype=torch.int64, device=device)
+    check(lib.pcc_kmap_count_pairs(nbr_ptr, nbr_ld, n_out, kvol, cnt.data_ptr(), _stream()))
+    return int(cnt.item())
 
 
 def _stream() -> int:
@@ -637,7 +648,8 @@ def spconv_umma(x: torch.Tensor, nbr: Optional[torch.Tensor], n_out: int, kvol: 
     cw = cstore if 0 < cstore < cout else cout
     nbytes = 2 * n_in * cin + n_out * (cw * ((2 if ob else 0) + (4 if of else 0)) + cout * (2 if rp else 0)) + \
         (4 * kvol * n_out if nbr is not None else 0) + 2 * kvol * cin * cout
-    with _prof(f"spconv_umma_k{kvol}_c{cin}x{cout}", nbytes, 2 * kvol * n_out * cin * cout):
+    pairs = kmap_pairs(nbr_p, nbr_ld, n_out, kvol, x.device) if nbr is not None else n_out
+    with _prof(f"spconv_umma_k{kvol}_c{cin}x{cout}", nbytes, 2 * pairs * cin * cout, 2 * kvol * n_out * cin * cout):
         check(lib.pcc_spconv_umma(x.data_ptr(), n_in, cin, nbr_p, nbr_ld, n_out, kvol, w_packed.data_ptr(), bias_p, cout,
                                   rp, ldr, int(relu), ob, of, ldo, cstore, _stream()))
 

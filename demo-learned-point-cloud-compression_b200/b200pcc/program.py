@@ -155,15 +155,16 @@ class Program:
             cw = cstore if 0 < cstore < cout else cout
             nbytes = 2 * n_in * cin + n_out * (cw * ((2 if ob else 0) + (4 if of else 0)) + cout * (2 if res else 0)) + \
                 (4 * kvol * n_out if nbr else 0) + 2 * kvol * cin * cout
-            return f"spconv_umma_k{kvol}_c{cin}x{cout}", nbytes, 2 * kvol * n_out * cin * cout
+            pairs = ops.kmap_pairs(nbr, int(a[4]), n_out, kvol, self.device) if nbr else n_out
+            return f"spconv_umma_k{kvol}_c{cin}x{cout}", nbytes, 2 * pairs * cin * cout, 2 * kvol * n_out * cin * cout
         if op == OP_KMAP_K3_BLOCKS:
-            return "kmap_k3", int(a[1]) * (8 + 27 * 4), 0
+            return "kmap_k3", int(a[1]) * (8 + 27 * 4), 0, 0
         if op == OP_BLOCKMAP_BUILD:
-            return "blockmap_build", int(a[1]) * 8 + int(a[5]) * 8 + (int(a[1]) // 8) * 24, 0
+            return "blockmap_build", int(a[1]) * 8 + int(a[5]) * 8 + (int(a[1]) // 8) * 24, 0, 0
         if op == OP_TOPK_SELECT:
-            return "topk_select", int(a[2]) * 16, 0
+            return "topk_select", int(a[2]) * 16, 0, 0
         return {OP_KMAP_DOWN2: "kmap_down2", OP_ROWS_F32_TO_BF16: "rows_f32_to_bf16", OP_COORDS_CHILDREN: "coords_children",
-                OP_GATHER_ROWS_BF16: "gather_rows", OP_GATHER_KEYS: "gather_keys", OP_FRAME_OFFSETS: "frame_offsets"}[op], 0, 0
+                OP_GATHER_ROWS_BF16: "gather_rows", OP_GATHER_KEYS: "gather_keys", OP_FRAME_OFFSETS: "frame_offsets"}[op], 0, 0, 0
 
     def flush(self) -> None:
         """Run the entries recorded so far and start an empty table over the SAME arena: the GPU gets the
@@ -187,6 +188,6 @@ class Program:
             return
         table = np.frombuffer(self.words, dtype=np.int64).reshape(self.n, _ROW)
         for i in range(self.n):
-            fam, nbytes, flops = self._family(table[i])
-            with ops._prof(fam, nbytes, flops):
+            fam, nbytes, flops, dense = self._family(table[i])
+            with ops._prof(fam, nbytes, flops, dense):
                 check(lib.pcc_run_program(addr + i * _ROW * 8, 1, st, C.byref(failed)))

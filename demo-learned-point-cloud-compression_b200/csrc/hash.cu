@@ -308,6 +308,21 @@ k_kmap_k3_blocks(const uint64_t* __restrict__ keys, int64_t n, int l, const uint
   }
 }
 
+// number of kernel-map entries that name a row (the P of SURVEY 8d's flop count 2 P Cin Cout)
+__global__ void k_kmap_count_pairs(const int32_t* __restrict__ nbr, int64_t ld, int64_t n_out, int kvol,
+                                   unsigned long long* __restrict__ count) {
+  pdl_trigger();
+  pdl_wait();
+  unsigned long long c = 0;
+  const int64_t total = (int64_t)kvol * n_out;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t j = i / n_out, o = i - j * n_out;
+    c += nbr[j * ld + o] >= 0;
+  }
+  c = __reduce_add_sync(0xffffffffu, (unsigned)c);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(count, c);
+}
+
 }  // namespace pcc
 
 using namespace pcc;
@@ -397,6 +412,17 @@ int pcc_kmap_k3_blocks(const uint64_t* keys, int64_t n, int log2_stride, const u
   PCC_CHECK_ARG(keys && table_keys && table_vals16 && nbr);
   launch_pdl(k_kmap_k3_blocks, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, as_stream(s), keys, n, log2_stride, table_keys, (const ulonglong2*)table_vals16, (uint64_t)capacity - 1, nbr,
       nbr_ld);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+
+int pcc_kmap_count_pairs(const int32_t* nbr, int64_t nbr_ld, int64_t n_out, int kvol, int64_t* count_dev, pcc_stream_t s) {
+  PCC_CHECK_ARG(n_out >= 0 && kvol >= 1 && nbr_ld >= n_out && count_dev);
+  cudaStream_t st = as_stream(s);
+  PCC_CUDA(cudaMemsetAsync(count_dev, 0, 8, st));
+  if (n_out == 0) return PCC_OK;
+  PCC_CHECK_ARG(nbr);
+  launch_pdl(k_kmap_count_pairs, dim3(592), dim3(256), 0, st, nbr, nbr_ld, n_out, kvol, (unsigned long long*)count_dev);
   PCC_LAUNCHED();
   return PCC_OK;
 }

@@ -149,6 +149,9 @@ int pcc_kmap_k3_blocks(const uint64_t* keys, int64_t n, int log2_stride, const u
                        pcc_stream_t s);
 /* Kernel map of a k=2, stride-2 convolution: nbr[j*nbr_ld + p] = child row with octant j or -1
  * (row pitch nbr_ld >= n_parent; see pcc_spconv_umma for why the pitch is padded). */
+/* Measurement helper: count_dev (device int64) = number of entries >= 0 in a kernel map [kvol][nbr_ld] restricted
+ * to its first n_out columns -- the pair count P of a sparse convolution (flops = 2 P Cin Cout). */
+int pcc_kmap_count_pairs(const int32_t* nbr, int64_t nbr_ld, int64_t n_out, int kvol, int64_t* count_dev, pcc_stream_t s);
 int pcc_kmap_down2(const uint64_t* child_keys, const int32_t* parent_row, int64_t n_child,
                    int log2_child_stride, int32_t* nbr, int64_t n_parent, int64_t nbr_ld,
                    pcc_stream_t s);
