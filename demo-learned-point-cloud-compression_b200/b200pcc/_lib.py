@@ -80,6 +80,9 @@ SIGNATURES = {
     "pcc_spconv_packed_weight_bytes": (I64, [INT, INT, INT]),
     "pcc_spconv_pack_weights": (INT, [P, INT, INT, INT, INT, P]),
     "pcc_spconv_umma": (INT, [P, I64, INT, P, I64, I64, INT, P, P, INT, P, I64, INT, P, P, I64, INT, P]),
+    "pcc_spconv_octet_packed_weight_bytes": (I64, [INT, INT]),
+    "pcc_spconv_octet_pack_weights": (INT, [P, INT, INT, INT, P]),
+    "pcc_spconv_octet": (INT, [P, I64, INT, P, I64, P, P, INT, P, I64, INT, P, P, I64, INT, P]),
     "pcc_spconv_set_tuning": (INT, [INT, INT, INT]),
     "pcc_spconv_simt": (INT, [P, I64, INT, P, I64, INT, P, P, INT, P, I64, INT, P, P, I64, P]),
     "pcc_rows_f32_to_bf16": (INT, [P, INT, P, I64, P, INT, P]),

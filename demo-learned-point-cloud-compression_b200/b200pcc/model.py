@@ -35,6 +35,9 @@ TAIL_MASS = 1e-9
 # per-layer path stays: it is the readable statement of the graph, serves return_intermediates and
 # degenerate (empty) inputs, and the tests require both paths to agree bit for bit.
 USE_PROGRAMS = True
+# k3 convolutions on the un-pruned candidates of a g_s level (complete octets) through pcc_spconv_octet with the
+# parents' kernel map, where the layer shape allows it (C_in = 32); False = the general kernel on the children's map.
+USE_OCTET = True
 
 
 def _pad16(c: int) -> int:
@@ -81,7 +84,21 @@ class Conv:
             self.bias_d = torch.from_numpy(b).to(device)
         else:
             self.w_d = ops.pack_weights_umma(self.kernel, self.cin_pad).to(device)
+        self.w_oct = None
+        if not self.simt and self.kvol == 27 and self.cin == 32 and self.cin_pad == 32 and (self.narrow or self.cout == 32):
+            self.w_oct = ops.pack_weights_octet(self.kernel, 16 if self.narrow else 32).to(device)
         return self
+
+    def octet(self, x: torch.Tensor, nbr_par: torch.Tensor, n_par: int, relu=False, residual: Optional[torch.Tensor] = None):
+        """The same layer on complete octets (x: bf16 [8 n_par, 32]) with the parents' kernel map."""
+        dev = x.device
+        if self.narrow:
+            out = torch.empty((8 * n_par, self.cout), dtype=torch.float32, device=dev)
+            ops.spconv_octet(x, nbr_par, n_par, self.w_oct, self.bias_d, 16, None, relu, None, out, cstore=self.cout)
+            return out
+        out = torch.empty((8 * n_par, self.cout), dtype=torch.bfloat16, device=dev)
+        ops.spconv_octet(x, nbr_par, n_par, self.w_oct, self.bias_d, self.cout, residual, relu, out, None)
+        return out
 
     def __call__(self, x: torch.Tensor, nbr: Optional[torch.Tensor], n_out: int, relu=False,
                  residual: Optional[torch.Tensor] = None, out_f32=False):
@@ -317,11 +334,20 @@ class SynthesisTransform(_Module):
         kd_all = torch.tensor([list(map(int, k[i])) for i in range(3)], dtype=torch.int32).to(dev, non_blocking=True)
         for i in range(3):
             f = self.up[i](f, relu=True)
+            parent = cm
             cm = cm.children()
             blk = self.blocks[i]
-            for b in range(0, len(blk), 2):
-                f = _resblock(blk[b], blk[b + 1], cm, f)
-            logits = self.occ[i](f, cm.nbr3(), cm.n)
+            if USE_OCTET and self.occ[i].w_oct is not None and all(c.w_oct is not None for c in blk):
+                # candidates = complete octets: the parents' kernel map drives every k3 layer of the level
+                nbp = parent.nbr3()
+                for b in range(0, len(blk), 2):
+                    h = blk[b].octet(f, nbp, parent.n, relu=True)
+                    f = blk[b + 1].octet(h, nbp, parent.n, relu=True, residual=f)
+                logits = self.occ[i].octet(f, nbp, parent.n)
+            else:
+                for b in range(0, len(blk), 2):
+                    f = _resblock(blk[b], blk[b + 1], cm, f)
+                logits = self.occ[i](f, cm.nbr3(), cm.n)
             off = ops.frame_offsets(cm.keys, num_frames)
             expect = None
             if prev is not None:
@@ -374,11 +400,20 @@ def _synthesis_program(self, f, cm, k, num_frames, prev, on_geometry=None):
         ck = pr.alloc(nc * 8)
         l2 -= 1
         pr.add(prg.OP_COORDS_CHILDREN, keys_ptr, n, l2, ck)
-        up1, up2 = n, up1
-        nb, ld = pr.kmap_k3(ck, nc, l2, up2 if up2 is not None else up1)
-        cur = pr.resblocks(self.blocks[i], cur, nc, c, nb, ld)
+        octet = USE_OCTET and self.occ[i].w_oct is not None and all(cv.w_oct is not None for cv in self.blocks[i])
         logits = pr.alloc(nc * 4)
-        pr.conv(self.occ[i], cur, nc, nb, ld, nc, out_f32=logits)
+        if octet:
+            # the level's k3 layers run on complete octets: kernel map of the n parents, not of the 8 n children
+            bound_par = up2 if up2 is not None else (up1 if up1 is not None else n)
+            nbp, ldp = pr.kmap_k3(keys_ptr, n, l2 + 1, bound_par)
+            cur = pr.resblocks_octet(self.blocks[i], cur, n, c, nbp, ldp)
+            pr.conv_octet(self.occ[i], cur, n, nbp, ldp, out_f32=logits)
+            up1, up2 = n, up1
+        else:
+            up1, up2 = n, up1
+            nb, ld = pr.kmap_k3(ck, nc, l2, up2 if up2 is not None else up1)
+            cur = pr.resblocks(self.blocks[i], cur, nc, c, nb, ld)
+            pr.conv(self.occ[i], cur, nc, nb, ld, nc, out_f32=logits)
         off = pr.alloc((num_frames + 1) * 4)
         pr.add(prg.OP_FRAME_OFFSETS, ck, nc, num_frames, off)
         m = sum(kept_l[i])

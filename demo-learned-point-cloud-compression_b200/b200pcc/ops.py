@@ -654,6 +654,66 @@ def spconv_umma(x: torch.Tensor, nbr: Optional[torch.Tensor], n_out: int, kvol: 
                                   rp, ldr, int(relu), ob, of, ldo, cstore, _stream()))
 
 
+_OCTET_BLOCKS = None
+
+
+def _octet_pairs(nbr_ptr: int, nbr_ld: int, n_par: int, device) -> int:
+    """Child-level pairs of an octet convolution from its PARENT map (measurement only): a present parent offset D
+    stands for 4^(number of zero axes of D) (source child, output child) blocks."""
+    global _OCTET_BLOCKS
+    if _OCTET_BLOCKS is None:
+        _OCTET_BLOCKS = [4 ** [dx, dy, dz].count(0) for dz in (-1, 0, 1) for dy in (-1, 0, 1) for dx in (-1, 0, 1)]
+    return sum(_OCTET_BLOCKS[j] * kmap_pairs(nbr_ptr + 4 * j * nbr_ld, nbr_ld, n_par, 1, device) for j in range(27))
+
+
+def pack_weights_octet(w: np.ndarray, cout_pad: int) -> torch.Tensor:
+    """w float32 [27, 32, cout] -> panels for pcc_spconv_octet (uint8 CPU tensor), columns padded to cout_pad."""
+    w = np.ascontiguousarray(w, dtype=np.float32)
+    kvol, cin, cout = w.shape
+    if kvol != 27:
+        raise _lib.PccError("octet weights need a k = 3 kernel")
+    out = np.empty(lib.pcc_spconv_octet_packed_weight_bytes(cin, cout_pad), dtype=np.uint8)
+    check(lib.pcc_spconv_octet_pack_weights(w.ctypes.data, cin, cout, cout_pad, out.ctypes.data))
+    return torch.from_numpy(out)
+
+
+def spconv_octet(x: torch.Tensor, nbr_par: torch.Tensor, n_par: int, w_packed: torch.Tensor, bias: Optional[torch.Tensor],
+                 cout: int, residual: Optional[torch.Tensor] = None, relu: bool = False,
+                 out_bf16: Optional[torch.Tensor] = None, out_f32: Optional[torch.Tensor] = None, cstore: int = 0) -> None:
+    """k3 convolution on complete octets (x has 8 n_par rows; nbr_par is the PARENTS' [27, n_par] kernel map)."""
+    if not x.is_cuda or x.dtype is not torch.bfloat16 or not x.is_contiguous() or x.shape[0] != 8 * n_par:
+        raise _lib.PccError("spconv_octet: expected a contiguous CUDA bfloat16 matrix with 8 rows per parent")
+    nbr_ld, cs = nbr_par.stride()
+    if cs != 1 or nbr_par.dtype is not torch.int32:
+        raise _lib.PccError("kernel map must be int32 [27, n] with unit column stride")
+    ob = None if out_bf16 is None else out_bf16.data_ptr()
+    of = None if out_f32 is None else out_f32.data_ptr()
+    ldo = (out_bf16 if out_bf16 is not None else out_f32).shape[1]
+    rp, ldr = (None, 0) if residual is None else (residual.data_ptr(), residual.shape[1])
+    bias_p = None if bias is None else bias.data_ptr()
+    args = (x.data_ptr(), n_par, x.shape[1], nbr_par.data_ptr(), nbr_ld, w_packed.data_ptr(), bias_p, cout, rp, ldr,
+            int(relu), ob, of, ldo, cstore, _stream())
+    if PROFILER is None:
+        rc = lib.pcc_spconv_octet(*args)
+        if rc:
+            check(rc)
+        return
+    fam, nbytes, flops, dense = octet_family(x.shape[1], cout, cstore, n_par, bool(ob), bool(of), bool(rp),
+                                             nbr_par.data_ptr(), nbr_ld, x.device)
+    with _prof(fam, nbytes, flops, dense):
+        check(lib.pcc_spconv_octet(*args))
+
+
+def octet_family(cin, cout, cstore, n_par, has_bf16, has_f32, has_res, nbr_ptr, nbr_ld, device):
+    """(family, algorithmic bytes, flops from counted pairs, dense-equivalent flops) of one pcc_spconv_octet launch."""
+    n = 8 * n_par
+    cw = cstore if 0 < cstore < cout else cout
+    nbytes = 2 * n * cin + n * (cw * ((2 if has_bf16 else 0) + (4 if has_f32 else 0)) + cout * (2 if has_res else 0)) + \
+        4 * 27 * n_par + 2 * 27 * cin * cout
+    pairs = _octet_pairs(nbr_ptr, nbr_ld, n_par, device)
+    return f"spconv_octet_k27_c{cin}x{cout}", nbytes, 2 * pairs * cin * cout, 2 * 27 * n * cin * cout
+
+
 def spconv_simt(x: torch.Tensor, nbr: Optional[torch.Tensor], n_out: int, kvol: int, w_bf16: torch.Tensor,
                 bias: Optional[torch.Tensor], cout: int, residual: Optional[torch.Tensor] = None,
                 relu: bool = False, out_bf16: Optional[torch.Tensor] = None,

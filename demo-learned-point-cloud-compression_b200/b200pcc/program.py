@@ -29,6 +29,7 @@ OP_GATHER_ROWS_BF16 = 7
 OP_GATHER_KEYS = 8
 OP_FRAME_OFFSETS = 9
 OP_TOPK_SELECT = 10
+OP_SPCONV_OCTET = 11
 
 _ROW = 20          # int64 words per entry: op + 19 arguments (pcc_op_t)
 _TLS = threading.local()
@@ -109,6 +110,24 @@ class Program:
         self.add(OP_SPCONV_UMMA, in_ptr, n_in, conv.cin_pad, nbr_ptr, nbr_ld, n_out, conv.kvol, conv.w_d.data_ptr(),
                  conv.bias_d.data_ptr(), cout, residual, ldr, int(relu), out_bf16, out_f32, ldo or conv.cout, cstore)
 
+    def conv_octet(self, conv, in_ptr: int, n_par: int, nbr_ptr: int, nbr_ld: int, out_bf16: int = 0, out_f32: int = 0,
+                   relu: bool = False, residual: int = 0, ldr: int = 0) -> None:
+        """One k3 model.Conv on complete octets through pcc_spconv_octet (parents' kernel map)."""
+        cout = 16 if conv.narrow else conv.cout
+        cstore = conv.cout if conv.narrow else 0
+        self.add(OP_SPCONV_OCTET, in_ptr, n_par, conv.cin_pad, nbr_ptr, nbr_ld, conv.w_oct.data_ptr(), conv.bias_d.data_ptr(),
+                 cout, residual, ldr, int(relu), out_bf16, out_f32, conv.cout, cstore)
+
+    def resblocks_octet(self, blk, cur: int, n_par: int, c: int, nb: int, ld: int) -> int:
+        n = 8 * n_par
+        for b in range(0, len(blk), 2):
+            h = self.alloc(n * c * 2)
+            self.conv_octet(blk[b], cur, n_par, nb, ld, out_bf16=h, relu=True)
+            o = self.alloc(n * c * 2)
+            self.conv_octet(blk[b + 1], h, n_par, nb, ld, out_bf16=o, relu=True, residual=cur, ldr=c)
+            cur = o
+        return cur
+
     def gen_up(self, up, in_ptr: int, n: int, relu: bool = True) -> int:
         """model.GenUp (dense form of the k2/s2 generative transpose) -> address of [8n, cout] bf16."""
         out = self.alloc(n * 8 * up.cout * 2)
@@ -157,6 +176,9 @@ class Program:
                 (4 * kvol * n_out if nbr else 0) + 2 * kvol * cin * cout
             pairs = ops.kmap_pairs(nbr, int(a[4]), n_out, kvol, self.device) if nbr else n_out
             return f"spconv_umma_k{kvol}_c{cin}x{cout}", nbytes, 2 * pairs * cin * cout, 2 * kvol * n_out * cin * cout
+        if op == OP_SPCONV_OCTET:
+            return ops.octet_family(int(a[2]), int(a[7]), int(a[14]), int(a[1]), bool(a[11]), bool(a[12]), bool(a[8]),
+                                    int(a[3]), int(a[4]), self.device)
         if op == OP_KMAP_K3_BLOCKS:
             return "kmap_k3", int(a[1]) * (8 + 27 * 4), 0, 0
         if op == OP_BLOCKMAP_BUILD:

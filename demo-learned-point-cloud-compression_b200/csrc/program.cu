@@ -52,6 +52,11 @@ int pcc_run_program(const pcc_op_t* ops, int32_t n_ops, pcc_stream_t s, int32_t*
         rc = pcc_topk_select((const float*)a[0], (const uint64_t*)a[1], a[2], (const int32_t*)a[3], (const int32_t*)a[4],
                              (int32_t)a[5], (int32_t*)a[6], (int32_t*)a[7], (void*)a[8], a[9], s);
         break;
+      case PCC_OP_SPCONV_OCTET:
+        rc = pcc_spconv_octet((const void*)a[0], a[1], (int)a[2], (const int32_t*)a[3], a[4], (const void*)a[5],
+                              (const float*)a[6], (int)a[7], (const void*)a[8], a[9], (int)a[10], (void*)a[11],
+                              (float*)a[12], a[13], (int)a[14], s);
+        break;
       default:
         set_error("pcc_run_program: unknown op %lld at entry %d", (long long)ops[i].op, (int)i);
         rc = PCC_E_INVALID;

@@ -219,6 +219,20 @@ int pcc_spconv_umma(const void* in_bf16, int64_t n_in, int cin, const int32_t* n
                     int64_t n_out, int kvol, const void* w_packed, const float* bias, int cout,
                     const void* residual_bf16, int64_t ldr, int relu, void* out_bf16,
                     float* out_f32, int64_t ldo, int cstore, pcc_stream_t s);
+/* The same convolution (k = 3, stride 1, C_in = 32) on a coordinate set made of COMPLETE OCTETS -- the un-pruned
+ * output of a generative transposed convolution, where the residual blocks and the occupancy head of every g_s level
+ * run (receiver/decoder/codec_parallel.py:469): row 8p + o is child o = ox + 2 oy + 4 oz of parent p (pcc_coords_children).
+ * Takes the kernel map of the PARENTS (pcc_kmap_k3_blocks on the parent keys at their stride: [27][nbr_ld], nbr_ld a
+ * multiple of 4 and >= n_parents rounded up to 128) instead of the 8x larger map of the children; in / out / residual
+ * have 8 n_parents rows.  cout = 32, or 16 for a narrow head (cstore < 16 columns stored, like pcc_spconv_umma).
+ * Weights are packed by pcc_spconv_octet_pack_weights from the ME layout w [27, cin, cout_src] (columns cout_src..cout
+ * zero).  Results equal pcc_spconv_umma's on the children's own kernel map up to fp32 summation order. */
+int64_t pcc_spconv_octet_packed_weight_bytes(int cin, int cout);
+int pcc_spconv_octet_pack_weights(const float* w, int cin, int cout_src, int cout, void* packed_host);
+int pcc_spconv_octet(const void* in_bf16, int64_t n_parents, int cin, const int32_t* nbr_parents, int64_t nbr_ld,
+                     const void* w_packed, const float* bias, int cout, const void* residual_bf16, int64_t ldr, int relu,
+                     void* out_bf16, float* out_f32, int64_t ldo, int cstore, pcc_stream_t s);
+
 /* Tuning knobs of pcc_spconv_umma (process wide; defaults 0, 4, 0): number of gather groups = ring
  * slots (0 = chosen from the channel count, else 1, 2, 4 or 5) and the maximum number T of 128-row
  * tiles gathered per stage and accumulated concurrently (1, 2 or 4).  use_cg must be 0 (the
@@ -344,6 +358,7 @@ int pcc_rans_decode(const uint8_t* container, int64_t container_bytes, int32_t s
 #define PCC_OP_GATHER_KEYS 8
 #define PCC_OP_FRAME_OFFSETS 9
 #define PCC_OP_TOPK_SELECT 10
+#define PCC_OP_SPCONV_OCTET 11
 typedef struct {
   int64_t op;
   int64_t a[19];

@@ -259,3 +259,64 @@ def test_topk_select_edge_cases(dev, case):
     ref = np.nonzero(S.topk_mask(logits, Ck, ks))[0]
     assert np.array_equal(keep, ref)
     assert len(keep) == sum(min(k, int(c)) for k, c in zip(ks, cnt))
+
+
+@pytest.mark.parametrize("n_target,stride_log2", [(3000, 1), (40000, 1), (40000, 2), (150000, 1)])
+def test_octet_conv_vs_oracle_and_general_kernel(dev, n_target, stride_log2):
+    """pcc_spconv_octet (k3 convolution on complete octets, driven by the PARENTS' kernel map) against the oracle
+    on the children's own kernel map and against pcc_spconv_umma: residual layer (bf16 out), plain layer, and the
+    narrow occupancy head (one fp32 column); several frames, tiles with a ragged tail, repeated launches identical."""
+    from b200pcc import synth, ops
+    from b200pcc.sparse import CoordMap
+    frames = [synth.small_frame(seed=61, n_target=n_target), synth.small_frame(seed=62, n_target=max(n_target // 3, 500), offset=(40, 3, -7))]
+    C, _ = stack_frames(frames)
+    t = 1 << stride_log2
+    Cp = S.stride_coords(C, t)                                             # parents at tensor stride t
+    pk, _ = ops.sort_unique(ops.keys_from_coords(torch.from_numpy(np.ascontiguousarray(Cp)).to(dev)))
+    parent = CoordMap(pk, stride_log2)
+    child = parent.children()                                              # rows 8p + o at stride t / 2
+    n_par, n = parent.n, child.n
+    assert n == 8 * n_par
+    Cc = ops.coords_from_keys(child.keys).cpu().numpy()
+    rng = np.random.default_rng(n_target + stride_log2)
+    F = rng.normal(0, 1, (n, 32)).astype(np.float32)
+    R = rng.normal(0, 1, (n, 32)).astype(np.float32)
+    W = (rng.normal(0, 1, (27, 32, 32)) / np.sqrt(32 * 14)).astype(np.float32)
+    Wh = (rng.normal(0, 1, (27, 32, 1)) / np.sqrt(32 * 14)).astype(np.float32)
+    b = rng.normal(0, 0.1, 32).astype(np.float32)
+    bh = np.array([0.3], np.float32)
+    x, r = _bf16_t(F, dev), _bf16_t(R, dev)
+    nbp = parent.nbr3()
+    nbc = child.nbr3()
+    nbc_np = nbc.cpu().numpy()
+    assert np.array_equal(nbc_np, S.kernel_map(Cc, Cc, S.region_offsets(3, t // 2)))
+    wo = ops.pack_weights_octet(W, 32).to(dev)
+    bd = torch.from_numpy(b).to(dev)
+    # residual + ReLU layer, bf16 output
+    got = torch.empty((n, 32), dtype=torch.bfloat16, device=dev)
+    ops.spconv_octet(x, nbp, n_par, wo, bd, 32, r, True, got, None)
+    ref = S.conv_forward(S.bf16_round(F), nbc_np, W, b, residual=S.bf16_round(R), relu=True, bf16=True)
+    g = got.float().cpu().numpy()
+    # bf16 output: half a bf16 step on top of the fp32 tolerance
+    np.testing.assert_allclose(g, ref, rtol=RTOL + 2.0 ** -8, atol=ATOL)
+    ob, of = _run_umma(ops, x, nbc, n, W, b, relu=True, residual=r)
+    assert (ob != got).float().mean().item() < 0.02                        # same values up to summation order (rare bf16 flips)
+    np.testing.assert_allclose(g, ob.float().cpu().numpy(), rtol=2.0 ** -7, atol=ATOL)
+    # plain layer, fp32 output
+    of2 = torch.empty((n, 32), dtype=torch.float32, device=dev)
+    ops.spconv_octet(x, nbp, n_par, wo, bd, 32, None, False, None, of2)
+    ref2 = S.conv_forward(S.bf16_round(F), nbc_np, W, b, bf16=True)
+    np.testing.assert_allclose(of2.cpu().numpy(), ref2, rtol=RTOL, atol=ATOL)
+    # narrow head: one fp32 column
+    wh = ops.pack_weights_octet(Wh, 16).to(dev)
+    bh16 = torch.zeros(16, dtype=torch.float32, device=dev)
+    bh16[0] = float(bh[0])
+    lg = torch.full((n, 1), float("nan"), dtype=torch.float32, device=dev)
+    ops.spconv_octet(x, nbp, n_par, wh, bh16, 16, None, False, None, lg, cstore=1)
+    refh = S.conv_forward(S.bf16_round(F), nbc_np, Wh, bh, bf16=True)
+    np.testing.assert_allclose(lg.cpu().numpy(), refh, rtol=RTOL, atol=ATOL)
+    # deterministic run to run
+    again = torch.empty_like(got)
+    ops.spconv_octet(x, nbp, n_par, wo, bd, 32, r, True, again, None)
+    assert torch.equal(again, got)
+    ops.verify_deferred(device=dev)                                        # no fault word left behind
