@@ -47,6 +47,8 @@ SIGNATURES = {
     "pcc_fault_fetch": (INT, [P, P]),
     "pcc_fault_string": (C.c_char_p, [I32]),
     "pcc_debug_inject": (INT, [I32]),
+    "pcc_debug_trace_words": (I64, []),
+    "pcc_debug_trace": (INT, [P]),
     "pcc_keys_from_coords_i32": (INT, [P, I64, P, P]),
     "pcc_keys_from_coords_f32": (INT, [P, I64, P, P]),
     "pcc_ingest_frame": (INT, [P, P, I64, I32, P, P, P]),

@@ -54,6 +54,10 @@ const char* pcc_fault_string(int32_t code);
 /* Test hook: what = 1 makes the next k = 3 pcc_spconv_umma launch of this process drop one pipeline hand-off (and spin
  * briefly instead of for seconds), so that the timeout path can be exercised; 0 disarms. */
 int pcc_debug_inject(int32_t what);
+/* Debug hook: the next cout = 32 pcc_spconv_octet launch records per-stage timestamps (globaltimer, ns) of its CTA 0 into
+ * buf (device memory, pcc_debug_trace_words() int64 words): tools/octet_trace.py prints the pipeline timeline. */
+int64_t pcc_debug_trace_words(void);
+int pcc_debug_trace(long long* buf);
 
 /* ------------------------------------------------------------------------------------------
  * (1) coordinates, hash, kernel maps

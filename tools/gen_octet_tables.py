@@ -2,7 +2,7 @@
 
 A k3 convolution on COMPLETE octets (children 8p+o of parent p, o = ox + 2 oy + 4 oz) equals a k3 convolution on the
 parents with block-sparse weights: child o' of the neighbour parent p + D contributes to child o of p through
-W[d], d = 2 D + o' - o, whenever d is in {-1,0,1}^3.  A tile (128 parents) is processed in 16 stages of 4 units;
+W[d], d = 2 D + o' - o, whenever d is in {-1,0,1}^3.  A tile (128 parents) is processed in 16 stages of 4 units (+ 4 half-filled stages for a residual input);
 a unit = (parent offset D, source child o') = one gathered [128 x Cin] A operand.
   c_unit[S][u]       = jD | o' << 8                       (jD = (Dx+1) + 3 (Dy+1) + 9 (Dz+1))
   c_mma[S][u][mw]    = valid | n2 << 1 | q << 2 | col << 8   issuer mw owns the output children (ox, oy, oz) with
@@ -81,13 +81,21 @@ def main():
         unit_tab.append(row_u)
         mma_tab.append(row_m)
     assert blocks == 216 and pairs == 144, (blocks, pairs)
+    # stages 16..19: the residual rows of the tile (children 2r, 2r+1 of the parent itself, read from the residual
+    # tensor) times the identity panel (slot 27): only issuer r has work in stage 16 + r; units 2, 3 stay empty
+    for r in range(4):
+        unit_tab.append([13 | ((2 * r) << 8), 13 | ((2 * r + 1) << 8), 0xffff, 0xffff])
+        row = []
+        for u in range(4):
+            row.append([(1 | (27 << 2) | ((2 * r + u) << 8)) if (mw == r and u < 2) else 0 for mw in range(4)])
+        mma_tab.append(row)
     # first MMA of a tile for every issuer is (stage 0, unit 0): it initialises both of the issuer's column blocks
     assert all((m & 3) == 3 for m in mma_tab[0][0])
-    print("__constant__ uint16_t c_unit[16][4] = {")
+    print("__constant__ uint16_t c_unit[20][4] = {")
     for r in unit_tab:
         print("    {" + ", ".join(f"0x{v:04x}" for v in r) + "},")
     print("};")
-    print("__constant__ uint16_t c_mma[16][4][4] = {")
+    print("constexpr uint16_t k_mma[20][4][4] = {")
     for r in mma_tab:
         print("    {" + ", ".join("{" + ", ".join(f"0x{v:04x}" for v in ms) + "}" for ms in r) + "},")
     print("};")
