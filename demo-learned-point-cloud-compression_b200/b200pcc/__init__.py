@@ -8,6 +8,7 @@ from . import _lib  # noqa: F401  (raises ImportError when the CUDA library is m
 from .sparse import SparseTensor, CoordMap, sort_points, sort_tensor  # noqa: F401
 from .model import ColorModel  # noqa: F401
 from .pipeline import CompressionPipeline, DecompressionPipeline, load_model  # noqa: F401
+from .single import CompressionPipelineSingle, DecompressionPipelineSingle  # noqa: F401
 
 __all__ = ["SparseTensor", "CoordMap", "ColorModel", "CompressionPipeline", "DecompressionPipeline",
-           "load_model", "sort_points", "sort_tensor"]
+           "CompressionPipelineSingle", "DecompressionPipelineSingle", "load_model", "sort_points", "sort_tensor"]

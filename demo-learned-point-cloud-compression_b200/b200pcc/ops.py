@@ -574,6 +574,12 @@ def gather_rows(src: torch.Tensor, src_row: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def gather_rows_i32(src: torch.Tensor, src_row: torch.Tensor) -> torch.Tensor:
+    """Rows of an int32 matrix (coordinates) through the float32 row gather: a bit-for-bit copy."""
+    _need_cuda(src, torch.int32)
+    return gather_rows(src.view(torch.float32), src_row).view(torch.int32)
+
+
 def gather_keys(src: torch.Tensor, src_row: torch.Tensor) -> torch.Tensor:
     n = src_row.shape[0]
     out = torch.empty(n, dtype=torch.int64, device=src.device)

@@ -141,6 +141,7 @@ def _log2(stride) -> int:
 class SparseTensor:
     def __init__(self, features=None, coordinates=None, tensor_stride=1, device=None, *, _cmap: CoordMap = None,
                  _feats: torch.Tensor = None, _channels: Optional[int] = None):
+        self._order = None          # sort_tensor(): permutation that .C / .F present the rows in (canonical order)
         if _cmap is not None:
             self.cmap = _cmap
             self._feats = _feats
@@ -167,14 +168,17 @@ class SparseTensor:
     # ---- reference-visible surface -------------------------------------------------------------------
     @property
     def C(self) -> torch.Tensor:
-        return self.cmap.coords()
+        c = self.cmap.coords()
+        return c if self._order is None else ops.gather_rows_i32(c, self._order)
 
     @property
     def F(self) -> torch.Tensor:
         f = self._feats
         if f.dtype == torch.bfloat16:
-            return ops.rows_bf16_to_f32(f, self._channels)
-        return f[:, : self._channels] if f.shape[1] != self._channels else f
+            f = ops.rows_bf16_to_f32(f, self._channels)
+        elif f.shape[1] != self._channels:
+            f = f[:, : self._channels].contiguous()
+        return f if self._order is None else ops.gather_rows(f.contiguous(), self._order)
 
     @property
     def tensor_stride(self):
@@ -224,9 +228,12 @@ def sort_points(points: torch.Tensor) -> torch.Tensor:
 
 
 def sort_tensor(t: SparseTensor) -> SparseTensor:
-    """shared/utils.py:116-141: same coordinates/features with rows in canonical order, as plain
-    tensors wrapped in a SparseTensor view whose .C/.F are canonically ordered."""
-    perm = t.cmap.lex_perm().long()
+    """shared/utils.py:116-141: the same tensor with its rows in canonical (b,x,y,z) order.  The reference builds a new
+    ME.SparseTensor from the sorted coordinates and features; here the result shares the coordinate map and the feature
+    storage (which stay in Morton order for the kernels) and presents `.C` / `.F` through the canonical permutation."""
     out = SparseTensor(_cmap=t.cmap, _feats=t._feats, _channels=t._channels)
-    out._sorted_view = (t.C[perm], t.F[perm])
+    out._order = t.cmap.lex_perm()
+    for name in ("num_frames", "frame_counts"):
+        if hasattr(t, name):
+            setattr(out, name, getattr(t, name))
     return out
