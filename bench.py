@@ -285,9 +285,19 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # the ranks of a node share its host cores (every GPU of the bench box reports the same CPU affinity): give each
+        # rank its own slice, so that its Python thread and its staging threads do not migrate onto another rank's cores
+        try:
+            cores = sorted(os.sched_getaffinity(0))
+            lw = int(os.environ.get("LOCAL_WORLD_SIZE", world))
+            per = len(cores) // lw
+            if per >= 2:
+                os.sched_setaffinity(0, set(cores[local * per:(local + 1) * per]))
+        except (AttributeError, OSError):
+            pass
         dist.init_process_group("nccl", device_id=dev)
 
-    steps, warmup = args.steps, max(args.warmup, 3)
+    steps, warmup = args.steps, max(args.warmup, 4)      # (every distinct frame is seen twice before timing starts)
     # per-rank frames (weak scaling): a handful of distinct frames cycled through the steps
     n_frames = 2
     frames = [synth.frame_8ivfb(seed=1 + rank * 100 + i, n_target=args.points) for i in range(n_frames)]
@@ -461,7 +471,8 @@ def main():
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": _config(n_points[0], world),
             "latency_ms": {"encode_p50": float(np.median(enc_ms)), "decode_p50": float(np.median(dec_ms)),
-                           "step_p50": float(np.median(step_ms))},
+                           "step_p50": float(np.median(step_ms)), "step_max": float(np.max(step_ms)),
+                           "step_ms_rank0": [round(float(v), 3) for v in step_ms]},
             "fps": steps / total_s,
             "e2e": None if not e2e_steps else {
                 "value": e2e_pts / e2e_total / 1e6, "unit": UNIT,

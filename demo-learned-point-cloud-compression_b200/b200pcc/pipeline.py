@@ -131,7 +131,11 @@ def _default_stage_threads() -> int:
     # six threads saturate the host copy on one GPU; ranks of one node share the cores (torchrun exports
     # LOCAL_WORLD_SIZE), so each takes its share but never fewer than two
     ranks = max(int(_os.environ.get("LOCAL_WORLD_SIZE", _os.environ.get("WORLD_SIZE", "1")) or 1), 1)
-    return max(2, min(6, (_os.cpu_count() or 8) // ranks))
+    try:
+        cores = len(_os.sched_getaffinity(0))       # what this process may run on (a launcher may have pinned it)
+    except (AttributeError, OSError):
+        cores = _os.cpu_count() or 8
+    return max(2, min(6, cores // ranks))
 
 
 _STAGE_THREADS = int(_os.environ.get("PCC_STAGE_THREADS", "0")) or _default_stage_threads()
