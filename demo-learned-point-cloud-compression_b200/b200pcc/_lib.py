@@ -62,6 +62,8 @@ SIGNATURES = {
     "pcc_sort_unique": (INT, [P, I64, P, P, P, P, I64, P]),
     "pcc_coords_downsample_workspace_bytes": (I64, [I64]),
     "pcc_coords_downsample": (INT, [P, I64, INT, P, P, P, P, I64, P]),
+    "pcc_coords_downsample_static_max_rows": (I64, []),
+    "pcc_coords_downsample_static": (INT, [P, I64, INT, P, P, P, P]),
     "pcc_coords_pyramid_workspace_bytes": (I64, [I64]),
     "pcc_coords_pyramid": (INT, [P, I64, INT, INT, P, P, P, I32, P, P, I64, P]),
     "pcc_coords_children": (INT, [P, I64, INT, P, P]),

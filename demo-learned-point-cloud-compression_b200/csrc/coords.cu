@@ -2,6 +2,7 @@
 // frame offsets, canonical lexicographic order, row gathers.  All HBM-bound, one pass each.
 #include "common.cuh"
 #include <cub/cub.cuh>
+#include <mutex>
 
 namespace pcc {
 
@@ -520,6 +521,86 @@ int pcc_coords_downsample(const uint64_t* keys_in, int64_t n, int log2_stride, u
     set_error("pcc_coords_downsample: workspace too small");
     return PCC_E_WORKSPACE;
   }
+  uint64_t mask = ~((1ull << (3 * log2_stride)) - 1ull);
+  launch_pdl(k_run_flags, dim3(blocks_for(n)), dim3(kThreads), 0, st, keys_in, n, mask, flags);
+  PCC_LAUNCHED();
+  PCC_CUDA(cub::DeviceScan::InclusiveSum(scan_ws, scan_b, flags, flags, (int)n, st));
+  g_launches.fetch_add(1);
+  launch_pdl(k_scatter_runs, dim3(blocks_for(n)), dim3(kThreads), 0, st, keys_in, nullptr, flags, n, mask, keys_out,
+                                                     nullptr, parent_row, n_out_dev);
+  PCC_LAUNCHED();
+  return PCC_OK;
+}
+
+// ---- pcc_coords_downsample_static: the same operation for callers that may not allocate ---------
+// The flags and the scan's temporary storage live in a file-scope device array that every GPU which
+// loads the library holds until exit.  `g_static_scratch` below is the HOST-side stand-in of that array:
+// host code may not hand it to a kernel; the device address comes from cudaGetSymbolAddress, looked up
+// once per device with that device current (static_scratch_ptr).
+constexpr int64_t kStaticMaxRows = 1ll << 20;                 // 1 Mi rows per call
+constexpr int64_t kStaticFlagBytes = kStaticMaxRows * 4;      // int32 run flags / inclusive scan, in place
+constexpr int64_t kStaticScanBytes = 256ll << 10;             // CUB DeviceScan temporary storage (a few KB at 1 Mi items)
+constexpr int64_t kStaticScratchBytes = kStaticFlagBytes + kStaticScanBytes;
+constexpr int kStaticMaxDevices = 64;
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+static std::mutex g_static_mu;
+static void* g_static_ptr[kStaticMaxDevices];   // device address of g_static_scratch, per device ordinal
+
+static int static_scratch_ptr(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) {
+    set_error("pcc_coords_downsample_static: cudaGetDevice: %s", cudaGetErrorString(e));
+    return PCC_E_CUDA;
+  }
+  if (dev < 0 || dev >= kStaticMaxDevices) {
+    set_error("pcc_coords_downsample_static: device ordinal %d beyond %d", dev, kStaticMaxDevices);
+    return PCC_E_INVALID;
+  }
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  if (!g_static_ptr[dev]) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_static_scratch);      // the current device's copy of the array
+    if (e != cudaSuccess || !ptr) {
+      set_error("pcc_coords_downsample_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return PCC_E_CUDA;
+    }
+    g_static_ptr[dev] = ptr;
+  }
+  *out = g_static_ptr[dev];
+  return PCC_OK;
+}
+
+int64_t pcc_coords_downsample_static_max_rows(void) { return kStaticMaxRows; }
+
+int pcc_coords_downsample_static(const uint64_t* keys_in, int64_t n, int log2_stride, uint64_t* keys_out,
+                                 int32_t* parent_row, int32_t* n_out_dev, pcc_stream_t s) {
+  PCC_CHECK_ARG(n >= 0 && n_out_dev && log2_stride >= 1 && log2_stride <= 15);
+  if (n > kStaticMaxRows) {
+    set_error("pcc_coords_downsample_static: n = %lld rows exceeds the static scratch limit of %lld rows; "
+              "use pcc_coords_downsample with a caller-owned workspace", (long long)n, (long long)kStaticMaxRows);
+    return PCC_E_INVALID;
+  }
+  cudaStream_t st = as_stream(s);
+  if (n == 0) {
+    PCC_CUDA(cudaMemsetAsync(n_out_dev, 0, 4, st));
+    return PCC_OK;
+  }
+  PCC_CHECK_ARG(keys_in && keys_out);
+  void* base = nullptr;
+  int rc = static_scratch_ptr(&base);
+  if (rc != PCC_OK) return rc;
+  int32_t* flags = (int32_t*)base;
+  void* scan_ws = (char*)base + kStaticFlagBytes;
+  size_t scan_b = cub_scan_bytes(n);
+  if ((int64_t)scan_b > kStaticScanBytes) {
+    set_error("pcc_coords_downsample_static: scan needs %lld bytes of temporary storage, %lld reserved",
+              (long long)scan_b, (long long)kStaticScanBytes);
+    return PCC_E_WORKSPACE;
+  }
+  // Nothing in the array has to start at zero: every flag the call reads is written by k_run_flags first and
+  // CUB's scan initialises its own tile states, so the previous call's contents are simply overwritten.
   uint64_t mask = ~((1ull << (3 * log2_stride)) - 1ull);
   launch_pdl(k_run_flags, dim3(blocks_for(n)), dim3(kThreads), 0, st, keys_in, n, mask, flags);
   PCC_LAUNCHED();

@@ -109,6 +109,19 @@ int64_t pcc_coords_downsample_workspace_bytes(int64_t n);
 int pcc_coords_downsample(const uint64_t* keys_in, int64_t n, int log2_stride, uint64_t* keys_out,
                           int32_t* parent_row, int32_t* n_out_dev, void* ws, int64_t ws_bytes,
                           pcc_stream_t s);
+/* pcc_coords_downsample for callers that may not allocate device memory (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same inputs, outputs and results as pcc_coords_downsample, but the scratch (run flags +
+ * scan storage) is a file-scope `static __device__` array inside the library (4 MiB + 256 KiB, held by every GPU
+ * that loads the library until exit) instead of a caller-owned workspace; the call performs no cudaMalloc /
+ * cudaFree and calls no allocating routine.  Limit: n <= pcc_coords_downsample_static_max_rows() (1 Mi rows);
+ * a larger n returns PCC_E_INVALID with a message naming the limit.  All calls on one device share the array:
+ * it keeps the previous call's contents (nothing in it has to start at zero - every word a call reads it has
+ * written first), and two calls that overlap on the GPU (different streams, or different host threads on
+ * different streams) RACE; serialise them on one stream. */
+int64_t pcc_coords_downsample_static_max_rows(void);
+int pcc_coords_downsample_static(const uint64_t* keys_in, int64_t n, int log2_stride, uint64_t* keys_out,
+                                 int32_t* parent_row, int32_t* n_out_dev, pcc_stream_t s);
 /* The whole stride pyramid of a coordinate set in one call (the output coordinates of the chained
  * stride-2 convolutions of g_a and h_a, codec_pipeline.py:273,287, and of g_s.down_conv x2,
  * codec_parallel.py:302-303): level l (0-based) holds the keys at stride 2^(log2_stride+l+1) in
