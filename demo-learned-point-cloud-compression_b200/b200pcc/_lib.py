@@ -107,6 +107,7 @@ SIGNATURES = {
     "pcc_rans_lut_entries": (I64, [I32]),
     "pcc_rans_build_lut": (INT, [C.POINTER(CdfTables), P, P]),
     "pcc_rans_encode": (INT, [P, P, I64, I64, I32, C.POINTER(CdfTables), P, P, P, I64, P]),
+    "pcc_rans_encode_batch": (INT, [P, P, I64, I64, I32, I32, C.POINTER(CdfTables), P, I64, P, P, I64, P]),
     "pcc_rans_decode": (INT, [P, I64, I32, P, I64, I64, C.POINTER(CdfTables), P, P, P]),
     "pcc_run_program": (INT, [P, I32, P, P]),
     "pcc_container_batched_bytes": (I64, [I32, I64, I64, P]),

@@ -543,6 +543,12 @@ class _CodedModel:
         """-> (device byte buffer, device int32 size): no host sync; see fetch_strings()."""
         return ops.rans_encode(sym_flat, idx_flat, chan_len, self.tables, self.seg_size)
 
+    def _encode_device_batch(self, sym: torch.Tensor, idx: Optional[torch.Tensor], chan_len: int):
+        """sym / idx: [Q, n].  -> [(device byte buffer, device int32 size)] * Q from one batched coder call."""
+        if sym.shape[0] == 1:
+            return [self._encode_device(sym.reshape(-1), None if idx is None else idx.reshape(-1), chan_len)]
+        return ops.rans_encode_batch(sym, idx, chan_len, self.tables, self.seg_size)
+
     def _encode(self, sym_flat: torch.Tensor, idx_flat: Optional[torch.Tensor], chan_len: int) -> bytes:
         return fetch_strings([self._encode_device(sym_flat, idx_flat, chan_len)])[0]
 

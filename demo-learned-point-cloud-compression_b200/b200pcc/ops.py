@@ -853,6 +853,29 @@ def rans_encode(sym: torch.Tensor, idx: Optional[torch.Tensor], chan_len: int, t
     return out, nbytes
 
 
+def rans_encode_batch(sym: torch.Tensor, idx: Optional[torch.Tensor], chan_len: int, tables: DeviceCdfTables,
+                      seg_size: Optional[int] = None):
+    """sym (and idx): [Q, ...] int32 (uint16) device tensors, one row of n symbols per quality level.  All Q
+    streams are coded by one call (three launches, grid.y = level; codec_pipeline.py:414-432 is the batched
+    call this matches).  Returns [(device uint8 buffer, device int32 byte count)] * Q, each an independent
+    container identical to rans_encode of that row."""
+    _need_cuda(sym, torch.int32)
+    Q = sym.shape[0]
+    n = sym.numel() // Q
+    if seg_size is None:
+        seg_size = auto_seg_size(n)
+    dev = sym.device
+    stride = (int(lib.pcc_rans_max_bytes(n, seg_size)) + 15) // 16 * 16
+    out = torch.empty((Q, stride), dtype=torch.uint8, device=dev)
+    nbytes = torch.empty(Q, dtype=torch.int32, device=dev)
+    wsb = lib.pcc_rans_workspace_bytes(n, seg_size) * Q
+    ws = workspace(wsb, dev, "rans")
+    with _prof("rans_encode", Q * n * 6):
+        check(lib.pcc_rans_encode_batch(_ptr(sym), _ptr(idx), chan_len, n, Q, seg_size, C.byref(tables.struct), _ptr(out),
+                                        stride, _ptr(nbytes), _ptr(ws), ws.numel(), _stream()))
+    return [(out[q], nbytes[q:q + 1]) for q in range(Q)]
+
+
 def rans_decode(container: torch.Tensor, seg_size: int, idx: Optional[torch.Tensor], chan_len: int, n: int,
                 tables: DeviceCdfTables) -> torch.Tensor:
     _need_cuda(container, torch.uint8)

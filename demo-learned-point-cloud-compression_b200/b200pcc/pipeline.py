@@ -416,7 +416,8 @@ class CompressionPipeline:
         sym, idx = ops.gauss_encode(y._feats, gaussian_params._feats, prow, perm, scale, gc.table_d, gc.scale_bound)
         if self.keep_debug:
             self.debug.update(y=y, gaussian_params=gaussian_params, y_sym=sym, y_idx=idx, scale=scale)
-        pending = [gc._encode_device(sym[qi].reshape(-1), idx[qi].reshape(-1), 1) for qi in range(len(settings))]
+        nq = len(settings)
+        pending = gc._encode_device_batch(sym.reshape(nq, -1), idx.reshape(nq, -1), 1)
         return pending, [y.cmap.n]
 
     # ---- entry point -----------------------------------------------------------------------------------------

@@ -81,15 +81,32 @@ __device__ __forceinline__ SymOps make_ops(int32_t symbol, int32_t t, const Tabl
   return o;
 }
 
+template <typename T>
+__device__ __forceinline__ T* ws_shift(T* p, int64_t ws_stride) {
+  return reinterpret_cast<T*>(reinterpret_cast<char*>(p) + (int64_t)blockIdx.y * ws_stride);
+}
+template <typename T>
+__device__ __forceinline__ const T* ws_shift(const T* p, int64_t ws_stride) {
+  return reinterpret_cast<const T*>(reinterpret_cast<const char*>(p) + (int64_t)blockIdx.y * ws_stride);
+}
+
 // Pass A (fully parallel): per symbol the packed (start | freq << 16) of the table entry it codes
 // with -- its own entry, or the table's last entry for a value outside the support (escape) -- the
 // escape payload raw[i] (0 when not an escape) and, per 32 symbols (= one coder round), the ballot of
 // escaping lanes.  The coder (pass B) then never touches the tables or the symbols.
 __global__ void __launch_bounds__(256)
 k_rans_prepare(const int32_t* __restrict__ sym, const uint16_t* __restrict__ idx, int64_t chan_len, int64_t n,
-               Tables T, uint32_t* __restrict__ packed, uint32_t* __restrict__ raw, uint32_t* __restrict__ escmask) {
+               Tables T, uint32_t* __restrict__ packed, uint32_t* __restrict__ raw, uint32_t* __restrict__ escmask,
+               int64_t ws_stride) {
   pdl_trigger();
   pdl_wait();
+  // blockIdx.y = stream of a batch (pcc_rans_encode_batch): its symbols follow the previous stream's, its
+  // workspace arrays lie ws_stride bytes after the previous stream's
+  sym += blockIdx.y * n;
+  if (idx) idx += blockIdx.y * n;
+  packed = ws_shift(packed, ws_stride);
+  raw = ws_shift(raw, ws_stride);
+  escmask = ws_shift(escmask, ws_stride);
   const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   uint32_t pk = 0, rw = 0;
   bool esc = false;
@@ -126,9 +143,16 @@ constexpr uint32_t kInactive = 0xffffffffu;
 __global__ void __launch_bounds__(32 * kEncWarps)
 k_rans_encode(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ raw,
               const uint32_t* __restrict__ escmask, int64_t n, int32_t seg_size, int32_t nseg,
-              uint16_t* __restrict__ scratch, uint32_t* __restrict__ states, int32_t* __restrict__ nwords) {
+              uint16_t* __restrict__ scratch, uint32_t* __restrict__ states, int32_t* __restrict__ nwords,
+              int64_t ws_stride) {
   pdl_trigger();
   pdl_wait();
+  packed = ws_shift(packed, ws_stride);
+  raw = ws_shift(raw, ws_stride);
+  escmask = ws_shift(escmask, ws_stride);
+  scratch = ws_shift(scratch, ws_stride);
+  states = ws_shift(states, ws_stride);
+  nwords = ws_shift(nwords, ws_stride);
   const int seg = blockIdx.x * kEncWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (seg >= nseg) return;
   const unsigned lt = (1u << lane) - 1u;
@@ -215,9 +239,14 @@ __device__ __forceinline__ uint32_t seg_bytes_of(int32_t nw) { return 4u + 128u 
 __global__ void __launch_bounds__(256)
 k_rans_pack(const uint16_t* __restrict__ scratch, const uint32_t* __restrict__ states,
             const int32_t* __restrict__ nwords, int32_t nseg, int32_t seg_size, uint32_t n,
-            uint8_t* __restrict__ out, int32_t* __restrict__ out_bytes) {
+            uint8_t* __restrict__ out, int32_t* __restrict__ out_bytes, int64_t ws_stride, int64_t out_stride) {
   pdl_trigger();
   pdl_wait();
+  scratch = ws_shift(scratch, ws_stride);
+  states = ws_shift(states, ws_stride);
+  nwords = ws_shift(nwords, ws_stride);
+  out += (int64_t)blockIdx.y * out_stride;
+  out_bytes += blockIdx.y;
   __shared__ uint32_t s_off;
   __shared__ uint32_t red[256];
   const int seg = blockIdx.x, tid = threadIdx.x;
@@ -510,16 +539,26 @@ int64_t pcc_rans_workspace_bytes(int64_t n, int32_t seg_size) {
          2 * align_up(n * 4, 256) + align_up((n + 31) / 32 * 4, 256) + 256;
 }
 
-int pcc_rans_encode(const int32_t* sym, const uint16_t* idx, int64_t chan_len, int64_t n,
-                    int32_t seg_size, const pcc_cdf_tables_t* tables, uint8_t* out,
-                    int32_t* out_bytes_dev, void* ws, int64_t ws_bytes, pcc_stream_t s) {
+// Q streams of n symbols each (sym / idx: [Q][n]; stream q's container at out + q * out_stride, its size in
+// out_bytes_dev[q]) coded by ONE launch of each pass: grid.y = stream.  Every stream is an independent PCL1
+// container, byte-identical to what pcc_rans_encode produces for it.
+static int rans_encode_streams(const int32_t* sym, const uint16_t* idx, int64_t chan_len, int64_t n, int32_t num_streams,
+                               int32_t seg_size, const pcc_cdf_tables_t* tables, uint8_t* out, int64_t out_stride,
+                               int32_t* out_bytes_dev, void* ws, int64_t ws_bytes, pcc_stream_t s, const char* who) {
   PCC_CHECK_ARG(n > 0 && n < (1ll << 31) && seg_size >= 32 && seg_size % 32 == 0 && tables && out &&
                 out_bytes_dev && ws && sym);
+  PCC_CHECK_ARG(num_streams >= 1 && num_streams <= 65535);
   PCC_CHECK_ARG(idx || chan_len > 0);
   PCC_CHECK_ARG(tables->cdf && tables->cdf_off && tables->cdf_size && tables->offset && tables->num_tables > 0);
-  if (ws_bytes < pcc_rans_workspace_bytes(n, seg_size)) {
-    set_error("pcc_rans_encode: workspace too small");
+  const int64_t ws_stride = num_streams > 1 ? pcc_rans_workspace_bytes(n, seg_size) : 0;
+  if (ws_bytes < pcc_rans_workspace_bytes(n, seg_size) * num_streams) {
+    set_error("%s: workspace too small", who);
     return PCC_E_WORKSPACE;
+  }
+  if (num_streams > 1 && (out_stride < pcc_rans_max_bytes(n, seg_size) || (out_stride & 3))) {
+    set_error("%s: out_stride %lld must be a multiple of 4 and at least pcc_rans_max_bytes = %lld", who,
+              (long long)out_stride, (long long)pcc_rans_max_bytes(n, seg_size));
+    return PCC_E_INVALID;
   }
   const int32_t ns = nseg_of(n, seg_size);
   char* p = (char*)ws;
@@ -537,14 +576,31 @@ int pcc_rans_encode(const int32_t* sym, const uint16_t* idx, int64_t chan_len, i
   Tables T{tables->cdf, tables->cdf_off, tables->cdf_size, tables->offset, tables->lut, tables->num_tables, tables->cdf_total};
   cudaStream_t st = as_stream(s);
   const int64_t cl = chan_len > 0 ? chan_len : 1;
-  launch_pdl(k_rans_prepare, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, st, sym, idx, cl, n, T, packed, raw, escmask);
+  const unsigned Q = (unsigned)num_streams;
+  launch_pdl(k_rans_prepare, dim3((unsigned)((n + 255) / 256), Q), dim3(256), 0, st, sym, idx, cl, n, T, packed, raw, escmask,
+             ws_stride);
   PCC_LAUNCHED();
-  launch_pdl(k_rans_encode, dim3((ns + kEncWarps - 1) / kEncWarps), dim3(32 * kEncWarps), 0, st, packed, raw, escmask, n, seg_size, ns,
-                                                                          scratch, states, nwords);
+  launch_pdl(k_rans_encode, dim3((ns + kEncWarps - 1) / kEncWarps, Q), dim3(32 * kEncWarps), 0, st, packed, raw, escmask, n,
+             seg_size, ns, scratch, states, nwords, ws_stride);
   PCC_LAUNCHED();
-  launch_pdl(k_rans_pack, dim3(ns), dim3(256), 0, st, scratch, states, nwords, ns, seg_size, (uint32_t)n, out, out_bytes_dev);
+  launch_pdl(k_rans_pack, dim3(ns, Q), dim3(256), 0, st, scratch, states, nwords, ns, seg_size, (uint32_t)n, out, out_bytes_dev,
+             ws_stride, num_streams > 1 ? out_stride : (int64_t)0);
   PCC_LAUNCHED();
   return PCC_OK;
+}
+
+int pcc_rans_encode(const int32_t* sym, const uint16_t* idx, int64_t chan_len, int64_t n,
+                    int32_t seg_size, const pcc_cdf_tables_t* tables, uint8_t* out,
+                    int32_t* out_bytes_dev, void* ws, int64_t ws_bytes, pcc_stream_t s) {
+  return rans_encode_streams(sym, idx, chan_len, n, 1, seg_size, tables, out, 0, out_bytes_dev, ws, ws_bytes, s,
+                             "pcc_rans_encode");
+}
+
+int pcc_rans_encode_batch(const int32_t* sym, const uint16_t* idx, int64_t chan_len, int64_t n, int32_t num_streams,
+                          int32_t seg_size, const pcc_cdf_tables_t* tables, uint8_t* out, int64_t out_stride,
+                          int32_t* out_bytes_dev, void* ws, int64_t ws_bytes, pcc_stream_t s) {
+  return rans_encode_streams(sym, idx, chan_len, n, num_streams, seg_size, tables, out, out_stride, out_bytes_dev, ws,
+                             ws_bytes, s, "pcc_rans_encode_batch");
 }
 
 int pcc_rans_decode(const uint8_t* container, int64_t container_bytes, int32_t seg_size,

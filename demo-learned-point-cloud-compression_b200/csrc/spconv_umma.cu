@@ -568,12 +568,23 @@ int pcc_spconv_umma(const void* in_bf16, int64_t n_in, int cin, const int32_t* n
     set_error("pcc_spconv_umma: cin %d cout %d kvol %d does not fit shared memory", cin, cout, kvol);
     return PCC_E_UNSUPPORTED;
   }
+  // T: more tiles per stage amortise the per-stage hand-off (a T = 2 round costs ~1.3-1.5x a T = 1 round and covers two
+  // tiles: tools/spconv_sweep.py, profiles/r2f_sweep_small.txt), but fewer, longer rounds leave SMs idle on small levels.
+  // Pick the T with the lowest estimate  rounds per CTA x (1 + 0.5 (T - 1)).  (Round 1 kept >= 2 rounds per SM, which held
+  // the 58 k-row C = 64 layers of g_a at T = 1: 57 us; with T = 2 they take 40 us.)
   int T = 1, lt = 0;
-  while (2 * T <= g_max_t && (uint32_t)(2 * (2 * T)) * p.acc_cols <= 512u && ntiles / (2 * T) >= 2 * sms &&
-         2 * T * (cin / 8) <= 32 &&
-         smem_need(groups, 2 * T) <= budget) {
-    T *= 2;
-    ++lt;
+  {
+    double best = 1e30;
+    for (int t = 1, l = 0; t <= g_max_t; t *= 2, ++l) {
+      if ((uint32_t)(2 * t) * p.acc_cols > 512u || t * (cin / 8) > 32 || smem_need(groups, t) > budget) break;
+      const int64_t nsuper = (ntiles + t - 1) / t;
+      const double est = (double)((nsuper + sms - 1) / sms) * (1.0 + 0.5 * (t - 1));
+      if (est < best - 1e-9) {
+        best = est;
+        T = t;
+        lt = l;
+      }
+    }
   }
   p.lt = lt;
   p.nrounds_total = (int)((ntiles + T - 1) / T);

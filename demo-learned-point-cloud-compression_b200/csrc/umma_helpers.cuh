@@ -32,6 +32,7 @@ struct WaitCtx {
   uint32_t abort_flag;   // shared-memory address of the CTA's abort word
   uint32_t spin_limit;
   int* fault;
+  uint32_t exp = 0;      // debug experiments (spconv_octet.cu, TRACE instantiation only)
 };
 __device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr) {
   uint32_t v;

@@ -351,6 +351,15 @@ int64_t pcc_rans_workspace_bytes(int64_t n, int32_t seg_size);
 int pcc_rans_encode(const int32_t* sym, const uint16_t* idx, int64_t chan_len, int64_t n,
                     int32_t seg_size, const pcc_cdf_tables_t* tables, uint8_t* out,
                     int32_t* out_bytes_dev, void* ws, int64_t ws_bytes, pcc_stream_t s);
+/* All quality levels of a GOP in one call (the reference codes them in ONE batched
+ * gaussian_conditional.compress call: sender/encoder/codec_pipeline.py:414-432).  sym / idx: [num_streams][n];
+ * stream q becomes an independent PCL1 container at out + q * out_stride (out_stride: multiple of 4,
+ * >= pcc_rans_max_bytes(n, seg_size)), byte-identical to pcc_rans_encode of that stream alone; its size lands in
+ * out_bytes_dev[q].  Three launches whatever num_streams is (grid.y = stream): 25 levels x 58 segments fill the
+ * machine that one stream leaves idle.  Workspace: num_streams * pcc_rans_workspace_bytes(n, seg_size). */
+int pcc_rans_encode_batch(const int32_t* sym, const uint16_t* idx, int64_t chan_len, int64_t n, int32_t num_streams,
+                          int32_t seg_size, const pcc_cdf_tables_t* tables, uint8_t* out, int64_t out_stride,
+                          int32_t* out_bytes_dev, void* ws, int64_t ws_bytes, pcc_stream_t s);
 /* seg_size = the container header's value (the caller holds the host copy of the bytes).
  * status_dev: 0 ok, 1 truncated container, 2 corrupt stream, 3 header mismatch. */
 int pcc_rans_decode(const uint8_t* container, int64_t container_bytes, int32_t seg_size,

@@ -137,6 +137,38 @@ def test_rans_gaussian_bytes_match_oracle_and_roundtrip(model, dev, n, seg):
         assert len(got) <= 1.02 * len(single), (len(got), len(single))
 
 
+def test_rans_encode_batch_equals_per_stream_and_the_oracle(model, dev):
+    """All quality levels in one coder call (codec_pipeline.py:414-432): every stream of the batch is byte-identical
+    to coding it alone, and to the scalar restatement."""
+    from b200pcc import ops
+    gc = model.entropy_model.gaussian_conditional
+    Q, n, seg = 5, 40_000 + 17, 4096
+    rng = np.random.default_rng(77)
+    idx = rng.integers(0, 64, (Q, n)).astype(np.int32)
+    sym = np.rint(rng.normal(0, 1, (Q, n)) * gc.scale_table[idx] * (1 + np.arange(Q))[:, None]).astype(np.int32)
+    sym[1, ::301] += 90000
+    sym[3, 7::911] -= 2 ** 29
+    ts, ti = torch.from_numpy(sym).to(dev), torch.from_numpy(idx.astype(np.int16)).to(dev)
+    pend = ops.rans_encode_batch(ts, ti, 1, gc.tables, seg)
+    assert len(pend) == Q
+    for q, (buf, nb) in enumerate(pend):
+        got = buf[: int(nb.item())].cpu().numpy().tobytes()
+        b1, n1 = ops.rans_encode(ts[q].contiguous(), ti[q].contiguous(), 1, gc.tables, seg)
+        assert got == b1[: int(n1.item())].cpu().numpy().tobytes()
+        assert got == R.pcl1_encode(sym[q], idx[q], 1, _tables_ref(gc), seg)
+    # the strings of a batch travel through fetch_strings like any others
+    from b200pcc.model import fetch_strings
+    strings = fetch_strings(pend)
+    assert [len(x) for x in strings] == [int(nb.item()) for _, nb in pend]
+    # factorized model (idx = None, table = channel) batched over two "levels"
+    eb = model.entropy_model.entropy_bottleneck
+    c, m = eb.channels, 333
+    zs = np.rint(rng.normal(0, 4, (2, c, m))).astype(np.int32)
+    pz = ops.rans_encode_batch(torch.from_numpy(zs.reshape(2, -1)).to(dev), None, m, eb.tables, 4096)
+    for q, (buf, nb) in enumerate(pz):
+        assert buf[: int(nb.item())].cpu().numpy().tobytes() == R.pcl1_encode(zs[q].reshape(-1), None, m, _tables_ref(eb), 4096)
+
+
 def test_rans_factorized_channel_index(model, dev):
     from b200pcc import ops
     eb = model.entropy_model.entropy_bottleneck

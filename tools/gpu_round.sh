@@ -1,12 +1,10 @@
-# one gpurun call: no-alloc test alone + whole suite, ncu --set full of the non-conv families, compute-sanitizer logs
+# round 2, call 4: MMA rate probe with commits, octet stage-order A/B (timing + output difference), conv tests and bench with
+# the new T selection (order 0 and order 1)
 set -x
-python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q > gpurun_out/r2e_pytest_noalloc_alone.log 2>&1; echo "noalloc alone rc $?"
-python -m pytest tests -m gpu -x -q > gpurun_out/r2e_pytest.log 2>&1; echo "pytest rc $?"
-tail -3 gpurun_out/r2e_pytest_noalloc_alone.log gpurun_out/r2e_pytest.log
-ncu --set full --clock-control none -k regex:"$(python tools/ncu_families.py regex)" -c 400 -f -o gpurun_out/r2e_families python tools/ncu_families.py run --capture > gpurun_out/r2e_families_ncu.log 2>&1; echo "ncu families rc $?"
-timeout 1200 compute-sanitizer --tool memcheck --log-file gpurun_out/r2e_sanitizer_memcheck.log python -m pytest tests/test_gpu_coords.py tests/test_gpu_entropy.py tests/test_gpu_octree.py tests/test_gpu_conv.py tests/test_zz_no_alloc.py -m gpu -q -x > gpurun_out/r2e_sanitizer_memcheck_pytest.log 2>&1; echo "memcheck rc $?"
-tail -5 gpurun_out/r2e_sanitizer_memcheck.log gpurun_out/r2e_sanitizer_memcheck_pytest.log
-timeout 900 compute-sanitizer --tool memcheck --log-file gpurun_out/r2e_sanitizer_memcheck_smoke.log python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r2e_sanitizer_memcheck_smoke_out.log 2>&1; echo "memcheck smoke rc $?"
-tail -5 gpurun_out/r2e_sanitizer_memcheck_smoke.log gpurun_out/r2e_sanitizer_memcheck_smoke_out.log
-timeout 900 compute-sanitizer --tool racecheck --log-file gpurun_out/r2e_sanitizer_racecheck_smoke.log python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r2e_sanitizer_racecheck_smoke_out.log 2>&1; echo "racecheck smoke rc $?"
-tail -5 gpurun_out/r2e_sanitizer_racecheck_smoke.log gpurun_out/r2e_sanitizer_racecheck_smoke_out.log
+nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -I demo-learned-point-cloud-compression_b200/csrc tools/umma_rate_probe.cu -o /tmp/umma_rate_probe && timeout 120 /tmp/umma_rate_probe > gpurun_out/r2g_umma_rate_probe.txt 2>&1; tail -n 30 gpurun_out/r2g_umma_rate_probe.txt
+python tools/octet_trace.py --exp > gpurun_out/r2g_octet_order_exp.txt 2>&1; cat gpurun_out/r2g_octet_order_exp.txt
+python -m pytest tests/test_gpu_conv.py tests/test_gpu_pipeline.py -m gpu -x -q > gpurun_out/r2g_pytest_conv.log 2>&1; echo "pytest rc $?"; tail -n 3 gpurun_out/r2g_pytest_conv.log
+PCC_OCTET_ORDER=1 python -m pytest tests/test_gpu_conv.py tests/test_gpu_pipeline.py tests/test_gpu_parity.py -m gpu -x -q > gpurun_out/r2g_pytest_order1.log 2>&1; echo "pytest order1 rc $?"; tail -n 3 gpurun_out/r2g_pytest_order1.log
+python bench.py --breakdown --no-configs --no-cpu-baseline > gpurun_out/r2g_bench_order0.json 2> gpurun_out/r2g_bench_order0_breakdown.txt; head -n 12 gpurun_out/r2g_bench_order0_breakdown.txt; tail -n 2 gpurun_out/r2g_bench_order0_breakdown.txt
+PCC_OCTET_ORDER=1 python bench.py --breakdown --no-configs --no-cpu-baseline > gpurun_out/r2g_bench_order1.json 2> gpurun_out/r2g_bench_order1_breakdown.txt; head -n 12 gpurun_out/r2g_bench_order1_breakdown.txt; tail -n 2 gpurun_out/r2g_bench_order1_breakdown.txt
+du -sh gpurun_out

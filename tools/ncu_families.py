@@ -101,7 +101,7 @@ def summarise(rep):
         total[name] = total.get(name, 0.0) + d
         if name not in best or d > val(best[name], "dur"):
             best[name] = r
-    print(f"# ncu --set full, largest launch per kernel of the non-convolution families (two resident cfg-2 steps)\n")
+    print("# ncu --set full, largest launch per kernel name (two resident cfg-2 steps)\n")
     print(f"Source: `{os.path.basename(rep)}` (`tools/ncu_families.py`); GB/s = (dram read + write bytes) / duration, peak = "
           f"{peak} GB/s (MEASURED_PEAKS.json).  Times under ncu are cold-cache and serialised; they rank, the bench breakdown times.\n")
     print("| kernel | launches | sum µs | largest µs | grid x block | regs | DRAM MB (r+w) | GB/s | frac of HBM peak | dram % | l1tex % | l2 % | sm % | issue % | warps active % | limiter |")

@@ -15,7 +15,7 @@ from b200pcc._lib import lib, check  # noqa: E402
 from b200pcc.sparse import CoordMap  # noqa: E402
 
 dev = torch.device("cuda:0")
-n_target = int(sys.argv[1]) if len(sys.argv) > 1 else 800_000
+n_target = int(sys.argv[1]) if len(sys.argv) > 1 and sys.argv[1].isdigit() else 800_000
 f = synth.frame_8ivfb(seed=1, n_target=n_target)
 C = np.concatenate([np.zeros((len(f["points"]), 1), np.int32), f["points"].astype(np.int32) // 2 * 2], axis=1)
 pk, _ = ops.sort_unique(ops.keys_from_coords(torch.from_numpy(np.ascontiguousarray(C)).to(dev)))
@@ -29,6 +29,44 @@ out = torch.empty_like(x)
 nbp = parent.nbr3()
 for _ in range(3):
     ops.spconv_octet(x, nbp, n_par, w, b, 32, r, True, out, None)
+def timed_traced(exp, reps=7):
+    """Median time of the TRACE instantiation with the experiment bits of PCC_OCTET_EXP (see OctetParams::exp)."""
+    os.environ["PCC_OCTET_EXP"] = str(exp)
+    tb = torch.zeros(int(lib.pcc_debug_trace_words()), dtype=torch.int64, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    ts = []
+    for rep in range(reps):
+        flush.fill_(rep)
+        check(lib.pcc_debug_trace(tb.data_ptr()))
+        a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        ops.spconv_octet(x, nbp, n_par, w, b, 32, r, True, out, None)
+        b_.record()
+        b_.synchronize()
+        ts.append(a.elapsed_time(b_) * 1e3)
+    os.environ["PCC_OCTET_EXP"] = "0"
+    return float(np.median(ts[1:])), float(np.min(ts[1:]))
+
+
+if "--exp" in sys.argv:
+    names = {0: "baseline (trace instantiation)", 1: "no zero fill", 2: "gather waits with suspend hint", 4: "issuer waits with suspend hint",
+             6: "gather + issuer waits with hint", 8: "epilogue without staging / stores", 16: "no row copies (MMAs on stale slots)",
+             24: "no row copies, no epilogue stores", 17: "no copies, no zero fill", 9: "no zero fill, no epilogue stores"}
+    ref = None
+    for order in (0, 1):
+        os.environ["PCC_OCTET_ORDER"] = str(order)
+        for e in (0, 8, 16, 24, 0):
+            med, mn = timed_traced(e)
+            print(f"order {order} exp {e:3d} {names.get(e, ''):45s} median {med:7.1f} us  min {mn:7.1f} us")
+            if e == 0:
+                torch.cuda.synchronize()
+                if ref is None:
+                    ref = out.clone()
+                elif order == 1:
+                    d = (out.float() - ref.float()).abs()
+                    print(f"   order 1 vs order 0 output: max abs diff {d.max().item():.4g}, differing elements {int((d > 0).sum())} of {d.numel()}")
+    sys.exit(0)
+
 words = int(lib.pcc_debug_trace_words())
 buf = torch.zeros(words, dtype=torch.int64, device=dev)
 check(lib.pcc_debug_trace(buf.data_ptr()))

@@ -23,9 +23,11 @@ def main():
     ap.add_argument("--cout", type=int, default=32)
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--one", action="store_true", help="default tuning only, candidates map only (for ncu)")
+    ap.add_argument("--n-target", type=int, default=800_000, help="points of the synthetic frame (smaller = the coarser levels' sizes)")
+    ap.add_argument("--kvol", type=int, default=27)
     args = ap.parse_args()
     dev = torch.device("cuda:0")
-    f = synth.frame_8ivfb(seed=1)
+    f = synth.frame_8ivfb(seed=1, n_target=args.n_target)
     pts = torch.from_numpy(np.concatenate([np.zeros((len(f["points"]), 1), np.int32), f["points"].astype(np.int32)], 1)).to(dev)
     keys, _ = ops.sort_unique(ops.keys_from_coords(pts))
     fine = CoordMap(keys, 0)
@@ -44,7 +46,7 @@ def main():
         alg = 2 * n * args.cin + 2 * n * args.cout + 4 * 27 * n
         print(f"{name}: n={n} pairs/row={pairs:.2f} algorithmic MB={alg / 1e6:.1f}")
         for groups, mt, cg in (((0, 4, 0),) if args.one else
-                               ((5, 4, 0), (4, 4, 0), (4, 2, 0), (2, 4, 0))):
+                               ((0, 4, 0), (5, 4, 0), (4, 4, 0), (4, 2, 0), (4, 1, 0), (2, 4, 0), (2, 2, 0), (2, 1, 0))):
             if True:
                 _lib.check(_lib.lib.pcc_spconv_set_tuning(groups, mt, cg))
                 ts = []
@@ -60,7 +62,7 @@ def main():
                 print(f"  groups={groups} T<={mt} cg={cg}: {t * 1e3:8.1f} us  {alg / t / 1e6:8.1f} GB/s "
                       f"{2 * pairs * n * args.cin * args.cout / t / 1e9:7.1f} TF/s(real pairs)")
         # kernel-map timings
-        for r in range(3):
+        for r in range(0 if args.one else 3):
             flush.fill_(r)
             e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
             e0.record()
@@ -69,7 +71,8 @@ def main():
             ops.kmap_k3_blocks(cm.keys, cm.log2_stride, bt)
             e2.record()
             e2.synchronize()
-        print(f"  blockmap_build {e0.elapsed_time(e1) * 1e3:.1f} us, kmap_k3_blocks {e1.elapsed_time(e2) * 1e3:.1f} us")
+        if not args.one:
+            print(f"  blockmap_build {e0.elapsed_time(e1) * 1e3:.1f} us, kmap_k3_blocks {e1.elapsed_time(e2) * 1e3:.1f} us")
 
 
 if __name__ == "__main__":
