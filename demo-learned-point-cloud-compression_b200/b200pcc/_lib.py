@@ -60,6 +60,7 @@ SIGNATURES = {
     "pcc_coords_from_keys": (INT, [P, I64, P, P]),
     "pcc_sort_unique_workspace_bytes": (I64, [I64]),
     "pcc_sort_unique": (INT, [P, I64, P, P, P, P, I64, P]),
+    "pcc_sort_unique_bits": (INT, [P, I64, INT, P, P, P, P, I64, P]),
     "pcc_coords_downsample_workspace_bytes": (I64, [I64]),
     "pcc_coords_downsample": (INT, [P, I64, INT, P, P, P, P, I64, P]),
     "pcc_coords_downsample_static_max_rows": (I64, []),
@@ -93,6 +94,7 @@ SIGNATURES = {
     "pcc_rows_bf16_to_f32": (INT, [P, INT, I64, P, INT, P]),
     "pcc_gather_rows_bf16": (INT, [P, INT, P, I64, P, P]),
     "pcc_gather_rows_f32": (INT, [P, INT, P, I64, P, P]),
+    "pcc_zero_unkept_rows": (INT, [P, I64, I64, P, INT, P]),
     "pcc_gather_keys": (INT, [P, P, I64, P, P]),
     "pcc_topk_workspace_bytes": (I64, [I64]),
     "pcc_topk_select": (INT, [P, P, I64, P, P, I32, P, P, P, I64, P]),

@@ -337,7 +337,8 @@ class SynthesisTransform(_Module):
             parent = cm
             cm = cm.children()
             blk = self.blocks[i]
-            if USE_OCTET and self.occ[i].w_oct is not None and all(c.w_oct is not None for c in blk):
+            octet = USE_OCTET and self.occ[i].w_oct is not None and all(c.w_oct is not None for c in blk)
+            if octet:
                 # candidates = complete octets: the parents' kernel map drives every k3 layer of the level
                 nbp = parent.nbr3()
                 for b in range(0, len(blk), 2):
@@ -357,10 +358,20 @@ class SynthesisTransform(_Module):
             if return_intermediates:
                 inter.append({"keys": cm.keys, "F": f, "logits": logits, "keep": keep})
             pruned = cm.subset(keep)
-            f = ops.gather_rows(f, keep)
+            if i == 2 and octet and self.color.w_oct is not None:
+                # colour head without a kernel map of the kept set: the pruned candidates are zeroed in place and the head
+                # runs over all candidates (complete octets, the parents' map is there already); on the kept rows that
+                # is the convolution over the kept set.  The kept rows' colours are then picked out.
+                fz = f.clone() if return_intermediates else f
+                ops.zero_unkept_rows(fz, keep)
+                colors = ops.gather_rows(self.color.octet(fz, nbp, parent.n), keep)
+                f = None
+            else:
+                f = ops.gather_rows(f, keep)
             cm.release_maps()
             cm = pruned
-        colors = self.color(f, cm.nbr3(), cm.n)
+        if f is not None:
+            colors = self.color(f, cm.nbr3(), cm.n)
         out = SparseTensor(_cmap=cm, _feats=colors, _channels=3)
         out.num_frames = num_frames
         out.frame_counts = prev
@@ -429,17 +440,30 @@ def _synthesis_program(self, f, cm, k, num_frames, prev, on_geometry=None):
         else:
             pk = pr.alloc(m * 8)
         pr.add(prg.OP_GATHER_KEYS, ck, keep, m, pk)
-        pf = pr.alloc(m * c * 2)
-        pr.add(prg.OP_GATHER_ROWS_BF16, cur, c, keep, m, pf)
-        keys_ptr, n, cur = pk, m, pf
+        color_on_candidates = i == 2 and octet and self.color.w_oct is not None
+        if i == 2 and on_geometry is not None:
+            pr.flush()                 # the geometry is final here: the caller may start shipping it while the colours are computed
+            on_geometry(out_keys)
+        if color_on_candidates:
+            # (see __call__) pruned candidates zeroed in place, colour head over the complete octets, kept rows picked out
+            pr.add(prg.OP_ZERO_UNKEPT_ROWS, keep, m, nc, cur, c)
+            col_all = pr.alloc(nc * 3 * 4)
+            pr.conv_octet(self.color, cur, n, nbp, ldp, out_f32=col_all)
+            colors = torch.empty((m, 3), dtype=torch.float32, device=dev)
+            col_job = (col_all, keep, m)
+        else:
+            pf = pr.alloc(m * c * 2)
+            pr.add(prg.OP_GATHER_ROWS_BF16, cur, c, keep, m, pf)
+            cur = pf
+        keys_ptr, n = pk, m
         if i < 2:
             pr.flush()          # this level runs while the next one is recorded
-    if on_geometry is not None:
-        pr.flush()                 # the geometry is final here: the caller may start shipping it
-        on_geometry(out_keys)
-    nb, ld = pr.kmap_k3(keys_ptr, n, l2, up2 if up2 is not None else up1)
-    colors = torch.empty((n, 3), dtype=torch.float32, device=dev)
-    pr.conv(self.color, cur, n, nb, ld, n, out_f32=colors.data_ptr())
+    if color_on_candidates:
+        pr.add(prg.OP_GATHER_ROWS_F32, col_job[0], 3, col_job[1], col_job[2], colors.data_ptr())
+    else:
+        nb, ld = pr.kmap_k3(keys_ptr, n, l2, up2 if up2 is not None else up1)
+        colors = torch.empty((n, 3), dtype=torch.float32, device=dev)
+        pr.conv(self.color, cur, n, nb, ld, n, out_f32=colors.data_ptr())
     pr.keep += [f, kd_all, counts, out_keys, colors]
     pr.run()
     ocm = CoordMap(out_keys, l2)

@@ -277,8 +277,11 @@ def capture_voxelize(xyzrgba: torch.Tensor, voxel_size: float, depth_clip: float
     return pts, col, cnt
 
 
-def sort_unique(keys: torch.Tensor, want_src: bool = True, expect: Optional[int] = None, sync: bool = True):
-    """-> (unique sorted keys, src_row or None).  One host sync for the count, none with `expect`."""
+def sort_unique(keys: torch.Tensor, want_src: bool = True, expect: Optional[int] = None, sync: bool = True,
+                key_bits: int = 64):
+    """-> (unique sorted keys, src_row or None).  One host sync for the count, none with `expect`.
+    key_bits: the caller guarantees that bits [key_bits, 64) of every key are zero (frame index below
+    2^(key_bits - 48)); the radix sort then skips those digit passes."""
     _need_cuda(keys, torch.int64)
     n = keys.shape[0]
     dev = keys.device
@@ -290,7 +293,8 @@ def sort_unique(keys: torch.Tensor, want_src: bool = True, expect: Optional[int]
     wsb = lib.pcc_sort_unique_workspace_bytes(n)
     ws = workspace(wsb, dev)
     with _prof("sort_unique", n * (16 + 12 + (8 if want_src else 0))):
-        check(lib.pcc_sort_unique(_ptr(keys), n, _ptr(out), _ptr(src), _ptr(cnt), _ptr(ws), ws.numel(), _stream()))
+        check(lib.pcc_sort_unique_bits(_ptr(keys), n, int(key_bits), _ptr(out), _ptr(src), _ptr(cnt), _ptr(ws), ws.numel(),
+                                       _stream()))
     if expect is not None:
         m = int(expect)
         _defer(cnt, m, "sort_unique")
@@ -572,6 +576,15 @@ def gather_rows(src: torch.Tensor, src_row: torch.Tensor) -> torch.Tensor:
     else:
         raise _lib.PccError(f"gather_rows: unsupported dtype {src.dtype}")
     return out
+
+
+def zero_unkept_rows(feats: torch.Tensor, keep: torch.Tensor) -> None:
+    """In place: rows of feats [n, c] (bf16) that are not listed in keep (ascending int32 row numbers) become zero."""
+    _need_cuda(feats, torch.bfloat16)
+    _need_cuda(keep, torch.int32)
+    n, c = feats.shape
+    with _prof("zero_unkept_rows", (n - keep.shape[0]) * c * 2 + keep.shape[0] * 4):
+        check(lib.pcc_zero_unkept_rows(_ptr(keep), keep.shape[0], n, _ptr(feats), c, _stream()))
 
 
 def gather_rows_i32(src: torch.Tensor, src_row: torch.Tensor) -> torch.Tensor:

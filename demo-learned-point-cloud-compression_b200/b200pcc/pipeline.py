@@ -205,6 +205,11 @@ _TORCH_DT = {"int16": torch.int16, "float64": torch.float64, "int32": torch.int3
              "uint8": torch.uint8, "int64": torch.int64}
 
 
+def _gop_key_bits(num_frames: int) -> int:
+    """Significant bits of the coordinate keys of a GOP: 48 Morton bits + the frame index (keys are b << 48 | morton)."""
+    return 48 + max(0, (int(num_frames) - 1).bit_length())
+
+
 class CompressionPipeline:
     def __init__(self, settings, device=None, config="synth_small", model: ColorModel = None):
         self.device = _require_cuda(device)
@@ -298,7 +303,7 @@ class CompressionPipeline:
         for b in range(nf):
             ops.ingest_points(pts_d[pos:pos + counts[b]], b, keys[pos:pos + counts[b]])
             pos += counts[b]
-        ukeys_all, src_all, cnt = ops.sort_unique(keys, want_src=True, sync=False)
+        ukeys_all, src_all, cnt = ops.sort_unique(keys, want_src=True, sync=False, key_bits=_gop_key_bits(nf))
         self.h2d_bytes += total * 12
         # speculate: capturer frames hold no duplicate points, so carry on as if all rows were unique and
         # let compress() check the device count with the pyramid's read-back (one host wait fewer)
@@ -338,11 +343,11 @@ class CompressionPipeline:
             ops.ingest_frame(pts[b], cols[b], b, keys[pos:pos + n], feats[pos:pos + n])
             pos += n
         if speculate:      # see _unpack_host_frames
-            ukeys_all, src_all, cnt = ops.sort_unique(keys, want_src=True, sync=False)
+            ukeys_all, src_all, cnt = ops.sort_unique(keys, want_src=True, sync=False, key_bits=_gop_key_bits(nf))
             x = SparseTensor(_cmap=CoordMap(ukeys_all, 0), _feats=ops.rows_f32_to_bf16(feats, 16, src_all), _channels=4)
             x._unique = (cnt, ukeys_all, src_all)
         else:
-            ukeys, src = ops.sort_unique(keys, want_src=True)
+            ukeys, src = ops.sort_unique(keys, want_src=True, key_bits=_gop_key_bits(nf))
             x = SparseTensor(_cmap=CoordMap(ukeys, 0), _feats=ops.rows_f32_to_bf16(feats, 16, src), _channels=4)
         x.num_frames = nf
         return x, gop

@@ -30,6 +30,8 @@ OP_GATHER_KEYS = 8
 OP_FRAME_OFFSETS = 9
 OP_TOPK_SELECT = 10
 OP_SPCONV_OCTET = 11
+OP_ZERO_UNKEPT_ROWS = 12
+OP_GATHER_ROWS_F32 = 13
 
 _ROW = 20          # int64 words per entry: op + 19 arguments (pcc_op_t)
 _TLS = threading.local()
@@ -185,6 +187,10 @@ class Program:
             return "blockmap_build", int(a[1]) * 8 + int(a[5]) * 8 + (int(a[1]) // 8) * 24, 0, 0
         if op == OP_TOPK_SELECT:
             return "topk_select", int(a[2]) * 16, 0, 0
+        if op == OP_ZERO_UNKEPT_ROWS:
+            return "zero_unkept_rows", (int(a[2]) - int(a[1])) * int(a[4]) * 2 + int(a[1]) * 4, 0, 0
+        if op == OP_GATHER_ROWS_F32:
+            return "gather_rows", int(a[3]) * (int(a[1]) * 8 + 4), 0, 0
         return {OP_KMAP_DOWN2: "kmap_down2", OP_ROWS_F32_TO_BF16: "rows_f32_to_bf16", OP_COORDS_CHILDREN: "coords_children",
                 OP_GATHER_ROWS_BF16: "gather_rows", OP_GATHER_KEYS: "gather_keys", OP_FRAME_OFFSETS: "frame_offsets"}[op], 0, 0, 0
 

@@ -57,6 +57,12 @@ int pcc_run_program(const pcc_op_t* ops, int32_t n_ops, pcc_stream_t s, int32_t*
                               (const float*)a[6], (int)a[7], (const void*)a[8], a[9], (int)a[10], (void*)a[11],
                               (float*)a[12], a[13], (int)a[14], s);
         break;
+      case PCC_OP_ZERO_UNKEPT_ROWS:
+        rc = pcc_zero_unkept_rows((const int32_t*)a[0], a[1], a[2], (void*)a[3], (int)a[4], s);
+        break;
+      case PCC_OP_GATHER_ROWS_F32:
+        rc = pcc_gather_rows_f32((const float*)a[0], (int)a[1], (const int32_t*)a[2], a[3], (float*)a[4], s);
+        break;
       default:
         set_error("pcc_run_program: unknown op %lld at entry %d", (long long)ops[i].op, (int)i);
         rc = PCC_E_INVALID;

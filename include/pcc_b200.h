@@ -101,6 +101,9 @@ int pcc_coords_from_keys(const uint64_t* keys, int64_t n, int32_t* coords, pcc_s
 int64_t pcc_sort_unique_workspace_bytes(int64_t n);
 int pcc_sort_unique(const uint64_t* keys_in, int64_t n, uint64_t* keys_out, int32_t* src_row,
                     int32_t* n_out_dev, void* ws, int64_t ws_bytes, pcc_stream_t s);
+/* Same, for keys whose bits [key_bits, 64) are zero (frame index < 2^(key_bits - 48)): fewer radix passes. */
+int pcc_sort_unique_bits(const uint64_t* keys_in, int64_t n, int key_bits, uint64_t* keys_out, int32_t* src_row,
+                         int32_t* n_out_dev, void* ws, int64_t ws_bytes, pcc_stream_t s);
 
 /* Stride-2 convolution output coordinates: c' = floor(c / t') * t' (MinkowskiConvolution with
  * stride 2 inside g_a / h_a / g_s.down_conv: codec_pipeline.py:273,287; codec_parallel.py:302-303).
@@ -273,6 +276,12 @@ int pcc_gather_rows_f32(const float* src, int c, const int32_t* src_row, int64_t
                         pcc_stream_t s);
 int pcc_gather_keys(const uint64_t* src, const int32_t* src_row, int64_t n_out, uint64_t* dst,
                     pcc_stream_t s);
+/* Prune applied in place for a convolution over the UN-pruned candidates: rows of feats [n, c] (bf16) whose number is not
+ * in keep (ascending, m entries -- what pcc_topk_select emits) become zero.  MinkowskiPruning followed by a k3
+ * convolution on the kept set (the colour head after the last prune of g_s, receiver/decoder/codec_parallel.py:469)
+ * equals, on the kept rows, the same convolution over all candidates with the pruned rows zeroed -- and the candidates
+ * are complete octets, so it runs through pcc_spconv_octet on the parents' kernel map and needs no map of its own. */
+int pcc_zero_unkept_rows(const int32_t* keep, int64_t m, int64_t n, void* feats_bf16, int c, pcc_stream_t s);
 
 /* Per-frame top-k occupancy selection + pruning (torch.topk + MinkowskiPruning inside
  * g_s(y_hat, k=ks), codec_parallel.py:469).  Keeps, in frame b, the k[b] rows with the largest
@@ -385,6 +394,8 @@ int pcc_rans_decode(const uint8_t* container, int64_t container_bytes, int32_t s
 #define PCC_OP_FRAME_OFFSETS 9
 #define PCC_OP_TOPK_SELECT 10
 #define PCC_OP_SPCONV_OCTET 11
+#define PCC_OP_ZERO_UNKEPT_ROWS 12
+#define PCC_OP_GATHER_ROWS_F32 13
 typedef struct {
   int64_t op;
   int64_t a[19];
