@@ -29,7 +29,7 @@ struct Tables {
   int32_t total;         // cdf entries over all tables (0 = unknown)
 };
 
-constexpr int kLutBits = 7, kLutN = 1 << kLutBits, kLutShift = 16 - kLutBits;
+constexpr int kLutBits = 8, kLutN = 1 << kLutBits, kLutShift = 16 - kLutBits;
 
 // q = x / fr, rem = x % fr for x < fr * 2^16 (so q < 2^16): one float multiply gives q within +-1
 // (relative error 2^-22 on a quotient below 2^16), one correction step makes it exact.
@@ -311,7 +311,10 @@ constexpr int kWordCap = 8192;    // renormalisation words of a segment staged i
 // SMEM: the CTA first copies the tables into shared memory (CDF entries as uint16 -- only the
 // terminating 65536 of a row does not fit and is implied --, per-table {offset, last symbol, symbol
 // offset} and the search windows), so the dependent look-ups of a round cost shared-memory latency.
-template <bool SMEM>
+// HAS_IDX: the table of a symbol comes from the index array (Gaussian conditional); without it the table is the symbol's
+// channel (factorized prior).  A template parameter: as a run-time test it sat, with its 64-bit channel arithmetic, in
+// every prefetch slot of the one instruction stream a segment's time consists of.
+template <bool SMEM, bool HAS_IDX>
 __global__ void __launch_bounds__(32 * kDecWarps)
 k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, int32_t seg_size_arg,
               const uint16_t* __restrict__ idx, int64_t chan_len, int64_t n, int32_t nseg_arg, Tables T,
@@ -401,21 +404,21 @@ k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, in
   // to round (a 64-bit division per round would sit in the one instruction stream the warp's time consists of).
   // load_chunk is called for consecutive chunks, so the pair always belongs to the next round to be loaded.
   int64_t ch_q = 0, ch_r = 0;
-  if (!idx) {
+  if constexpr (!HAS_IDX) {
     ch_q = (start + lane) / chan_len;
     ch_r = (start + lane) - ch_q * chan_len;
   }
+  const uint16_t* idx_lane = HAS_IDX ? idx + start + lane : nullptr;      // this lane's entries: idx_lane[32 r]
   auto load_chunk = [&](int32_t r0, int32_t (&buf)[kChunk]) {   // rounds r0 ... r0+kChunk-1
 #pragma unroll
     for (int k = 0; k < kChunk; ++k) {
       const int32_t li = (r0 + k) * 32 + lane;
       // the raw value only: clamping here would make every chunk wait for its own loads
       int32_t t = -1;
-      if (r0 + k < rounds && li < cnt) {
-        const int64_t i = start + li;
-        t = idx ? (int32_t)__ldg(idx + i) : (int32_t)ch_q;
-      }
-      if (!idx) {
+      if constexpr (HAS_IDX) {
+        if (li < cnt) t = (int32_t)__ldg(idx_lane + (r0 + k) * 32);      // (li < cnt implies r0 + k < rounds)
+      } else {
+        if (r0 + k < rounds && li < cnt) t = (int32_t)ch_q;
         ch_r += 32;
         while (ch_r >= chan_len) {
           ch_r -= chan_len;
@@ -425,6 +428,7 @@ k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, in
       buf[k] = t;
     }
   };
+  int32_t* sym_lane = sym + start + lane;      // this lane's outputs: sym_lane[32 r]
   load_chunk(0, cur);
   for (int32_t r0 = 0; r0 < rounds; r0 += kChunk) {
     load_chunk(r0 + kChunk, nxt);
@@ -434,7 +438,6 @@ k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, in
       if (r >= rounds) break;
       const bool active = cur[k] >= 0;
       const int32_t t = cur[k] < T.T ? cur[k] : T.T - 1;
-      const int64_t i = start + r * 32 + lane;
       int32_t coff = 0, maxv = 0, offs = 0;
       if (active) {
         if (SMEM) {
@@ -510,7 +513,7 @@ k_rans_decode(const uint8_t* __restrict__ container, int64_t container_bytes, in
           val = (int64_t)(raw >> 1);
           if (raw & 1u) val = -val - 1; else val += maxv;
         }
-        sym[i] = (int32_t)(val + offs);
+        sym_lane[r * 32] = (int32_t)(val + offs);
       }
     }
 #pragma unroll
@@ -623,16 +626,20 @@ int pcc_rans_decode(const uint8_t* container, int64_t container_bytes, int32_t s
   static PerDeviceOnce configured;      // the opt-in is per device, not per process
   const int dev = current_device();
   if (configured.needed(dev)) {
-    PCC_CUDA(cudaFuncSetAttribute(k_rans_decode<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
-    PCC_CUDA(cudaFuncSetAttribute(k_rans_decode<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsm));
+    PCC_CUDA(cudaFuncSetAttribute(k_rans_decode<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+    PCC_CUDA(cudaFuncSetAttribute(k_rans_decode<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+    PCC_CUDA(cudaFuncSetAttribute(k_rans_decode<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsm));
+    PCC_CUDA(cudaFuncSetAttribute(k_rans_decode<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsm));
     configured.mark(dev);
   }
+  const int64_t cl = chan_len > 0 ? chan_len : 1;
+  const dim3 g(grid), b(32 * kDecWarps);
   if (T.lut && T.total > 0 && smem <= 224 * 1024) {
-    launch_pdl(k_rans_decode<true>, dim3(grid), dim3(32 * kDecWarps), smem, st, container, container_bytes, seg_size, idx,
-                                                          chan_len > 0 ? chan_len : 1, n, ns, T, sym, status_dev);
+    if (idx) launch_pdl(k_rans_decode<true, true>, g, b, smem, st, container, container_bytes, seg_size, idx, cl, n, ns, T, sym, status_dev);
+    else launch_pdl(k_rans_decode<true, false>, g, b, smem, st, container, container_bytes, seg_size, idx, cl, n, ns, T, sym, status_dev);
   } else {
-    launch_pdl(k_rans_decode<false>, dim3(grid), dim3(32 * kDecWarps), wsm, st, container, container_bytes, seg_size, idx,
-                                                        chan_len > 0 ? chan_len : 1, n, ns, T, sym, status_dev);
+    if (idx) launch_pdl(k_rans_decode<false, true>, g, b, wsm, st, container, container_bytes, seg_size, idx, cl, n, ns, T, sym, status_dev);
+    else launch_pdl(k_rans_decode<false, false>, g, b, wsm, st, container, container_bytes, seg_size, idx, cl, n, ns, T, sym, status_dev);
   }
   PCC_LAUNCHED();
   return PCC_OK;

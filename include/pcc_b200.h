@@ -340,14 +340,14 @@ typedef struct {
   const int32_t* cdf_off;   /* [T] start of table t in cdf */
   const int32_t* cdf_size;  /* [T] entries in table t (= pmf_length + 2) */
   const int32_t* offset;    /* [T] symbol offset of table t */
-  const uint16_t* lut;      /* [T][129] decode search windows from pcc_rans_build_lut, or NULL */
+  const uint16_t* lut;      /* [T][257] decode search windows from pcc_rans_build_lut, or NULL */
   int32_t num_tables;
   int32_t cdf_total;        /* entries in cdf over all tables; 0 = unknown (decoder then reads the
                                tables from global memory instead of staging them in shared memory) */
 } pcc_cdf_tables_t;
 
-/* Decoder acceleration table: lut[t][b] = largest s with cdf_t[s] <= b << 9 (b = 0..127),
- * lut[t][128] = last symbol; narrows the CDF search to a few entries.  pcc_rans_lut_entries()
+/* Decoder acceleration table: lut[t][b] = largest s with cdf_t[s] <= b << 8 (b = 0..255),
+ * lut[t][256] = last symbol; narrows the CDF search to a few entries.  pcc_rans_lut_entries()
  * uint16 elements; build once per table set (model.update()). */
 int64_t pcc_rans_lut_entries(int32_t num_tables);
 int pcc_rans_build_lut(const pcc_cdf_tables_t* tables, uint16_t* lut, pcc_stream_t s);
