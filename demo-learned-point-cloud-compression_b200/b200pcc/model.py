@@ -263,6 +263,8 @@ def _analysis_program(self, f, cm, nlev):
         pr.conv(self.down[i], cur, cm.n, nd, ld, coarse.n, out_bf16=o, relu=True)
         cm, cur = coarse, o
         nb, ld3 = pr.kmap_k3(cm.keys.data_ptr(), cm.n, cm.log2_stride, _block_bound(cm))
+        if i == 0:
+            pr.flush()          # the GPU has been waiting for the level sizes: hand it the first kernels at once
         cur = pr.resblocks(self.blocks[i], cur, cm.n, c, nb, ld3)
         if i == 0:
             pr.flush()

@@ -48,9 +48,17 @@ def main():
     busy = sum(b - a for a, b, _ in ks)
     span = ks[-1][1] - t0
     print(f"{len(ks)} device activities, span {span / 1e3:.3f} ms, busy {busy / 1e3:.3f} ms, idle {(span - busy) / 1e3:.3f} ms")
+    # idle = the complement of the UNION of the activities (copies on side streams and programmatic dependent launches
+    # overlap): a gap starts at the latest end seen so far, not at the end of the previously started activity
     gaps = []
-    for (a0, b0, n0), (a1, b1, n1) in zip(ks[:-1], ks[1:]):
-        gaps.append((a1 - b0, (b0 - t0) / 1e3, n0[:50], n1[:50]))
+    end, last = ks[0][1], ks[0][2]
+    for a1, b1, n1 in ks[1:]:
+        if a1 > end:
+            gaps.append((a1 - end, (end - t0) / 1e3, last[:50], n1[:50]))
+        if b1 > end:
+            end, last = b1, n1
+    union_idle = sum(g for g, *_ in gaps)
+    print(f"union of activities: busy {(span - union_idle) / 1e3:.3f} ms, idle {union_idle / 1e3:.3f} ms in {len(gaps)} gaps")
     small = sum(g for g, *_ in gaps if 0 < g <= 10)
     print(f"sum of gaps <= 10 us: {small / 1e3:.3f} ms over {sum(1 for g, *_ in gaps if 0 < g <= 10)} gaps")
     if e2e:
