@@ -9,6 +9,10 @@ A "step" = compress() + decompress() of one GOP of one synthetic 8iVFB-shaped fr
 frame already resident in HBM and the reconstruction left on the device; `e2e` goes through the public
 CompressionPipeline.compress(gop) / DecompressionPipeline.decompress(bytes) calls with host buffers
 (host->device copy of the frame and device->host copy of the reconstruction inside the timed region).
+Both are throughputs with --inflight (default 2) GOPs per GPU: caller threads, each with its own pipeline
+pair and CUDA stream, as the reference's encoder / decoder services run 3-worker pools around the two calls;
+the K steps are bracketed by one start and one end event that all caller streams are tied to.  The latencies
+(`latency_ms`, `rank_step_ms`) and the one-caller throughput (`sequential`) come from a separate pass.
 Frames are independent, so with N GPUs every rank codes its own frames (weak scaling, no collective on
 the data path); the timed region is bracketed by barrier + synchronize and the max over ranks is used.
 """
@@ -60,9 +64,32 @@ class ClockSampler(threading.Thread):
         self.max_mhz = None
 
     def run(self):
+        # NVML in-process when the module is there (a query costs microseconds); nvidia-smi otherwise -- starting that
+        # program every 0.2 s attaches to the driver each time, which showed up as stalls of the two caller threads
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            bits = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            get_reasons = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+                pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
+            while not self.stop_flag:
+                try:
+                    self.samples.append(float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)))
+                    r = int(get_reasons(h))
+                    for n in names:
+                        if r & bits[n]:
+                            self.reasons.add(n)
+                except Exception:
+                    pass
+                time.sleep(0.05)
+            return
+        except Exception:
+            pass
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         while not self.stop_flag:
             try:
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i",
@@ -250,6 +277,66 @@ def run_configs(model, dev):
     return {"cfg1": bc.cfg1(model, dev, 10), "cfg3": bc.cfg3(model, dev, 120, 30.0), "cfg5": bc.cfg5(model, dev, 6)}
 
 
+def run_inflight(torch, pairs, streams, gop_of, staged_of, steps, flush, host_buffers, barrier):
+    """K steps (compress + decompress of one GOP each) issued by len(pairs) caller threads, worker w taking the steps
+    w, w + W, ...; every worker has its own pipeline pair and CUDA stream, so the kernels of one GOP fill the gaps and the
+    thin phases (lane coder, host turn-arounds) of the other.  Device time: a start event every worker stream waits
+    for, an end event that waits for every worker.  The L2 flush of a step is inside the timed region.
+    -> (seconds, points coded)."""
+    import threading
+    import itertools
+    W = len(pairs)
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ends = [torch.cuda.Event() for _ in range(W)]
+    errors, pts = [], [0] * W
+    ticket, ticket_lock = itertools.count(), threading.Lock()
+
+    def next_step():          # the callers draw their steps from one counter, so they finish together
+        with ticket_lock:
+            i = next(ticket)
+        return i if i < steps else None
+
+    def work(w):
+        try:
+            enc, dec = pairs[w]
+            with torch.cuda.stream(streams[w]):
+                streams[w].wait_event(start)
+                out = None
+                while True:
+                    i = next_step()
+                    if i is None:
+                        break
+                    flush.fill_(i & 0xFF)
+                    g, n = gop_of(i)
+                    c, _ = enc.compress(g) if host_buffers else enc.compress(g, staged=staged_of(w, i))
+                    out = dec.decompress(c[1], to_host=host_buffers)
+                    pts[w] += n
+                ends[w].record(streams[w])
+                del out
+        except BaseException as exc:      # noqa: BLE001  (reported by the caller; a worker must not die silently)
+            errors.append(f"worker {w}: {exc!r}")
+
+    # the interpreter hands the lock over every 5 ms by default: a caller coming back from a C call could wait that long
+    # behind the other one's Python; 0.2 ms keeps the two launch sequences interleaved
+    switch = sys.getswitchinterval()
+    sys.setswitchinterval(2e-4)
+    barrier()
+    start.record()
+    threads = [threading.Thread(target=work, args=(w,), name=f"bench-caller-{w}") for w in range(W)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    sys.setswitchinterval(switch)
+    if errors:
+        raise SystemExit("bench: " + "; ".join(errors))
+    for w in range(W):
+        torch.cuda.current_stream().wait_event(ends[w])
+    end.record()
+    barrier()
+    return start.elapsed_time(end) * 1e-3, sum(pts)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -263,6 +350,9 @@ def main():
     ap.add_argument("--points", type=int, default=800_000)
     ap.add_argument("--breakdown", action="store_true", help="print per-kernel-family table to stderr")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer arm (short runs under ncu)")
+    ap.add_argument("--inflight", type=int, default=2,
+                    help="GOPs in flight per GPU in the throughput arms: caller threads, each with its own pipeline pair and "
+                         "CUDA stream (the reference runs 3-worker pools around compress() / decompress()); 1 = one caller")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -342,11 +432,32 @@ def main():
     barrier()
     t_wall = time.time() - t_wall0
     launches = _lib.launch_count() - launches0
-    clocks = sampler.result()
     enc_ms = [a.elapsed_time(b) for a, b, _ in ev]
     dec_ms = [b.elapsed_time(c_) for _, b, c_ in ev]
     step_ms = [a + b for a, b in zip(enc_ms, dec_ms)]
     total_s = sum(step_ms) * 1e-3
+    seq_value = pts_done / total_s / 1e6          # one caller: the sum of the steps' own device times (flush excluded)
+    seq_ms_per_step = 1e3 * total_s / steps
+
+    # ---------------- throughput: `inflight` GOPs per GPU, each caller thread with its own pipelines and stream ----------------
+    W = max(1, args.inflight)
+    pairs = [(enc, dec)] + [(CompressionPipeline(settings, device=dev, model=model), DecompressionPipeline(device=dev, model=model))
+                            for _ in range(W - 1)]
+    streams = [torch.cuda.Stream(device=dev) for _ in range(W)]
+    if W > 1:
+        staged_w = [staged] + [[pairs[w][0].stage_frames(g["frames"]) for g in (gop(0), gop(1))] for w in range(1, W)]
+        torch.cuda.synchronize()
+        for w in range(1, W):                      # warm the new pipelines (workspaces, pinned buffers) one by one ...
+            for i in range(max(warmup, 3)):
+                c, _ = pairs[w][0].compress(gop(i), staged=staged_w[w][i % n_frames])
+                pairs[w][1].decompress(c[1], to_host=False)
+        run_inflight(torch, pairs, streams, lambda i: (gop(i), n_points[i % n_frames]),
+                     lambda w, i: staged_w[w][i % n_frames], max(4 * W, 8), flush, False, barrier)     # ... and together
+        launches0 = _lib.launch_count()
+        total_s, pts_done = run_inflight(torch, pairs, streams, lambda i: (gop(i), n_points[i % n_frames]),
+                                         lambda w, i: staged_w[w][i % n_frames], steps, flush, False, barrier)
+        launches = _lib.launch_count() - launches0
+    clocks = sampler.result()
 
     # ---------------- per-kernel pass (roofline leg): the same steps once more with a CUDA-event pair
     # around every launch of this library (programs then run entry by entry); not part of `value` ----
@@ -388,8 +499,23 @@ def main():
         print("e2e per-step ms: " + " ".join(f"{t:.2f}" for t in e2e_ms), file=sys.stderr)
     e2e_total = sum(e2e_ms) * 1e-3
     e2e_pts = sum(n_points[i % n_frames] for i in range(e2e_steps))
-
     e2e_h2d, e2e_d2h = enc2.h2d_bytes + dec2.h2d_bytes, enc2.d2h_bytes + dec2.d2h_bytes
+    e2e_seq = None if not e2e_steps else {"value": e2e_pts / e2e_total / 1e6, "ms_per_step": 1e3 * e2e_total / e2e_steps}
+    if W > 1 and e2e_steps:
+        pairs2 = [(enc2, dec2)] + [(CompressionPipeline(settings, device=dev, model=model), DecompressionPipeline(device=dev, model=model))
+                                   for _ in range(W - 1)]
+        for w in range(1, W):
+            for i in range(max(warmup, 4)):
+                c, _ = pairs2[w][0].compress(gop(i))
+                pairs2[w][1].decompress(c[1])
+        run_inflight(torch, pairs2, streams, lambda i: (gop(i), n_points[i % n_frames]), None, max(6 * W, 12), flush, True, barrier)
+        for e_, d_ in pairs2:
+            e_.h2d_bytes = e_.d2h_bytes = d_.h2d_bytes = d_.d2h_bytes = 0
+        e2e_steps = steps
+        e2e_total, e2e_pts = run_inflight(torch, pairs2, streams, lambda i: (gop(i), n_points[i % n_frames]), None, e2e_steps,
+                                          flush, True, barrier)
+        e2e_h2d = sum(e_.h2d_bytes + d_.h2d_bytes for e_, d_ in pairs2)
+        e2e_d2h = sum(e_.d2h_bytes + d_.d2h_bytes for e_, d_ in pairs2)
 
     # ---------------- the other BASELINE.json configurations ----------------
     configs = None
@@ -482,6 +608,12 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": roof,
+            # value / e2e are throughputs with `inflight` GOPs per GPU (caller threads with their own pipeline pair and
+            # CUDA stream, like the reference's 3-worker pools around compress() / decompress()); the one-caller numbers
+            # (sum of the steps' own device times) and the latencies above are measured in a separate pass
+            "inflight": W,
+            "sequential": {"value": seq_value, "ms_per_step": seq_ms_per_step, "e2e": e2e_seq,
+                           "note": "one caller, rank 0: compress() then decompress() of a GOP, next GOP after that"},
         }
         line["rank_step_ms"] = rank_stats
         if configs is not None:

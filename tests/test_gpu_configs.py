@@ -128,3 +128,42 @@ def test_three_concurrent_callers(model, dev):
     assert not errors, errors
     for a, b in zip(serial, results):
         assert a[0] == b[0] and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+
+
+def test_two_gops_in_flight_on_their_own_streams(model, dev):
+    """bench.py's throughput arms: two caller threads, each with its OWN pipeline pair and CUDA stream, code different
+    frames at the same time on one GPU (the kernels of the two GOPs interleave).  Every result must equal the serial
+    one bit for bit: bitstream, points, colours."""
+    from b200pcc import CompressionPipeline, DecompressionPipeline, synth
+    frames = [synth.small_frame(seed=60 + i, n_target=30_000 + 9000 * (i % 3)) for i in range(8)]
+    enc = CompressionPipeline([[1.0, 1.0]], device=dev, model=model)
+    dec = DecompressionPipeline(device=dev, model=model)
+    serial = []
+    for f in frames:
+        c, _ = enc.compress({"frames": [copy.deepcopy(f)]})
+        o, _ = dec.decompress(c[1])
+        serial.append((c[1], o[0]["points"].copy(), o[0]["colors"].copy()))
+    W = 2
+    pairs = [(CompressionPipeline([[1.0, 1.0]], device=dev, model=model), DecompressionPipeline(device=dev, model=model))
+             for _ in range(W)]
+    streams = [torch.cuda.Stream(device=dev) for _ in range(W)]
+    results = [None] * len(frames)
+    errors = []
+
+    def work(w):
+        try:
+            with torch.cuda.stream(streams[w]):
+                for rep in range(2):
+                    for i in range(w, len(frames), W):
+                        c, _ = pairs[w][0].compress({"frames": [copy.deepcopy(frames[i])]})
+                        o, _ = pairs[w][1].decompress(c[1])
+                        results[i] = (c[1], o[0]["points"].copy(), o[0]["colors"].copy())
+        except Exception as e:   # noqa: BLE001
+            errors.append(e)
+    ts = [threading.Thread(target=work, args=(w,)) for w in range(W)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    torch.cuda.synchronize()
+    assert not errors, errors
+    for a, b in zip(serial, results):
+        assert a[0] == b[0] and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])

@@ -1,4 +1,8 @@
-# round 2, call 11: several GOPs in flight on one GPU (feasibility)
+# round 2, call 13: variance of the two-in-flight arms (five runs)
 set -x
-timeout 300 python tools/inflight_bench.py --workers 1,2,3 --steps 24 > gpurun_out/r2n_inflight.txt 2>&1; cat gpurun_out/r2n_inflight.txt | tail -n 12
-timeout 300 python tools/inflight_bench.py --workers 1,2,3 --steps 24 --e2e > gpurun_out/r2n_inflight_e2e.txt 2>&1; cat gpurun_out/r2n_inflight_e2e.txt | tail -n 12
+for r in 1 2 3 4 5; do python bench.py --no-configs --no-cpu-baseline > gpurun_out/r2p_bench_run$r.json 2> gpurun_out/r2p_bench_run$r.err; echo "bench rc $?"; tail -n 2 gpurun_out/r2p_bench_run$r.err; python - <<PY
+import json
+d=json.loads(open("gpurun_out/r2p_bench_run$r.json").read().strip().splitlines()[-1])
+print("RUN $r", round(d["value"],1), round(d["ms_per_step"],3), "e2e", round(d["e2e"]["value"],1), "seq", round(d["sequential"]["value"],1), round(d["sequential"]["e2e"]["value"],1), d["clocks"])
+PY
+done
