@@ -381,7 +381,7 @@ def main():
             cores = sorted(os.sched_getaffinity(0))
             lw = int(os.environ.get("LOCAL_WORLD_SIZE", world))
             per = len(cores) // lw
-            if per >= 2:
+            if per >= 2 and os.environ.get("PCC_BENCH_PIN", "1") != "0":
                 os.sched_setaffinity(0, set(cores[local * per:(local + 1) * per]))
         except (AttributeError, OSError):
             pass

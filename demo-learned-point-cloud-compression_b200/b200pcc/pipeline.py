@@ -6,6 +6,7 @@ shares one result dict between them; here a call is one stream-ordered sequence 
 serialised per pipeline object by a lock (the callers use a 3-worker pool: encoder.py:50,75,
 decoder.py:47), so concurrent callers cannot receive each other's results.
 """
+import os
 import threading
 import time
 from typing import List
@@ -41,19 +42,43 @@ def _shared_model(device, config):
         return _MODEL_CACHE[key]
 
 
+_NVTX = os.environ.get("PCC_NVTX", "0") not in ("", "0")
+ENC_STAGES = ("unpack", "analysis", "geometry_compression", "hyper_analysis", "factorized_model", "hyper_synthesis",
+              "gaussian_model")
+DEC_STAGES = ("bitstream_reading", "geometry_decompression", "factorized_model", "hyper_synthesis", "guassian_model",
+              "synthesis_transform")
+
+
 class _StageTimer:
     """CUDA-event stage timing resolved after the call's final sync (the reference brackets each
-    stage with torch.cuda.synchronize(): codec_pipeline.py:270-291)."""
+    stage with torch.cuda.synchronize(): codec_pipeline.py:270-291).  mark(name) closes the stage `name`.
+    With PCC_NVTX=1 every stage is also an NVTX range named after the reference's stage key
+    (`pcc.enc.analysis`, `pcc.dec.guassian_model`, ... -- codec_pipeline.py:218-225, codec_parallel.py:156-163) for
+    Nsight timelines; `order` is the sequence of stage keys the caller is going to close."""
 
-    def __init__(self):
+    def __init__(self, order=None, prefix="pcc"):
         self.marks = []
+        self.order = order if _NVTX else None
+        self.prefix = prefix
+        self.open = False
 
     def mark(self, name):
         ev = torch.cuda.Event(enable_timing=True)
         ev.record()
         self.marks.append((name, ev, time.time()))
+        if self.order is not None:
+            if self.open:
+                torch.cuda.nvtx.range_pop()
+                self.open = False
+            i = len(self.marks) - 1          # mark 0 is "start": stage order[i] begins now
+            if i < len(self.order):
+                torch.cuda.nvtx.range_push(f"{self.prefix}.{self.order[i]}")
+                self.open = True
 
     def resolve(self):
+        if self.open:
+            torch.cuda.nvtx.range_pop()
+            self.open = False
         out = {}
         for (n0, e0, _), (n1, e1, _) in zip(self.marks[:-1], self.marks[1:]):
             out[n1] = out.get(n1, 0.0) + e0.elapsed_time(e1) * 1e-3
@@ -432,7 +457,7 @@ class CompressionPipeline:
         with self._lock, torch.cuda.device(self.device), ops.stream_scope():
             t_start = time.time()
             compressed_data = {0: data["frames"]}
-            tm = _StageTimer()
+            tm = _StageTimer(ENC_STAGES, "pcc.enc")
             tm.mark("start")
             x, sideinfo = self.unpack_batch(data, staged, defer_features=True, speculate=True)
             nf = x.num_frames
@@ -627,7 +652,7 @@ class DecompressionPipeline:
         with self._lock, torch.cuda.device(self.device), ops.stream_scope():
             t_start = time.time()
             ops.clear_deferred()
-            tm = _StageTimer()
+            tm = _StageTimer(DEC_STAGES, "pcc.dec")
             tm.mark("start")
             y_strings, z_strings, y_shape, z_shape, points_streams, ks, q = self.read_bitstream_batched(compressed_data)
             nf = len(points_streams)

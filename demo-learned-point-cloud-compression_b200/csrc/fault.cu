@@ -1,5 +1,6 @@
 // Device fault word + small per-device caches shared by the launchers (see common.cuh).
 #include "common.cuh"
+#include <cstdlib>
 
 namespace pcc {
 
@@ -28,6 +29,9 @@ int sm_count() {
   int d = 0;
   if (cudaGetDevice(&d) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, d) != cudaSuccess || n <= 0)
     n = 148;
+  // PCC_CONV_SMS (measurements): cap the persistent convolution grids, leaving SMs to kernels of another stream
+  const char* cap = getenv("PCC_CONV_SMS");
+  if (cap && atoi(cap) > 0 && atoi(cap) < n) n = atoi(cap);
   cache[dev].store(n, std::memory_order_release);
   return n;
 }

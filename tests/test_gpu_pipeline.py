@@ -298,3 +298,25 @@ def test_playout_buffers_match_client_packing(model, dev, frames):
         want = np.array(points, dtype=np.float32).tobytes() + np.array(colors, dtype=np.uint8).tobytes()
         assert buf == want
     assert dec.playout_buffers(x_hat, num_frames=len(frames)) == got
+
+
+def test_nvtx_stage_ranges_do_not_change_results(model, dev, frames, monkeypatch):
+    """PCC_NVTX=1: every stage of compress() / decompress() is an NVTX range named after the reference's stage key;
+    the ranges are balanced and the results are the ones without them."""
+    from b200pcc import pipeline as P
+    enc = P.CompressionPipeline([[1.0, 1.0]], device=dev, model=model)
+    dec = P.DecompressionPipeline(device=dev, model=model)
+    c0, _ = enc.compress(_gop(frames))
+    o0, _ = dec.decompress(c0[1])
+    monkeypatch.setattr(P, "_NVTX", True)
+    pushed, popped = [], []
+    monkeypatch.setattr(torch.cuda.nvtx, "range_push", lambda name: pushed.append(name))
+    monkeypatch.setattr(torch.cuda.nvtx, "range_pop", lambda: popped.append(1))
+    c1, s1 = enc.compress(_gop(frames))
+    o1, d1 = dec.decompress(c1[1])
+    assert c1[1] == c0[1]
+    for a, b in zip(o0, o1):
+        assert np.array_equal(a["points"], b["points"]) and np.array_equal(a["colors"], b["colors"])
+    assert pushed == [f"pcc.enc.{k}" for k in P.ENC_STAGES] + [f"pcc.dec.{k}" for k in P.DEC_STAGES]
+    assert len(popped) == len(pushed)
+    assert set(d1["time_measurements"]) >= set(P.DEC_STAGES)

@@ -1,8 +1,9 @@
-# round 2, call 13: variance of the two-in-flight arms (five runs)
+# round 2, call 18: two callers in phase vs out of phase; persistent conv grids capped below 148 SMs
 set -x
-for r in 1 2 3 4 5; do python bench.py --no-configs --no-cpu-baseline > gpurun_out/r2p_bench_run$r.json 2> gpurun_out/r2p_bench_run$r.err; echo "bench rc $?"; tail -n 2 gpurun_out/r2p_bench_run$r.err; python - <<PY
-import json
-d=json.loads(open("gpurun_out/r2p_bench_run$r.json").read().strip().splitlines()[-1])
-print("RUN $r", round(d["value"],1), round(d["ms_per_step"],3), "e2e", round(d["e2e"]["value"],1), "seq", round(d["sequential"]["value"],1), round(d["sequential"]["e2e"]["value"],1), d["clocks"])
-PY
+for st in 0 2.5; do
+  timeout 300 python tools/inflight_bench.py --workers 2 --steps 20 --reps 8 --stagger-ms $st 2>&1 | grep workers
+  timeout 300 python tools/inflight_bench.py --workers 2 --steps 20 --reps 8 --stagger-ms $st --e2e 2>&1 | grep workers
+done
+for cap in 140 132; do
+  PCC_CONV_SMS=$cap timeout 300 python tools/inflight_bench.py --workers 1,2 --steps 20 --reps 5 2>&1 | grep "workers" | sed "s/^/cap $cap: /"
 done

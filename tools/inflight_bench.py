@@ -6,6 +6,7 @@ for to an end event that waits for all of them.  Usage: python tools/inflight_be
 import os
 import sys
 import threading
+import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 for p in (ROOT, os.path.join(ROOT, "demo-learned-point-cloud-compression_b200")):
@@ -25,6 +26,8 @@ def main():
     workers_list = [int(w) for w in arg("--workers", "1,2,3").split(",")]
     steps = int(arg("--steps", "24"))
     e2e = "--e2e" in sys.argv
+    stagger_ms = float(arg("--stagger-ms", "0"))
+    reps = int(arg("--reps", "1"))
     model = load_model(dev)
     frames = [synth.frame_8ivfb(seed=1 + i) for i in range(2)]
     npts = [len(f["points"]) for f in frames]
@@ -45,6 +48,8 @@ def main():
                 with torch.cuda.stream(streams[w]):
                     if timed:
                         streams[w].wait_event(start)
+                        if stagger_ms and w:
+                            time.sleep(1e-3 * stagger_ms * w / W)      # callers out of phase: one encodes while the other decodes
                     for i in range(n):
                         j = (w + i) % 2
                         flush.fill_(i & 0xFF)          # L2 flush between this worker's iterations (inside the timed region)
@@ -58,7 +63,8 @@ def main():
             except Exception as exc:      # noqa: BLE001
                 errors.append(repr(exc))
 
-        for timed, n in ((False, 4), (True, steps // W)):
+        results = []
+        for timed, n in [(False, 4)] + [(True, steps // W)] * reps:
             torch.cuda.synchronize()
             if timed:
                 start.record()
@@ -72,15 +78,18 @@ def main():
                     torch.cuda.current_stream().wait_event(ends[w])
                 end.record()
             torch.cuda.synchronize()
+            if timed:
+                results.append(start.elapsed_time(end))
         if errors:
             print(f"workers {W}: ERROR {errors[:2]}")
             continue
-        ms = start.elapsed_time(end)
+        ms = float(np.median(results))
         done = (steps // W) * W
         pts = sum(npts[(w + i) % 2] for w in range(W) for i in range(steps // W))
         ref_bytes.setdefault(0, digests[0])
         same = all(d == ref_bytes[0] for d in digests if d is not None)
-        print(f"workers {W}: {done} steps in {ms:.2f} ms -> {ms / done:.3f} ms/step, {pts / ms / 1e3:.1f} Mpoints/s "
+        print(f"workers {W} stagger {stagger_ms} ms, {reps} reps, ms/step each: " + " ".join(f"{r / done:.3f}" for r in results))
+        print(f"workers {W}: {done} steps in {ms:.2f} ms (median) -> {ms / done:.3f} ms/step, {pts / ms / 1e3:.1f} Mpoints/s "
               f"({'host buffers' if e2e else 'resident'}; flush inside; frame-0 bitstreams identical across workers: {same})")
 
 
