@@ -278,6 +278,10 @@ def run_configs(model, dev):
 
 
 def run_inflight(torch, pairs, streams, gop_of, staged_of, steps, flush, host_buffers, barrier):
+    # Resident frames: the callers draw their steps from one counter and start together (183-187 Mpoints/s over five
+    # runs; out of phase 175-187).  Host buffers: caller w takes the steps w, w + W, ... and starts w / W of 2.5 ms late,
+    # so that one caller's copies fall on the other's kernels (4.55-4.82 ms/step against 4.75-5.09 in phase,
+    # tools/inflight_bench.py --stagger-ms, profiles/r2u_*).
     """K steps (compress + decompress of one GOP each) issued by len(pairs) caller threads, worker w taking the steps
     w, w + W, ...; every worker has its own pipeline pair and CUDA stream, so the kernels of one GOP fill the gaps and the
     thin phases (lane coder, host turn-arounds) of the other.  Device time: a start event every worker stream waits
@@ -291,8 +295,12 @@ def run_inflight(torch, pairs, streams, gop_of, staged_of, steps, flush, host_bu
     errors, pts = [], [0] * W
     ticket, ticket_lock = itertools.count(), threading.Lock()
 
-    def next_step():          # the callers draw their steps from one counter, so they finish together
-        with ticket_lock:
+    mine = [iter(range(w, steps, W)) for w in range(W)]
+
+    def next_step(w):
+        if host_buffers:      # fixed share: the callers keep their phase offset
+            return next(mine[w], None)
+        with ticket_lock:     # one counter: the callers finish together
             i = next(ticket)
         return i if i < steps else None
 
@@ -301,9 +309,11 @@ def run_inflight(torch, pairs, streams, gop_of, staged_of, steps, flush, host_bu
             enc, dec = pairs[w]
             with torch.cuda.stream(streams[w]):
                 streams[w].wait_event(start)
+                if w and host_buffers:       # callers out of phase: one copies while the other computes
+                    time.sleep(2.5e-3 * w / W)
                 out = None
                 while True:
-                    i = next_step()
+                    i = next_step(w)
                     if i is None:
                         break
                     flush.fill_(i & 0xFF)

@@ -1,9 +1,15 @@
-# round 2, call 18: two callers in phase vs out of phase; persistent conv grids capped below 148 SMs
+# round 2, call 21 (8 GPUs): per-rank core pinning off (default: on)
 set -x
-for st in 0 2.5; do
-  timeout 300 python tools/inflight_bench.py --workers 2 --steps 20 --reps 8 --stagger-ms $st 2>&1 | grep workers
-  timeout 300 python tools/inflight_bench.py --workers 2 --steps 20 --reps 8 --stagger-ms $st --e2e 2>&1 | grep workers
-done
-for cap in 140 132; do
-  PCC_CONV_SMS=$cap timeout 300 python tools/inflight_bench.py --workers 1,2 --steps 20 --reps 5 2>&1 | grep "workers" | sed "s/^/cap $cap: /"
-done
+PCC_BENCH_PIN=0 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29543 bench.py --gpus 8 --steps 20 --warmup 3 --no-configs > gpurun_out/r2s_bench_n8_nopin.json 2> gpurun_out/r2s_bench_n8_nopin.err; echo "n8 nopin rc $?"
+python - <<PY
+import json
+d=json.loads(open("gpurun_out/r2s_bench_n8_nopin.json").read().strip().splitlines()[-1])
+print("NOPIN", round(d["value"],1), round(d["ms_per_step"],3), "e2e", round(d["e2e"]["value"],1), round(d["e2e"]["ms_per_step"],3), "seq", d["sequential"], d["rank_step_ms"])
+PY
+python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29544 bench.py --gpus 8 --steps 20 --warmup 3 --no-configs > gpurun_out/r2s_bench_n8_pin.json 2> gpurun_out/r2s_bench_n8_pin.err; echo "n8 pin rc $?"
+python - <<PY
+import json
+d=json.loads(open("gpurun_out/r2s_bench_n8_pin.json").read().strip().splitlines()[-1])
+print("PIN", round(d["value"],1), round(d["ms_per_step"],3), "e2e", round(d["e2e"]["value"],1), round(d["e2e"]["ms_per_step"],3), "seq", d["sequential"], d["rank_step_ms"])
+PY
+lscpu -e | head -36
