@@ -77,6 +77,7 @@ SIGNATURES = {
     "pcc_frame_offsets": (INT, [P, I64, I32, P, P]),
     "pcc_lex_order_workspace_bytes": (I64, [I64]),
     "pcc_lex_order": (INT, [P, I64, P, P, I64, P]),
+    "pcc_lex_order_bits": (INT, [P, I64, INT, INT, P, P, I64, P]),
     "pcc_octree_max_bytes": (I64, [I64]),
     "pcc_octree_encode_workspace_bytes": (I64, [I64, I32]),
     "pcc_octree_encode": (INT, [P, I64, P, I32, INT, P, P, P, P, I64, P]),

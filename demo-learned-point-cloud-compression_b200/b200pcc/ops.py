@@ -494,12 +494,16 @@ def frame_offsets(keys: torch.Tensor, num_frames: int) -> torch.Tensor:
     return off
 
 
-def lex_order(keys: torch.Tensor) -> torch.Tensor:
+def lex_order(keys: torch.Tensor, log2_stride: int = 0, frame_bits: int = 16) -> torch.Tensor:
+    """perm[r] = row holding canonical (b,x,y,z) rank r.  log2_stride / frame_bits: what the caller knows about the
+    keys (coordinates are multiples of 2^log2_stride, frame index < 2^frame_bits) -- fewer radix passes; the defaults
+    assume nothing."""
     n = keys.shape[0]
     perm = torch.empty(n, dtype=torch.int32, device=keys.device)
     wsb = lib.pcc_lex_order_workspace_bytes(n)
     ws = workspace(wsb, keys.device)
-    check(lib.pcc_lex_order(_ptr(keys), n, _ptr(perm), _ptr(ws), ws.numel(), _stream()))
+    check(lib.pcc_lex_order_bits(_ptr(keys), n, int(log2_stride), int(frame_bits), _ptr(perm), _ptr(ws), ws.numel(),
+                                 _stream()))
     return perm
 
 

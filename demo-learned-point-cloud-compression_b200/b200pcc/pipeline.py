@@ -540,7 +540,9 @@ class DecompressionPipeline:
         device (replaces gpcc_decode + stack_tensors, codec_parallel.py:266-289).  The octree expands
         in ascending key order, so no sort / de-duplication pass follows."""
         ykeys, status = geometry.decode_device(blob_d, offs_d, meta32_d, counts)
-        return CoordMap(ykeys, geometry.LOG2_STRIDE), status
+        ycm = CoordMap(ykeys, geometry.LOG2_STRIDE)
+        ycm.num_frames = len(counts)
+        return ycm, status
 
     def factorized_model_step_batched(self, z_string_dev, z_hdr, z_shape, ycm):
         """Rebuild the stride-32 coordinates from the y coordinates and decode z_hat
@@ -549,6 +551,7 @@ class DecompressionPipeline:
         m = self.decompression_model
         zkeys = ops.coords_pyramid_expect(ycm.keys, 3, 2, z_shape)
         zcm = CoordMap(zkeys, 5)
+        zcm.num_frames = ycm.num_frames
         eb = m.entropy_model.entropy_bottleneck
         sym, status = eb._decode_device(z_string_dev, z_hdr, None, zcm.n, zcm.n * eb.channels)
         zhat, _ = ops.factorized_dequant(sym.view(eb.channels, zcm.n), zcm.lex_perm(), eb.medians_d)

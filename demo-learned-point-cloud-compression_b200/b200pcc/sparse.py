@@ -32,6 +32,7 @@ class CoordMap:
         self.frame_off_host = None  # set by build_pyramid
         self.frame_off_dev = None   # int32 [num_frames+1] device row offsets (levels made by build_pyramid)
         self.frame_counts = None    # the same as host row counts
+        self.num_frames = None      # frames in the set when the owner knows it (bounds the frame bits of sort keys)
         self.up1 = None             # host-known upper bounds on the number of coordinates one / two levels
         self.up2 = None             # coarser (exact where the coarser maps exist); None = unknown
 
@@ -66,7 +67,10 @@ class CoordMap:
     def lex_perm(self) -> torch.Tensor:
         """perm[r] = row holding canonical (b,x,y,z) rank r."""
         if self._lex is None:
-            self._lex = ops.lex_order(self.keys)
+            # the set's coordinates are multiples of its stride; a set with per-frame counts knows its frame count
+            nf = self.num_frames if self.num_frames is not None else (len(self.frame_counts) if self.frame_counts is not None else None)
+            bits = 16 if nf is None else max(0, (int(nf) - 1).bit_length())
+            self._lex = ops.lex_order(self.keys, self.log2_stride, bits)
         return self._lex
 
     def downsample(self) -> "CoordMap":

@@ -261,7 +261,9 @@ __global__ void k_frame_offsets(const uint64_t* __restrict__ keys, int64_t n, in
   off[b] = (int32_t)lo;
 }
 
-__global__ void k_lex_keys(const uint64_t* __restrict__ keys, int64_t n, uint64_t* __restrict__ lex,
+// shift = log2 of the tensor stride: coordinates are multiples of it, so their low bits carry nothing and each
+// coordinate takes cb = 16 - shift bits of the sort key (fewer radix passes); shift = 0 is the general form.
+__global__ void k_lex_keys(const uint64_t* __restrict__ keys, int64_t n, int shift, uint64_t* __restrict__ lex,
                            int32_t* __restrict__ row) {
   pdl_trigger();
   pdl_wait();
@@ -269,8 +271,9 @@ __global__ void k_lex_keys(const uint64_t* __restrict__ keys, int64_t n, uint64_
   if (i >= n) return;
   int b, x, y, z;
   unpack_key(keys[i], b, x, y, z);
-  lex[i] = ((uint64_t)b << 48) | ((uint64_t)(x + 32768) << 32) | ((uint64_t)(y + 32768) << 16) |
-           (uint64_t)(z + 32768);
+  const int cb = 16 - shift;
+  lex[i] = ((uint64_t)b << (3 * cb)) | ((uint64_t)((uint32_t)(x + 32768) >> shift) << (2 * cb)) |
+           ((uint64_t)((uint32_t)(y + 32768) >> shift) << cb) | (uint64_t)((uint32_t)(z + 32768) >> shift);
   row[i] = (int32_t)i;
 }
 
@@ -718,7 +721,14 @@ int64_t pcc_lex_order_workspace_bytes(int64_t n) {
 }
 int pcc_lex_order(const uint64_t* keys, int64_t n, int32_t* perm, void* ws, int64_t ws_bytes,
                   pcc_stream_t s) {
-  PCC_CHECK_ARG(n >= 0 && n < (1ll << 31));
+  return pcc_lex_order_bits(keys, n, 0, 16, perm, ws, ws_bytes, s);
+}
+
+// log2_stride: every coordinate is a multiple of 2^log2_stride (the tensor stride of the set); frame_bits: the frame
+// index is below 2^frame_bits.  The sort key then has 3 (16 - log2_stride) + frame_bits significant bits.
+int pcc_lex_order_bits(const uint64_t* keys, int64_t n, int log2_stride, int frame_bits, int32_t* perm, void* ws,
+                       int64_t ws_bytes, pcc_stream_t s) {
+  PCC_CHECK_ARG(n >= 0 && n < (1ll << 31) && log2_stride >= 0 && log2_stride <= 15 && frame_bits >= 0 && frame_bits <= 16);
   if (n == 0) return PCC_OK;
   PCC_CHECK_ARG(keys && perm && ws);
   cudaStream_t st = as_stream(s);
@@ -732,10 +742,12 @@ int pcc_lex_order(const uint64_t* keys, int64_t n, int32_t* perm, void* ws, int6
     set_error("pcc_lex_order: workspace too small");
     return PCC_E_WORKSPACE;
   }
-  launch_pdl(k_lex_keys, dim3(blocks_for(n)), dim3(kThreads), 0, st, keys, n, lex, row);
+  launch_pdl(k_lex_keys, dim3(blocks_for(n)), dim3(kThreads), 0, st, keys, n, log2_stride, lex, row);
   PCC_LAUNCHED();
+  int end_bit = 3 * (16 - log2_stride) + frame_bits;
+  if (end_bit < 1) end_bit = 1;
   PCC_CUDA(cub::DeviceRadixSort::SortPairs(sort_ws, sort_b, lex, lex_sorted, row, perm, (int)n, 0,
-                                           64, st));
+                                           end_bit, st));
   g_launches.fetch_add(1);
   return PCC_OK;
 }

@@ -183,6 +183,10 @@ int pcc_frame_offsets(const uint64_t* keys, int64_t n, int32_t num_frames, int32
 int64_t pcc_lex_order_workspace_bytes(int64_t n);
 int pcc_lex_order(const uint64_t* keys, int64_t n, int32_t* perm, void* ws, int64_t ws_bytes,
                   pcc_stream_t s);
+/* Same order with fewer radix passes when the caller knows that every coordinate is a multiple of 2^log2_stride (the
+ * set's tensor stride) and that frame indices are below 2^frame_bits. */
+int pcc_lex_order_bits(const uint64_t* keys, int64_t n, int log2_stride, int frame_bits, int32_t* perm, void* ws,
+                       int64_t ws_bytes, pcc_stream_t s);
 
 /* Lossless coordinate coder ("OCT2" streams): fills the slot the reference fills
  * with gpcc_encode / gpcc_decode -- a G-PCC tmc3 subprocess over temporary PLY files
