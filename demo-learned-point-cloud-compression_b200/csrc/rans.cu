@@ -135,7 +135,12 @@ k_rans_prepare(const int32_t* __restrict__ sym, const uint16_t* __restrict__ idx
 }
 
 constexpr int kEncWarps = 4;      // segments per CTA
-constexpr int kChunk = 8;         // rounds whose inputs are prefetched together
+constexpr int kChunk = 8;         // decoder: rounds whose table indexes are prefetched together
+// encoder: three words per round are prefetched (entry, escape payload, escape ballot), double buffered.  With 8 rounds
+// per chunk those 48 registers pushed the kernel to 72 registers and one spilled value -- the store of a just-loaded
+// word to local memory waited for its load, 14 % of the kernel's samples, and the chunk's first use another 12 %
+// (profiles/r2y_rans_encode_ncu.txt).  Four rounds still lead the loads by ~2500 cycles.
+constexpr int kEncChunk = 4;
 constexpr uint32_t kInactive = 0xffffffffu;
 
 // Pass B: one warp per segment, rounds in reverse.  State update only; pass A's per-symbol words
@@ -165,10 +170,10 @@ k_rans_encode(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ 
   const uint32_t* em_seg = escmask + (start >> 5);
   uint32_t x = kRansL;
   int32_t wpos = 0;
-  uint32_t cur[kChunk], nxt[kChunk], cur_raw[kChunk], nxt_raw[kChunk], cur_em[kChunk], nxt_em[kChunk];
-  auto load_chunk = [&](int32_t rb, uint32_t (&buf)[kChunk], uint32_t (&braw)[kChunk], uint32_t (&bem)[kChunk]) {
+  uint32_t cur[kEncChunk], nxt[kEncChunk], cur_raw[kEncChunk], nxt_raw[kEncChunk], cur_em[kEncChunk], nxt_em[kEncChunk];
+  auto load_chunk = [&](int32_t rb, uint32_t (&buf)[kEncChunk], uint32_t (&braw)[kEncChunk], uint32_t (&bem)[kEncChunk]) {
 #pragma unroll
-    for (int k = 0; k < kChunk; ++k) {   // rounds rb-1 ... rb-kChunk
+    for (int k = 0; k < kEncChunk; ++k) {   // rounds rb-1 ... rb-kEncChunk
       const int32_t r = rb - 1 - k;
       const int32_t li = r * 32 + lane;
       bem[k] = r >= 0 ? __ldg(em_seg + r) : 0u;
@@ -177,10 +182,10 @@ k_rans_encode(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ 
     }
   };
   load_chunk(rounds, cur, cur_raw, cur_em);
-  for (int32_t rb = rounds; rb > 0; rb -= kChunk) {
-    load_chunk(rb - kChunk, nxt, nxt_raw, nxt_em);
+  for (int32_t rb = rounds; rb > 0; rb -= kEncChunk) {
+    load_chunk(rb - kEncChunk, nxt, nxt_raw, nxt_em);
 #pragma unroll
-    for (int k = 0; k < kChunk; ++k) {
+    for (int k = 0; k < kEncChunk; ++k) {
       const int32_t r = rb - 1 - k;
       if (r < 0) break;
       const uint32_t pk = cur[k];
@@ -224,7 +229,7 @@ k_rans_encode(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ 
       }
     }
 #pragma unroll
-    for (int k = 0; k < kChunk; ++k) {
+    for (int k = 0; k < kEncChunk; ++k) {
       cur[k] = nxt[k];
       cur_raw[k] = nxt_raw[k];
       cur_em[k] = nxt_em[k];

@@ -1,5 +1,4 @@
-# round 2, call 25: ncu --set full (with source) of the lane-rANS decoder and encoder on the cfg-2-shaped stream
+# round 2, call 26: lane encoder with 4-round prefetch chunks (no spill): coder tests, coder timing
 set -x
-ncu --set full --clock-control none --import-source on -k regex:k_rans_decode -s 1 -c 1 -f -o gpurun_out/r2y_rans_decode python tools/rans_bench.py --reps 1 --segs 16384 > gpurun_out/r2y_rans_decode_ncu.log 2>&1; echo "rc $?"
-ncu --set full --clock-control none --import-source on -k regex:k_rans_encode -s 1 -c 1 -f -o gpurun_out/r2y_rans_encode python tools/rans_bench.py --reps 1 --segs 16384 > gpurun_out/r2y_rans_encode_ncu.log 2>&1; echo "rc $?"
-ls -la gpurun_out/*.ncu-rep
+python -m pytest tests/test_gpu_entropy.py tests/test_gpu_faults.py tests/test_gpu_pipeline.py -m gpu -x -q > gpurun_out/r2z_pytest.log 2>&1; echo "pytest rc $?"; tail -n 2 gpurun_out/r2z_pytest.log
+python tools/rans_bench.py --reps 5 > gpurun_out/r2z_rans_segs.txt 2>&1; cat gpurun_out/r2z_rans_segs.txt
