@@ -29,9 +29,6 @@ int sm_count() {
   int d = 0;
   if (cudaGetDevice(&d) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, d) != cudaSuccess || n <= 0)
     n = 148;
-  // PCC_CONV_SMS (measurements): cap the persistent convolution grids, leaving SMs to kernels of another stream
-  const char* cap = getenv("PCC_CONV_SMS");
-  if (cap && atoi(cap) > 0 && atoi(cap) < n) n = atoi(cap);
   cache[dev].store(n, std::memory_order_release);
   return n;
 }
