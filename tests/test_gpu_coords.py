@@ -167,3 +167,49 @@ def test_empty_inputs(dev):
     k = ops.keys_from_coords(e)
     u, src = ops.sort_unique(k)
     assert u.numel() == 0 and src.numel() == 0
+
+
+def test_sort_and_lex_with_known_zero_bits_equal_the_general_calls(frames, dev):
+    """pcc_sort_unique_bits / pcc_lex_order_bits skip the radix passes of bits the caller knows to be zero: same results
+    as the 64-bit calls on multi-frame sets with negative coordinates, at strides 1 and 8."""
+    from b200pcc import ops
+    C, _ = stack_frames(frames)                      # two frames (b = 0, 1), coordinates straddle zero
+    k_all = ops.keys_from_coords(torch.from_numpy(np.ascontiguousarray(C, np.int32)).to(dev))
+    perm = torch.randperm(k_all.shape[0], device=dev)
+    shuffled = k_all[perm].contiguous()
+    u0, s0 = ops.sort_unique(shuffled)
+    for bits in (49, 50, 56, 64):                    # 2 frames need 48 + 1 bits
+        u1, s1 = ops.sort_unique(shuffled, key_bits=bits)
+        assert torch.equal(u0, u1) and torch.equal(s0, s1), bits
+    # canonical order at stride 1 and at stride 8 (coordinates are multiples of 8 there)
+    p0 = ops.lex_order(u0)
+    for fb in (1, 2, 16):
+        assert torch.equal(ops.lex_order(u0, 0, fb), p0), fb
+    C8 = C.copy()
+    C8[:, 1:] = np.floor_divide(C8[:, 1:], 8) * 8
+    k8, _ = ops.sort_unique(ops.keys_from_coords(torch.from_numpy(np.ascontiguousarray(C8, np.int32)).to(dev)))
+    q0 = ops.lex_order(k8)
+    for l2, fb in ((3, 1), (3, 16), (2, 1), (0, 1)):
+        assert torch.equal(ops.lex_order(k8, l2, fb), q0), (l2, fb)
+    ref = S.sort_order_reference(ops.coords_from_keys(k8).cpu().numpy())
+    assert np.array_equal(q0.cpu().numpy(), ref)
+
+
+def test_zero_unkept_rows_matches_numpy(dev):
+    """pcc_zero_unkept_rows: rows not listed in keep (ascending) become zero, the others stay bit for bit; edge cases
+    keep = nothing, keep = everything, first / last row kept or not, long gaps."""
+    from b200pcc import ops
+    rng = np.random.default_rng(5)
+    n, c = 5003, 32
+    x = torch.randn((n, c), device=dev).to(torch.bfloat16)
+    cases = [np.array([], np.int32), np.arange(n, dtype=np.int32), np.array([0], np.int32), np.array([n - 1], np.int32),
+             np.sort(rng.choice(n, 1777, replace=False)).astype(np.int32),
+             np.concatenate([np.arange(10), np.arange(4000, 4003)]).astype(np.int32)]
+    for keep in cases:
+        y = x.clone()
+        ops.zero_unkept_rows(y, torch.from_numpy(keep).to(dev))
+        want = torch.zeros_like(x)
+        if len(keep):
+            idx = torch.from_numpy(keep.astype(np.int64)).to(dev)
+            want[idx] = x[idx]
+        assert torch.equal(y.view(torch.int16), want.view(torch.int16)), len(keep)
