@@ -61,9 +61,18 @@ class _StageTimer:
         self.order = order if _NVTX else None
         self.prefix = prefix
         self.open = False
+        self.dev = None
+
+    _POOL = threading.local()      # timing events are recycled per thread (creating one costs more than recording it)
 
     def mark(self, name):
-        ev = torch.cuda.Event(enable_timing=True)
+        pools = getattr(self._POOL, "free", None)
+        if pools is None:
+            pools = self._POOL.free = {}
+        if self.dev is None:
+            self.dev = torch.cuda.current_device()       # an event belongs to the device it was first recorded on
+        free = pools.setdefault(self.dev, [])
+        ev = free.pop() if free else torch.cuda.Event(enable_timing=True)
         ev.record()
         self.marks.append((name, ev, time.time()))
         if self.order is not None:
@@ -82,6 +91,10 @@ class _StageTimer:
         out = {}
         for (n0, e0, _), (n1, e1, _) in zip(self.marks[:-1], self.marks[1:]):
             out[n1] = out.get(n1, 0.0) + e0.elapsed_time(e1) * 1e-3
+        pools = getattr(self._POOL, "free", None)
+        if pools is not None and self.dev is not None and len(pools.setdefault(self.dev, [])) < 64:
+            pools[self.dev].extend(ev for _, ev, _ in self.marks)      # (resolve() runs after the call's final sync)
+        self.marks = []
         return out
 
 
