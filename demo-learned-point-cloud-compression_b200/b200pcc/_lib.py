@@ -45,6 +45,7 @@ SIGNATURES = {
     "pcc_launch_count": (I64, []),
     "pcc_kmap_count_pairs": (INT, [P, I64, I64, INT, P, P]),
     "pcc_fault_fetch": (INT, [P, P]),
+    "pcc_fetch_words": (INT, [P, I32, I32, P, P]),
     "pcc_fault_string": (C.c_char_p, [I32]),
     "pcc_debug_inject": (INT, [I32]),
     "pcc_debug_trace_words": (I64, []),

@@ -83,13 +83,22 @@ class stream_scope:
     The cached handle is thread local."""
 
     def __enter__(self):
-        self.prev = getattr(_TLS, "stream", None)
-        _TLS.stream = torch.cuda.current_stream().cuda_stream
+        self.prev = (getattr(_TLS, "stream", None), getattr(_TLS, "stream_obj", None))
+        so = torch.cuda.current_stream()
+        _TLS.stream_obj = so
+        _TLS.stream = so.cuda_stream
         return self
 
     def __exit__(self, *exc):
-        _TLS.stream = self.prev
+        _TLS.stream, _TLS.stream_obj = self.prev
         return False
+
+
+def stream_obj():
+    """The torch Stream the current call runs on (cached by stream_scope; event.record(stream_obj()) skips torch's
+    current-stream lookup, which costs more than the record itself)."""
+    so = getattr(_TLS, "stream_obj", None)
+    return so if so is not None else torch.cuda.current_stream()
 
 
 def _ptr(t: Optional[torch.Tensor]):
@@ -230,16 +239,31 @@ def fault_message(code: int) -> str:
 
 
 def verify_deferred(extra_status=(), device=None):
-    """One device->host copy for every deferred count and status word -- and, when `device` is given, the device
-    fault word; raises PccError on mismatch."""
+    """One launch and one device->host copy for every deferred count and status word -- and, when `device` is given,
+    the device fault word; raises PccError on mismatch.  (pcc_fetch_words gathers the words; the copy lands in a pinned
+    buffer of this thread.  Counters must be int32 device words.)"""
     items = list(_deferred_list())
     _TLS.deferred = []
-    tensors = [c.reshape(1).to(torch.int32) for c, _, _ in items] + [t.reshape(1).to(torch.int32) for t, _ in extra_status]
-    if device is not None:
-        tensors.append(fault_fetch(device))
-    if not tensors:
+    words = [c for c, _, _ in items] + [t for t, _ in extra_status]
+    if not words and device is None:
         return
-    host = torch.cat(tensors).cpu().numpy()
+    if len(words) >= 47 or any(w.dtype != torch.int32 for w in words):      # (not on the codec's path) the general way
+        tensors = [w.reshape(1).to(torch.int32) for w in words]
+        if device is not None:
+            tensors.append(fault_fetch(device))
+        host = torch.cat(tensors).cpu().numpy()
+    else:
+        dev = device if device is not None else words[0].device
+        n = len(words)
+        srcs = (C.c_void_p * max(n, 1))(*[w.data_ptr() for w in words])
+        dst = torch.empty(n + 1, dtype=torch.int32, device=dev)
+        check(lib.pcc_fetch_words(srcs, n, 1 if device is not None else 0, _ptr(dst), _stream()))
+        pin = getattr(_TLS, "verify_pin", None)
+        if pin is None or pin.numel() < n + 1:
+            pin = _TLS.verify_pin = torch.empty(64, dtype=torch.int32, pin_memory=True)
+        pin[:n + 1].copy_(dst, non_blocking=True)
+        stream_obj().synchronize()
+        host = pin[:n + 1].numpy().copy() if device is not None else pin[:n].numpy().copy()
     if device is not None and int(host[-1]) != 0:
         raise _lib.PccError(fault_message(int(host[-1])))
     for (c, e, what), v in zip(items, host[:len(items)]):

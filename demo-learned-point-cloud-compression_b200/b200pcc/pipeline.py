@@ -73,7 +73,7 @@ class _StageTimer:
             self.dev = torch.cuda.current_device()       # an event belongs to the device it was first recorded on
         free = pools.setdefault(self.dev, [])
         ev = free.pop() if free else torch.cuda.Event(enable_timing=True)
-        ev.record()
+        ev.record(ops.stream_obj())
         self.marks.append((name, ev, time.time()))
         if self.order is not None:
             if self.open:

@@ -50,6 +50,10 @@ int64_t pcc_launch_count(void);
 #define PCC_FAULT_BLOCKMAP_FULL 1
 #define PCC_FAULT_PIPELINE_TIMEOUT 2
 int pcc_fault_fetch(int32_t* dst_dev, pcc_stream_t s);
+/* Every deferred check of a call in one launch: dst_dev[i] = *srcs[i] (srcs: HOST array of n < 48 device addresses of
+ * int32 counters / status words), dst_dev[n] = the fault word, fetched and cleared, when with_fault != 0.  The caller
+ * then reads dst_dev with one copy (decompress()'s single synchronisation). */
+int pcc_fetch_words(const int32_t* const* srcs_dev, int32_t n, int32_t with_fault, int32_t* dst_dev, pcc_stream_t s);
 const char* pcc_fault_string(int32_t code);
 /* Test hook: what = 1 makes the next k = 3 pcc_spconv_umma launch of this process drop one pipeline hand-off (and spin
  * briefly instead of for seconds), so that the timeout path can be exercised; 0 disarms. */
