@@ -333,7 +333,7 @@ class SynthesisTransform(_Module):
         f = self.pre(f, None, cm.n, relu=True)
         inter = []
         prev = getattr(y_hat, "frame_counts", None)
-        kd_all = torch.tensor([list(map(int, k[i])) for i in range(3)], dtype=torch.int32).to(dev, non_blocking=True)
+        kd_all = torch.tensor([list(map(int, k[i])) for i in range(3)], dtype=torch.int32, pin_memory=True).to(dev, non_blocking=True)   # (pinned: a pageable copy waits behind other callers' transfers)
         for i in range(3):
             f = self.up[i](f, relu=True)
             parent = cm
@@ -398,7 +398,7 @@ def _synthesis_program(self, f, cm, k, num_frames, prev, on_geometry=None):
         n_l.append(8 * n)
         n, prev = sum(kept), kept
     pr = prg.Program(dev)
-    kd_all = torch.tensor([list(map(int, k[i])) for i in range(3)], dtype=torch.int32).to(dev, non_blocking=True)
+    kd_all = torch.tensor([list(map(int, k[i])) for i in range(3)], dtype=torch.int32, pin_memory=True).to(dev, non_blocking=True)   # (pinned: a pageable copy waits behind other callers' transfers)
     counts = torch.empty(3, dtype=torch.int32, device=dev)
     n = cm.n
     cur = pr.alloc(n * self.pre.cout * 2)

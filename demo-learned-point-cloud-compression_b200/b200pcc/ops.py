@@ -546,7 +546,7 @@ def octree_encode(keys: torch.Tensor, frame_off_dev: torch.Tensor, frame_counts,
     offs = np.zeros(nf + 1, dtype=np.int64)
     offs[1:] = np.cumsum(bounds)
     out = torch.empty(max(int(offs[-1]), 4), dtype=torch.uint8, device=dev)
-    out_off = torch.from_numpy(offs[:nf].copy()).to(dev, non_blocking=True)
+    out_off = torch.from_numpy(offs[:nf].copy()).pin_memory().to(dev, non_blocking=True)      # (pinned: see verify_deferred)
     sizes = torch.empty(max(nf, 1), dtype=torch.int32, device=dev)
     n = keys.shape[0]
     ws = workspace(lib.pcc_octree_encode_workspace_bytes(n, nf), dev, "octree")
