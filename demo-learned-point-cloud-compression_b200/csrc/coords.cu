@@ -221,6 +221,21 @@ __global__ void k_scatter_runs_dc(const uint64_t* __restrict__ keys, const int32
   run_of[i] = r;
   if (i == n - 1) *n_out = incl[i];
 }
+// First row of frame b in a sorted key array: lower bound of b << 48.  The ends are looked at first -- frame 0 starts at
+// row 0 and a frame index beyond the last key's starts at n -- so a one-frame GOP needs two loads per boundary instead
+// of a 21-step chain of dependent loads (13 us per launch on 1.8 M keys, six to nine launches per GOP).
+__device__ __forceinline__ int64_t frame_lower_bound(const uint64_t* __restrict__ keys, int64_t n, int b) {
+  const uint64_t target = (uint64_t)b << 48;
+  if (n <= 0 || keys[0] >= target) return 0;
+  if (keys[n - 1] < target) return n;
+  int64_t lo = 1, hi = n - 1;        // keys[0] < target <= keys[n - 1]
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (keys[mid] < target) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
 __global__ void k_frame_offsets_dc(const uint64_t* __restrict__ keys, const int32_t* __restrict__ n_dev,
                                    int64_t nmax, int nf, int32_t* __restrict__ off) {
   pdl_trigger();
@@ -228,13 +243,7 @@ __global__ void k_frame_offsets_dc(const uint64_t* __restrict__ keys, const int3
   int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b > nf) return;
   const int64_t n = n_dev ? (int64_t)*n_dev : nmax;
-  uint64_t target = (uint64_t)b << 48;
-  int64_t lo = 0, hi = n;
-  while (lo < hi) {
-    int64_t mid = (lo + hi) >> 1;
-    if (keys[mid] < target) lo = mid + 1; else hi = mid;
-  }
-  off[b] = (int32_t)lo;
+  off[b] = (int32_t)frame_lower_bound(keys, n, b);
 }
 
 __global__ void k_children(const uint64_t* __restrict__ keys, int64_t n, int shift,
@@ -252,13 +261,7 @@ __global__ void k_frame_offsets(const uint64_t* __restrict__ keys, int64_t n, in
   pdl_wait();
   int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b > nf) return;
-  uint64_t target = (uint64_t)b << 48;
-  int64_t lo = 0, hi = n;
-  while (lo < hi) {
-    int64_t mid = (lo + hi) >> 1;
-    if (keys[mid] < target) lo = mid + 1; else hi = mid;
-  }
-  off[b] = (int32_t)lo;
+  off[b] = (int32_t)frame_lower_bound(keys, n, b);
 }
 
 // shift = log2 of the tensor stride: coordinates are multiples of it, so their low bits carry nothing and each
